@@ -1,0 +1,839 @@
+// dvo_cuda.cu — C-ABI (include/dvo_cuda.h) over the sm_100a kernels in dvo_kernels.cuh.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false -lineinfo -O3 -shared
+// No CPU fallback: every entry point needs a CUDA device.
+#include "dvo_kernels.cuh"
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <random>
+#include <string>
+#include <vector>
+
+using namespace dvo;
+
+struct SlotHost {
+    void* base = nullptr;
+    bool in_use = false;
+    SlotDev dev{};
+};
+
+struct dvo_ctx {
+    dvo_params P{};
+    Consts c{};
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    std::vector<SlotHost> slots;
+    size_t slot_bytes = 0;
+    SlotDev* d_slots = nullptr;
+    TrackState* d_ts = nullptr;
+    MapState* d_ms = nullptr;
+    VoState* d_vo = nullptr;
+    int* d_hist = nullptr;
+    PoseTab* d_tab = nullptr;
+    double* d_partials = nullptr;
+    int max_blocks = 0, ppt = 1;
+    dvo_iter_log* d_log = nullptr;
+    int log_cap = 0;
+    uint8_t* d_flags = nullptr;
+    uint8_t* d_mask = nullptr;
+    unsigned int* d_blockcnt = nullptr;
+    int nblk_top = 0;
+    int* d_winner = nullptr;
+    float* d_tmp = nullptr;
+    uint32_t* d_rng = nullptr;
+    float* d_stage_in = nullptr;   // [S][in_h][in_w]
+    float* d_stage[3] = {nullptr, nullptr, nullptr}; // depth/sigma/age uploads, download staging
+    float* d_small = nullptr;      // [S][32] small vectors (xi, poses)
+    int* d_ismall = nullptr;       // small int scratch
+    void* h_pinned = nullptr;      // pinned staging for small readbacks
+    size_t h_pinned_bytes = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    uint64_t launches = 0;
+    // gn timing
+    bool gn_timing = false;
+    std::vector<cudaEvent_t> gn_ev;
+    size_t gn_ev_used = 0;
+    // VO host mirror
+    int vo_frame_id = -1;
+    int vo_last_slot = -1;
+    std::mt19937 engine; // default seed 5489, src/math/gaussian.cpp:8
+};
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e__ = (call);                                                                  \
+        if (e__ != cudaSuccess) {                                                                  \
+            ctx->err = std::string(#call) + ": " + cudaGetErrorString(e__);                        \
+            return DVO_ERR_CUDA;                                                                   \
+        }                                                                                          \
+    } while (0)
+#define KCHECK()                                                                                   \
+    do {                                                                                           \
+        ctx->launches++;                                                                           \
+        cudaError_t e__ = cudaGetLastError();                                                      \
+        if (e__ != cudaSuccess) {                                                                  \
+            ctx->err = std::string("kernel launch: ") + cudaGetErrorString(e__);                   \
+            return DVO_ERR_CUDA;                                                                   \
+        }                                                                                          \
+    } while (0)
+#define ARG(cond, msg)                                                                             \
+    do {                                                                                           \
+        if (!(cond)) {                                                                             \
+            ctx->err = msg;                                                                        \
+            return DVO_ERR_ARG;                                                                    \
+        }                                                                                          \
+    } while (0)
+
+static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+extern "C" void dvo_params_default(dvo_params* p)
+{
+    memset(p, 0, sizeof(*p));
+    p->n_streams = 1;
+    p->width = 640; p->height = 480;
+    p->levels = 3; p->culls = 2; // system.hpp:47
+    const float K[9] = {7.93852356e+02f, 0.f, 3.77845917e+02f, 0.f, 7.96643677e+02f, 2.20205841e+02f, 0.f, 0.f, 1.f};
+    memcpy(p->K, K, sizeof K); // external/camera-calibration/data/logicool_00/config.yaml
+    p->max_frames = 64;
+    p->max_keyframes = 64;
+    p->min_residual = 5e-3f; p->min_update = 5e-4f; p->max_iterations = 15;
+    p->roi_level = 2; p->roi_x0 = 20; p->roi_x1 = 140; p->roi_y0 = 20; p->roi_y1 = 100;
+    p->min_depth = 0.20; p->sigma_lo = 0.01f; p->sigma_hi = 0.5f;
+    p->step_default = 2.0f; p->step_level1 = 1.5f; p->step_level2 = 1.0f;
+    p->map_roi_x0 = 16; p->map_roi_x1 = 144; p->map_roi_y0 = 12; p->map_roi_y1 = 108;
+    p->min_movement = 0.02f; p->max_forward = 6;
+    p->accept_depth_lo = 0.2f; p->accept_depth_hi = 6.0f; p->accept_sigma_hi = 0.5f;
+    p->rng_table = 1 << 22;
+}
+
+static int alloc_slot(dvo_ctx* ctx, int idx)
+{
+    SlotHost& sh = ctx->slots[idx];
+    if (sh.base) return DVO_OK;
+    CK(cudaMalloc(&sh.base, ctx->slot_bytes));
+    CK(cudaMemsetAsync(sh.base, 0, ctx->slot_bytes, ctx->stream));
+    char* p = (char*)sh.base;
+    const Consts& c = ctx->c;
+    auto take = [&](size_t bytes) { char* r = p; p += (bytes + 255) & ~(size_t)255; return r; };
+    for (int l = 0; l < c.L; l++) sh.dev.tex[l] = (float4*)take((size_t)c.S * c.lv[l].n * sizeof(float4));
+    for (int l = 0; l < c.L; l++) sh.dev.ds[l] = (float2*)take((size_t)c.S * c.lv[l].n * sizeof(float2));
+    for (int l = 0; l < c.L; l++) sh.dev.gray[l] = (float*)take((size_t)c.S * c.lv[l].n * sizeof(float));
+    sh.dev.age = (float*)take((size_t)c.S * c.lv[c.L - 1].n * sizeof(float));
+    sh.dev.xi = (float*)take((size_t)c.S * 6 * sizeof(float));
+    sh.dev.rel_xi = (float*)take((size_t)c.S * 6 * sizeof(float));
+    CK(cudaMemcpyAsync(ctx->d_slots + idx, &sh.dev, sizeof(SlotDev), cudaMemcpyHostToDevice, ctx->stream));
+    return DVO_OK;
+}
+
+extern "C" int dvo_create(dvo_ctx** out, const dvo_params* p)
+{
+    if (!out || !p) return DVO_ERR_ARG;
+    *out = nullptr;
+    dvo_ctx* ctx = new dvo_ctx();
+    *out = ctx; // returned even on failure so that dvo_last_error can be read
+    ctx->P = *p;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        ctx->err = "no CUDA device: libdvo_cuda has no CPU fallback";
+        return DVO_ERR_CUDA;
+    }
+    CK(cudaGetDevice(&ctx->device));
+    ARG(p->n_streams >= 1 && p->width > 0 && p->height > 0, "bad geometry");
+    ARG(p->levels >= 1 && p->levels <= MAXL && p->culls >= 0 && p->culls < 16, "bad levels/culls");
+    ARG(p->max_frames >= 2 && p->max_keyframes >= 1, "bad capacities");
+    Consts& c = ctx->c;
+    c.S = p->n_streams; c.L = p->levels; c.in_w = p->width; c.in_h = p->height; c.culls = p->culls;
+    const int bw = p->width >> p->culls, bh = p->height >> p->culls;
+    ARG((bw >> (p->levels - 1)) >= 1 && (bh >> (p->levels - 1)) >= 1, "image too small for the pyramid");
+    for (int l = 0; l < c.L; l++) {
+        const int t = c.L - 1 - l;
+        LevelGeom& g = c.lv[l];
+        g.w = bw >> t; g.h = bh >> t; g.n = g.w * g.h;
+        // Convert::cullIntrinsic (convert.cpp:22-29): K * (1/2^times) from the base level's K
+        const float s0 = (float)(1.0 / (double)(1 << p->culls));
+        float Kb[4] = {p->K[0], p->K[4], p->K[2], p->K[5]};
+        if (p->culls) for (float& v : Kb) v = v * s0;
+        const float s1 = (float)(1.0 / (double)(1 << t));
+        if (t) for (float& v : Kb) v = v * s1;
+        g.fx = Kb[0]; g.fy = Kb[1]; g.cx = Kb[2]; g.cy = Kb[3];
+    }
+    c.max_kf = p->max_keyframes;
+    c.max_iter = p->max_iterations;
+    c.roi_level = p->roi_level; c.roi_x0 = p->roi_x0; c.roi_x1 = p->roi_x1; c.roi_y0 = p->roi_y0; c.roi_y1 = p->roi_y1;
+    {   // (double)d < min_depth  <=>  d < smallest float >= min_depth
+        float f = (float)p->min_depth;
+        if ((double)f < p->min_depth) f = nextafterf(f, INFINITY);
+        c.min_depth_f = f;
+    }
+    c.sigma_lo = p->sigma_lo; c.sigma_hi = p->sigma_hi;
+    c.step_default = p->step_default; c.step_level1 = p->step_level1; c.step_level2 = p->step_level2;
+    c.map_x0 = p->map_roi_x0; c.map_x1 = p->map_roi_x1; c.map_y0 = p->map_roi_y0; c.map_y1 = p->map_roi_y1;
+    c.min_movement = p->min_movement; c.max_forward = p->max_forward;
+    c.acc_d_lo = p->accept_depth_lo; c.acc_d_hi = p->accept_depth_hi; c.acc_s_hi = p->accept_sigma_hi;
+    c.rng_table = (unsigned)(p->rng_table > 0 ? p->rng_table : (1 << 22));
+
+    CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    CK(cudaEventCreate(&ctx->ev0));
+    CK(cudaEventCreate(&ctx->ev1));
+    const int S = c.S, ntop = c.lv[c.L - 1].n;
+    size_t sb = 0;
+    auto rnd = [](size_t b) { return (b + 255) & ~(size_t)255; };
+    for (int l = 0; l < c.L; l++) sb += rnd((size_t)S * c.lv[l].n * 16) + rnd((size_t)S * c.lv[l].n * 8) + rnd((size_t)S * c.lv[l].n * 4);
+    sb += rnd((size_t)S * ntop * 4) + 2 * rnd((size_t)S * 24);
+    ctx->slot_bytes = sb;
+    ctx->slots.resize(p->max_frames);
+    CK(cudaMalloc(&ctx->d_slots, sizeof(SlotDev) * p->max_frames));
+    CK(cudaMemset(ctx->d_slots, 0, sizeof(SlotDev) * p->max_frames));
+    CK(cudaMalloc(&ctx->d_ts, sizeof(TrackState) * S));
+    CK(cudaMemset(ctx->d_ts, 0, sizeof(TrackState) * S));
+    CK(cudaMalloc(&ctx->d_ms, sizeof(MapState) * S));
+    CK(cudaMemset(ctx->d_ms, 0, sizeof(MapState) * S));
+    CK(cudaMalloc(&ctx->d_vo, sizeof(VoState) * S));
+    CK(cudaMalloc(&ctx->d_hist, sizeof(int) * (size_t)S * c.max_kf));
+    CK(cudaMalloc(&ctx->d_tab, sizeof(PoseTab) * (size_t)S * c.max_kf));
+    // GN launch shape: enough blocks to fill 148 SMs several times over, few enough that the
+    // fixed-order reduction of block partials in the kernel tail stays short.
+    {
+        const double total = (double)S * ntop;
+        int ppt = 1;
+        while (ppt < 8 && total / (256.0 * ppt) > 148.0 * 16) ppt *= 2;
+        ctx->ppt = ppt;
+        ctx->max_blocks = cdiv(ntop, GN_THREADS * ppt);
+    }
+    CK(cudaMalloc(&ctx->d_partials, sizeof(double) * 32 * (size_t)S * ctx->max_blocks));
+    ctx->log_cap = c.L * c.max_iter;
+    CK(cudaMalloc(&ctx->d_log, sizeof(dvo_iter_log) * (size_t)S * ctx->log_cap));
+    CK(cudaMemset(ctx->d_log, 0, sizeof(dvo_iter_log) * (size_t)S * ctx->log_cap));
+    size_t nmax = 0;
+    for (int l = 0; l < c.L; l++) nmax = nmax > (size_t)c.lv[l].n ? nmax : (size_t)c.lv[l].n;
+    CK(cudaMalloc(&ctx->d_flags, (size_t)S * ntop));
+    CK(cudaMalloc(&ctx->d_mask, (size_t)S * nmax));
+    ctx->nblk_top = cdiv(ntop, 256);
+    CK(cudaMalloc(&ctx->d_blockcnt, sizeof(unsigned) * (size_t)S * ctx->nblk_top));
+    CK(cudaMalloc(&ctx->d_winner, sizeof(int) * (size_t)S * ntop));
+    CK(cudaMalloc(&ctx->d_tmp, sizeof(float) * (size_t)S * ntop));
+    CK(cudaMalloc(&ctx->d_stage_in, sizeof(float) * (size_t)S * c.in_w * c.in_h));
+    for (int k = 0; k < 3; k++) CK(cudaMalloc(&ctx->d_stage[k], sizeof(float) * (size_t)S * c.in_w * c.in_h));
+    CK(cudaMalloc(&ctx->d_small, sizeof(float) * (size_t)S * 64));
+    CK(cudaMalloc(&ctx->d_ismall, sizeof(int) * (size_t)(S > 4096 ? S : 4096)));
+    ctx->h_pinned_bytes = sizeof(float) * (size_t)S * 64 + sizeof(dvo_iter_log) * (size_t)S * ctx->log_cap + sizeof(TrackState) * (size_t)S;
+    CK(cudaMallocHost(&ctx->h_pinned, ctx->h_pinned_bytes));
+    {   // mt19937 replay table (src/math/gaussian.cpp:8): raw 32-bit outputs, default seed
+        std::vector<uint32_t> raw(c.rng_table);
+        for (auto& v : raw) v = (uint32_t)ctx->engine();
+        CK(cudaMalloc(&ctx->d_rng, sizeof(uint32_t) * (size_t)c.rng_table));
+        CK(cudaMemcpy(ctx->d_rng, raw.data(), sizeof(uint32_t) * (size_t)c.rng_table, cudaMemcpyHostToDevice));
+    }
+    int rc = dvo_vo_reset(ctx);
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(ctx->stream));
+    return DVO_OK;
+}
+
+extern "C" void dvo_destroy(dvo_ctx* ctx)
+{
+    if (!ctx) return;
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    for (auto& s : ctx->slots) if (s.base) cudaFree(s.base);
+    cudaFree(ctx->d_slots); cudaFree(ctx->d_ts); cudaFree(ctx->d_ms); cudaFree(ctx->d_vo); cudaFree(ctx->d_hist);
+    cudaFree(ctx->d_tab); cudaFree(ctx->d_partials); cudaFree(ctx->d_log); cudaFree(ctx->d_flags); cudaFree(ctx->d_mask);
+    cudaFree(ctx->d_blockcnt); cudaFree(ctx->d_winner); cudaFree(ctx->d_tmp); cudaFree(ctx->d_rng); cudaFree(ctx->d_stage_in);
+    for (int k = 0; k < 3; k++) cudaFree(ctx->d_stage[k]);
+    cudaFree(ctx->d_small); cudaFree(ctx->d_ismall);
+    if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
+    for (auto e : ctx->gn_ev) cudaEventDestroy(e);
+    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+extern "C" const char* dvo_last_error(const dvo_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+extern "C" int dvo_sync(dvo_ctx* ctx) { CK(cudaStreamSynchronize(ctx->stream)); return DVO_OK; }
+extern "C" uint64_t dvo_launch_count(const dvo_ctx* ctx) { return ctx->launches; }
+
+extern "C" int dvo_level_size(const dvo_ctx* ctx, int level, int* w, int* h)
+{
+    if (!ctx || level < 0 || level >= ctx->c.L) return DVO_ERR_ARG;
+    *w = ctx->c.lv[level].w; *h = ctx->c.lv[level].h;
+    return DVO_OK;
+}
+extern "C" int dvo_level_K(const dvo_ctx* ctx, int level, float K[9])
+{
+    if (!ctx || level < 0 || level >= ctx->c.L) return DVO_ERR_ARG;
+    const LevelGeom& g = ctx->c.lv[level];
+    const float k[9] = {g.fx, 0, g.cx, 0, g.fy, g.cy, 0, 0, 1};
+    memcpy(K, k, sizeof k);
+    return DVO_OK;
+}
+extern "C" void* dvo_host_alloc(size_t bytes)
+{
+    void* p = nullptr;
+    if (cudaMallocHost(&p, bytes) != cudaSuccess) return nullptr;
+    return p;
+}
+extern "C" void dvo_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+// ---- frames ---------------------------------------------------------------------------------
+static int find_free_slot(dvo_ctx* ctx, int* slot)
+{
+    for (size_t i = 0; i < ctx->slots.size(); i++)
+        if (!ctx->slots[i].in_use) {
+            int rc = alloc_slot(ctx, (int)i);
+            if (rc) return rc;
+            ctx->slots[i].in_use = true;
+            *slot = (int)i;
+            return DVO_OK;
+        }
+    ctx->err = "frame slots exhausted (dvo_params.max_frames)";
+    return DVO_ERR_SLOT;
+}
+static int check_slot(dvo_ctx* ctx, int slot)
+{
+    if (slot < 0 || slot >= (int)ctx->slots.size() || !ctx->slots[slot].in_use) {
+        ctx->err = "bad frame slot";
+        return DVO_ERR_SLOT;
+    }
+    return DVO_OK;
+}
+
+static int build_frame(dvo_ctx* ctx, int slot, const float* gray_dev)
+{
+    const Consts& c = ctx->c;
+    const SlotDev& sd = ctx->slots[slot].dev;
+    dim3 grid(cdiv(c.lv[c.L - 1].n, 256), c.S, c.L);
+    k_cull_gray<<<grid, 256, 0, ctx->stream>>>(c, gray_dev, sd);
+    KCHECK();
+    k_build_tex<<<grid, 256, 0, ctx->stream>>>(c, sd);
+    KCHECK();
+    return DVO_OK;
+}
+
+extern "C" int dvo_frame_create_dev(dvo_ctx* ctx, int* slot, const float* gray_dev)
+{
+    ARG(slot && gray_dev, "null argument");
+    int rc = find_free_slot(ctx, slot);
+    if (rc) return rc;
+    return build_frame(ctx, *slot, gray_dev);
+}
+
+extern "C" int dvo_frame_create(dvo_ctx* ctx, int* slot, const float* gray)
+{
+    ARG(slot && gray, "null argument");
+    const Consts& c = ctx->c;
+    CK(cudaMemcpyAsync(ctx->d_stage_in, gray, sizeof(float) * (size_t)c.S * c.in_w * c.in_h, cudaMemcpyHostToDevice, ctx->stream));
+    return dvo_frame_create_dev(ctx, slot, ctx->d_stage_in);
+}
+
+extern "C" int dvo_frame_release(dvo_ctx* ctx, int slot)
+{
+    int rc = check_slot(ctx, slot);
+    if (rc) return rc;
+    ctx->slots[slot].in_use = false;
+    return DVO_OK;
+}
+
+static int recull_ds(dvo_ctx* ctx, int slot)
+{
+    const Consts& c = ctx->c;
+    if (c.L < 2) return DVO_OK;
+    dim3 grid(cdiv(c.lv[c.L - 2].n, 256), c.S, c.L - 1);
+    k_cull_ds<<<grid, 256, 0, ctx->stream>>>(c, ctx->slots[slot].dev);
+    KCHECK();
+    return DVO_OK;
+}
+
+extern "C" int dvo_frame_set_depth(dvo_ctx* ctx, int slot, const float* depth, const float* sigma, const float* age, int full_res)
+{
+    int rc = check_slot(ctx, slot);
+    if (rc) return rc;
+    const Consts& c = ctx->c;
+    const LevelGeom& gt = c.lv[c.L - 1];
+    const int sw = full_res ? c.in_w : gt.w, sh = full_res ? c.in_h : gt.h;
+    const float* src[3] = {depth, sigma, age};
+    const float* dev[3] = {nullptr, nullptr, nullptr};
+    for (int k = 0; k < 3; k++)
+        if (src[k]) {
+            CK(cudaMemcpyAsync(ctx->d_stage[k], src[k], sizeof(float) * (size_t)c.S * sw * sh, cudaMemcpyHostToDevice, ctx->stream));
+            dev[k] = ctx->d_stage[k];
+        }
+    dim3 grid(cdiv(gt.n, 256), c.S);
+    k_set_top<<<grid, 256, 0, ctx->stream>>>(c, ctx->slots[slot].dev, dev[0], dev[1], dev[2], sw, sh, full_res ? c.culls : 0);
+    KCHECK();
+    rc = recull_ds(ctx, slot);
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(ctx->stream)); // host buffers may be pageable: do not return before the copies finish
+    return DVO_OK;
+}
+
+extern "C" int dvo_frame_download(dvo_ctx* ctx, int slot, int level, int kind, float* out)
+{
+    int rc = check_slot(ctx, slot);
+    if (rc) return rc;
+    const Consts& c = ctx->c;
+    ARG(level >= 0 && level < c.L && out, "bad level");
+    ARG(kind >= 0 && kind <= 5, "bad image kind");
+    ARG(kind != DVO_IMG_AGE || level == c.L - 1, "age exists on the finest level only");
+    const LevelGeom& g = c.lv[level];
+    dim3 grid(cdiv(g.n, 256), c.S);
+    k_extract<<<grid, 256, 0, ctx->stream>>>(c, ctx->slots[slot].dev, level, kind, ctx->d_stage[0]);
+    KCHECK();
+    CK(cudaMemcpyAsync(out, ctx->d_stage[0], sizeof(float) * (size_t)c.S * g.n, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return DVO_OK;
+}
+
+extern "C" int dvo_frame_set_xi(dvo_ctx* ctx, int slot, const float* xi, const float* rel_xi)
+{
+    int rc = check_slot(ctx, slot);
+    if (rc) return rc;
+    const size_t b = sizeof(float) * 6 * (size_t)ctx->c.S;
+    if (xi) CK(cudaMemcpyAsync(ctx->slots[slot].dev.xi, xi, b, cudaMemcpyHostToDevice, ctx->stream));
+    if (rel_xi) CK(cudaMemcpyAsync(ctx->slots[slot].dev.rel_xi, rel_xi, b, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return DVO_OK;
+}
+extern "C" int dvo_frame_get_xi(dvo_ctx* ctx, int slot, float* xi, float* rel_xi)
+{
+    int rc = check_slot(ctx, slot);
+    if (rc) return rc;
+    const size_t b = sizeof(float) * 6 * (size_t)ctx->c.S;
+    if (xi) CK(cudaMemcpyAsync(xi, ctx->slots[slot].dev.xi, b, cudaMemcpyDeviceToHost, ctx->stream));
+    if (rel_xi) CK(cudaMemcpyAsync(rel_xi, ctx->slots[slot].dev.rel_xi, b, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return DVO_OK;
+}
+
+// ---- tracking -------------------------------------------------------------------------------
+extern "C" int dvo_warp_image(dvo_ctx* ctx, int ref_slot, int level, const float* xi, float* out)
+{
+    int rc = check_slot(ctx, ref_slot);
+    if (rc) return rc;
+    const Consts& c = ctx->c;
+    ARG(level >= 0 && level < c.L && xi && out, "bad argument");
+    const LevelGeom& g = c.lv[level];
+    CK(cudaMemcpyAsync(ctx->d_small, xi, sizeof(float) * 6 * (size_t)c.S, cudaMemcpyHostToDevice, ctx->stream));
+    dim3 grid(cdiv(g.n, 256), c.S);
+    k_warp_image<<<grid, 256, 0, ctx->stream>>>(c, ctx->slots[ref_slot].dev, level, ctx->d_small, ctx->d_stage[0]);
+    KCHECK();
+    CK(cudaMemcpyAsync(out, ctx->d_stage[0], sizeof(float) * (size_t)c.S * g.n, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return DVO_OK;
+}
+
+static int launch_gn(dvo_ctx* ctx, uint8_t* mask)
+{
+    const Consts& c = ctx->c;
+    GnArgs a;
+    a.st = ctx->d_ts; a.partials = ctx->d_partials; a.max_blocks = ctx->max_blocks;
+    a.log = ctx->d_log; a.log_cap = ctx->log_cap; a.mask = mask; a.ppt = ctx->ppt;
+    dim3 grid(ctx->max_blocks, c.S);
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (ctx->gn_timing) {
+        if (ctx->gn_ev_used + 2 > ctx->gn_ev.size()) {
+            for (int k = 0; k < 2; k++) {
+                cudaEvent_t e;
+                CK(cudaEventCreate(&e));
+                ctx->gn_ev.push_back(e);
+            }
+        }
+        e0 = ctx->gn_ev[ctx->gn_ev_used++];
+        e1 = ctx->gn_ev[ctx->gn_ev_used++];
+        CK(cudaEventRecord(e0, ctx->stream));
+    }
+    switch (ctx->ppt) {
+    case 1: k_gn_step<1><<<grid, GN_THREADS, 0, ctx->stream>>>(c, a); break;
+    case 2: k_gn_step<2><<<grid, GN_THREADS, 0, ctx->stream>>>(c, a); break;
+    case 4: k_gn_step<4><<<grid, GN_THREADS, 0, ctx->stream>>>(c, a); break;
+    default: k_gn_step<8><<<grid, GN_THREADS, 0, ctx->stream>>>(c, a); break;
+    }
+    KCHECK();
+    if (e1) CK(cudaEventRecord(e1, ctx->stream));
+    return DVO_OK;
+}
+
+extern "C" int dvo_gn_timing(dvo_ctx* ctx, int enable, float* total_ms, int* launches)
+{
+    if (enable) {
+        ctx->gn_timing = true;
+        ctx->gn_ev_used = 0;
+        return DVO_OK;
+    }
+    ctx->gn_timing = false;
+    CK(cudaStreamSynchronize(ctx->stream));
+    float tot = 0;
+    for (size_t k = 0; k + 1 < ctx->gn_ev_used; k += 2) {
+        float ms = 0;
+        CK(cudaEventElapsedTime(&ms, ctx->gn_ev[k], ctx->gn_ev[k + 1]));
+        tot += ms;
+    }
+    if (total_ms) *total_ms = tot;
+    if (launches) *launches = (int)(ctx->gn_ev_used / 2);
+    ctx->gn_ev_used = 0;
+    return DVO_OK;
+}
+
+extern "C" int dvo_gn_step(dvo_ctx* ctx, int obj_slot, int ref_slot, int level, const float* xi, float* upd, float* residual,
+                           int* valid, uint8_t* mask)
+{
+    int rc = check_slot(ctx, obj_slot);
+    if (rc) return rc;
+    rc = check_slot(ctx, ref_slot);
+    if (rc) return rc;
+    const Consts& c = ctx->c;
+    ARG(level >= 0 && level < c.L && xi, "bad argument");
+    const LevelGeom& g = c.lv[level];
+    CK(cudaMemcpyAsync(ctx->d_small, xi, sizeof(float) * 6 * (size_t)c.S, cudaMemcpyHostToDevice, ctx->stream));
+    k_track_init<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_ts, ctx->d_slots, obj_slot, ref_slot, nullptr, 1, level, ctx->d_small,
+                                                        0.0, 0.0f);
+    KCHECK();
+    rc = launch_gn(ctx, mask ? ctx->d_mask : nullptr);
+    if (rc) return rc;
+    dvo_iter_log* hl = (dvo_iter_log*)ctx->h_pinned;
+    CK(cudaMemcpy2DAsync(hl, sizeof(dvo_iter_log), ctx->d_log, sizeof(dvo_iter_log) * ctx->log_cap, sizeof(dvo_iter_log), c.S,
+                         cudaMemcpyDeviceToHost, ctx->stream));
+    if (mask) CK(cudaMemcpyAsync(mask, ctx->d_mask, (size_t)c.S * g.n, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (int s = 0; s < c.S; s++) {
+        if (upd) memcpy(upd + 6 * s, hl[s].update, sizeof(float) * 6);
+        if (residual) residual[s] = hl[s].residual;
+        if (valid) valid[s] = hl[s].valid_pixels;
+    }
+    return DVO_OK;
+}
+
+static int enqueue_track(dvo_ctx* ctx, int obj_slot, int ref_slot, bool use_vo, double stop_update, float stop_residual)
+{
+    const Consts& c = ctx->c;
+    if (stop_update < 0) stop_update = (double)ctx->P.min_update; // cv::norm(...) < MINIMUM_UPDATE: float promoted
+    if (stop_residual < 0) stop_residual = ctx->P.min_residual;
+    k_track_init<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_ts, ctx->d_slots, obj_slot, ref_slot, use_vo ? ctx->d_vo : nullptr, 0, 0,
+                                                        nullptr, stop_update, stop_residual);
+    KCHECK();
+    const int n = c.L * c.max_iter;
+    for (int k = 0; k < n; k++) {
+        int rc = launch_gn(ctx, nullptr);
+        if (rc) return rc;
+    }
+    return DVO_OK;
+}
+
+extern "C" int dvo_track(dvo_ctx* ctx, int obj_slot, int ref_slot, float* xi_out, dvo_iter_log* log, int log_cap, int* n_iters,
+                         double stop_update, float stop_residual)
+{
+    int rc = check_slot(ctx, obj_slot);
+    if (rc) return rc;
+    rc = check_slot(ctx, ref_slot);
+    if (rc) return rc;
+    const Consts& c = ctx->c;
+    rc = enqueue_track(ctx, obj_slot, ref_slot, false, stop_update, stop_residual);
+    if (rc) return rc;
+    TrackState* hts = (TrackState*)((char*)ctx->h_pinned + sizeof(dvo_iter_log) * (size_t)c.S * ctx->log_cap);
+    CK(cudaMemcpyAsync(hts, ctx->d_ts, sizeof(TrackState) * (size_t)c.S, cudaMemcpyDeviceToHost, ctx->stream));
+    dvo_iter_log* hl = (dvo_iter_log*)ctx->h_pinned;
+    if (log) CK(cudaMemcpyAsync(hl, ctx->d_log, sizeof(dvo_iter_log) * (size_t)c.S * ctx->log_cap, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (int s = 0; s < c.S; s++) {
+        if (xi_out) memcpy(xi_out + 6 * s, hts[s].xi, sizeof(float) * 6);
+        if (n_iters) n_iters[s] = hts[s].n_total;
+        if (log)
+            for (int k = 0; k < hts[s].n_total && k < log_cap && k < ctx->log_cap; k++) log[(size_t)s * log_cap + k] = hl[(size_t)s * ctx->log_cap + k];
+    }
+    return DVO_OK;
+}
+
+// ---- mapping --------------------------------------------------------------------------------
+__global__ void k_map_config(Consts c, MapState* mst, int ref_slot, int obj_slot, int new_slot, int n_hist, int do_p, int do_u, int do_r,
+                             int reg_slot)
+{
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= c.S) return;
+    MapState* m = mst + s;
+    m->ref_slot = ref_slot; m->obj_slot = obj_slot; m->new_slot = new_slot; m->n_hist = n_hist;
+    m->do_propagate = do_p; m->do_update = do_u; m->do_regularize = do_r; m->reg_slot = reg_slot;
+}
+__global__ void k_hist_fill(Consts c, int* hist, const int* list, int n)
+{
+    const int s = blockIdx.x;
+    for (int k = threadIdx.x; k < n; k += blockDim.x) hist[(size_t)s * c.max_kf + k] = list[k];
+}
+
+static int enqueue_propagate(dvo_ctx* ctx)
+{
+    const Consts& c = ctx->c;
+    const int ntop = c.lv[c.L - 1].n;
+    dim3 grid(cdiv(ntop, 256), c.S);
+    CK(cudaMemsetAsync(ctx->d_winner, 0xFF, sizeof(int) * (size_t)c.S * ntop, ctx->stream));
+    k_propagate_scatter<<<grid, 256, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ms, ctx->d_winner);
+    KCHECK();
+    k_propagate_gather<<<grid, 256, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ms, ctx->d_winner);
+    KCHECK();
+    return DVO_OK;
+}
+static int enqueue_update(dvo_ctx* ctx)
+{
+    const Consts& c = ctx->c;
+    const int ntop = c.lv[c.L - 1].n;
+    dim3 tgrid(cdiv(c.max_kf, 64), c.S);
+    k_pose_tables<<<tgrid, 64, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ms, ctx->d_hist, ctx->d_tab);
+    KCHECK();
+    dim3 grid(cdiv(ntop, 256), c.S);
+    k_map_update<<<grid, 256, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ms, ctx->d_hist, ctx->d_tab, ctx->d_flags, ctx->d_blockcnt, ctx->nblk_top);
+    KCHECK();
+    k_map_update_apply<<<grid, 256, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ms, ctx->d_flags, ctx->d_blockcnt, ctx->nblk_top, ctx->d_rng);
+    KCHECK();
+    return DVO_OK;
+}
+static int enqueue_regularize(dvo_ctx* ctx)
+{
+    const Consts& c = ctx->c;
+    const int ntop = c.lv[c.L - 1].n;
+    dim3 grid(cdiv(ntop, 256), c.S);
+    k_regularize<<<grid, 256, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ms, ctx->d_tmp);
+    KCHECK();
+    dim3 grid3(cdiv(ntop, 256), c.S, c.L);
+    k_ds_rebuild<<<grid3, 256, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ms, ctx->d_tmp);
+    KCHECK();
+    return DVO_OK;
+}
+
+static int map_error(dvo_ctx* ctx)
+{   // first error flagged by any stream
+    const Consts& c = ctx->c;
+    MapState* hm = (MapState*)ctx->h_pinned;
+    if (sizeof(MapState) * (size_t)c.S > ctx->h_pinned_bytes) return DVO_OK;
+    CK(cudaMemcpyAsync(hm, ctx->d_ms, sizeof(MapState) * (size_t)c.S, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (int s = 0; s < c.S; s++)
+        if (hm[s].err) {
+            ctx->err = hm[s].err == DVO_ERR_HISTORY ? "age >= history size (FrameHistory::operator[] would throw)" : "mt19937 replay table exhausted";
+            return hm[s].err;
+        }
+    return DVO_OK;
+}
+
+extern "C" int dvo_map_propagate(dvo_ctx* ctx, int ref_slot, int new_slot, const float* rel_xi)
+{
+    int rc = check_slot(ctx, ref_slot);
+    if (rc) return rc;
+    rc = check_slot(ctx, new_slot);
+    if (rc) return rc;
+    ARG(rel_xi && ref_slot != new_slot, "bad argument");
+    const Consts& c = ctx->c;
+    CK(cudaMemcpyAsync(ctx->d_small, rel_xi, sizeof(float) * 6 * (size_t)c.S, cudaMemcpyHostToDevice, ctx->stream));
+    k_map_config<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_ms, ref_slot, new_slot, new_slot, 0, 1, 0, 0, new_slot);
+    KCHECK();
+    k_map_prepare<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_ms, ctx->d_small);
+    KCHECK();
+    rc = enqueue_propagate(ctx);
+    if (rc) return rc;
+    rc = recull_ds(ctx, new_slot);
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(ctx->stream));
+    return DVO_OK;
+}
+
+extern "C" int dvo_map_update(dvo_ctx* ctx, int obj_slot, int ref_slot, const int* history_slots, int n_hist, int* valid_updates,
+                              uint8_t* mask)
+{
+    int rc = check_slot(ctx, obj_slot);
+    if (rc) return rc;
+    rc = check_slot(ctx, ref_slot);
+    if (rc) return rc;
+    const Consts& c = ctx->c;
+    ARG(history_slots && n_hist >= 1 && n_hist <= c.max_kf, "bad history");
+    for (int k = 0; k < n_hist; k++) {
+        rc = check_slot(ctx, history_slots[k]);
+        if (rc) return rc;
+    }
+    // hist is stored in push order (oldest first); history_slots is indexed by age (newest first)
+    std::vector<int> order(n_hist);
+    for (int a = 0; a < n_hist; a++) order[n_hist - 1 - a] = history_slots[a];
+    CK(cudaMemcpyAsync(ctx->d_ismall, order.data(), sizeof(int) * n_hist, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    k_hist_fill<<<c.S, 64, 0, ctx->stream>>>(c, ctx->d_hist, ctx->d_ismall, n_hist);
+    KCHECK();
+    k_map_config<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_ms, ref_slot, obj_slot, obj_slot, n_hist, 0, 1, 0, ref_slot);
+    KCHECK();
+    k_map_prepare<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_ms, ctx->slots[obj_slot].dev.rel_xi);
+    KCHECK();
+    rc = enqueue_update(ctx);
+    if (rc) return rc;
+    rc = recull_ds(ctx, ref_slot); // ref->updateDepthSigma, mapper.cpp:135
+    if (rc) return rc;
+    const int ntop = c.lv[c.L - 1].n;
+    if (mask) CK(cudaMemcpyAsync(mask, ctx->d_flags, (size_t)c.S * ntop, cudaMemcpyDeviceToHost, ctx->stream));
+    rc = map_error(ctx);
+    if (rc) return rc;
+    if (valid_updates) {
+        MapState* hm = (MapState*)ctx->h_pinned;
+        for (int s = 0; s < c.S; s++) valid_updates[s] = hm[s].valid_update;
+    }
+    return DVO_OK;
+}
+
+extern "C" int dvo_map_regularize(dvo_ctx* ctx, int slot)
+{
+    int rc = check_slot(ctx, slot);
+    if (rc) return rc;
+    const Consts& c = ctx->c;
+    k_map_config<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_ms, slot, slot, slot, 0, 0, 0, 1, slot);
+    KCHECK();
+    rc = enqueue_regularize(ctx);
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(ctx->stream));
+    return DVO_OK;
+}
+
+extern "C" int dvo_rng_position(dvo_ctx* ctx, uint64_t* pos)
+{
+    const Consts& c = ctx->c;
+    MapState* hm = (MapState*)ctx->h_pinned;
+    CK(cudaMemcpyAsync(hm, ctx->d_ms, sizeof(MapState) * (size_t)c.S, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (int s = 0; s < c.S; s++) pos[s] = hm[s].rng_pos;
+    return DVO_OK;
+}
+
+// ---- mask compaction ------------------------------------------------------------------------
+extern "C" int dvo_mask_compact(dvo_ctx* ctx, const uint8_t* mask, int n, int32_t* idx, int* count)
+{
+    ARG(mask && idx && count && n > 0, "bad argument");
+    uint8_t* d_m = nullptr;
+    int32_t* d_i = nullptr;
+    unsigned int* d_c = nullptr;
+    const int nb = cdiv(n, 256);
+    CK(cudaMalloc(&d_m, n));
+    CK(cudaMalloc(&d_i, sizeof(int32_t) * (size_t)n));
+    CK(cudaMalloc(&d_c, sizeof(unsigned) * (size_t)(nb + 1)));
+    CK(cudaMemcpyAsync(d_m, mask, n, cudaMemcpyHostToDevice, ctx->stream));
+    k_compact_count<<<nb, 256, 0, ctx->stream>>>(d_m, n, d_c);
+    KCHECK();
+    k_compact_scatter<<<nb, 256, 0, ctx->stream>>>(d_m, n, d_c, d_i, d_c + nb);
+    KCHECK();
+    unsigned int total = 0;
+    CK(cudaMemcpyAsync(&total, d_c + nb, sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (total) CK(cudaMemcpy(idx, d_i, sizeof(int32_t) * (size_t)total, cudaMemcpyDeviceToHost));
+    *count = (int)total;
+    cudaFree(d_m); cudaFree(d_i); cudaFree(d_c);
+    return DVO_OK;
+}
+
+// ---- full VO --------------------------------------------------------------------------------
+__global__ void k_vo_reset(Consts c, VoState* vo, MapState* mst)
+{
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= c.S) return;
+    vo[s].kf_slot = -1; vo[s].kf_frame_id = -1; vo[s].n_kf = 0; vo[s].need_new = 0; vo[s].was_keyframe = 0; vo[s].n_iters = 0;
+    mst[s].rng_pos = 0; mst[s].err = 0; mst[s].valid_update = 0; mst[s].ticket = 0;
+}
+
+extern "C" int dvo_vo_reset(dvo_ctx* ctx)
+{
+    const Consts& c = ctx->c;
+    for (auto& s : ctx->slots) s.in_use = false;
+    ctx->vo_frame_id = -1;
+    ctx->vo_last_slot = -1;
+    k_vo_reset<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_vo, ctx->d_ms);
+    KCHECK();
+    return DVO_OK;
+}
+
+extern "C" int dvo_vo_push_dev(dvo_ctx* ctx, const float* gray_dev, const float* init_depth, const float* init_sigma, float* T_out)
+{
+    const Consts& c = ctx->c;
+    int cur = -1;
+    int rc = dvo_frame_create_dev(ctx, &cur, gray_dev); // make_shared<Frame>(gray, K, 3, 2), system.hpp:47
+    if (rc) return rc;
+    const int frame_id = ++ctx->vo_frame_id; // Frame::latest_id, frame.cpp:5
+    if (init_depth || init_sigma) {
+        rc = dvo_frame_set_depth(ctx, cur, init_depth, init_sigma, nullptr, 0);
+        if (rc) return rc;
+    }
+    // Tracking (system.hpp:57): against each stream's current keyframe; no-op on the first frame
+    rc = enqueue_track(ctx, cur, cur, true, -1.0, -1.0f);
+    if (rc) return rc;
+    k_vo_decide<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ts, ctx->d_vo, ctx->d_ms, cur, frame_id);
+    KCHECK();
+    // Mapping (system.hpp:67, mapper.cpp:16-33): per stream either propagate or update
+    rc = enqueue_propagate(ctx);
+    if (rc) return rc;
+    rc = enqueue_update(ctx);
+    if (rc) return rc;
+    k_vo_commit<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_vo, ctx->d_ms, ctx->d_hist, cur, frame_id);
+    KCHECK();
+    rc = enqueue_regularize(ctx);
+    if (rc) return rc;
+    ctx->vo_last_slot = cur;
+    if (T_out) {
+        k_pose_out<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->slots[cur].dev, ctx->d_small);
+        KCHECK();
+        CK(cudaMemcpyAsync(T_out, ctx->d_small, sizeof(float) * 16 * (size_t)c.S, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+    }
+    return DVO_OK;
+}
+
+extern "C" int dvo_vo_push(dvo_ctx* ctx, const float* gray, const float* init_depth, const float* init_sigma, float* T_out)
+{
+    ARG(gray, "null gray");
+    const Consts& c = ctx->c;
+    CK(cudaMemcpyAsync(ctx->d_stage_in, gray, sizeof(float) * (size_t)c.S * c.in_w * c.in_h, cudaMemcpyHostToDevice, ctx->stream));
+    return dvo_vo_push_dev(ctx, ctx->d_stage_in, init_depth, init_sigma, T_out);
+}
+
+extern "C" int dvo_vo_state(dvo_ctx* ctx, float* xi, float* rel_xi, int* was_keyframe, int* n_keyframes, int* valid_updates, int* n_iters)
+{
+    const Consts& c = ctx->c;
+    ARG(ctx->vo_last_slot >= 0, "no frame pushed");
+    std::vector<VoState> hv(c.S);
+    std::vector<MapState> hm(c.S);
+    CK(cudaMemcpyAsync(hv.data(), ctx->d_vo, sizeof(VoState) * (size_t)c.S, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(hm.data(), ctx->d_ms, sizeof(MapState) * (size_t)c.S, cudaMemcpyDeviceToHost, ctx->stream));
+    const SlotDev& sd = ctx->slots[ctx->vo_last_slot].dev;
+    if (xi) CK(cudaMemcpyAsync(xi, sd.xi, sizeof(float) * 6 * (size_t)c.S, cudaMemcpyDeviceToHost, ctx->stream));
+    if (rel_xi) CK(cudaMemcpyAsync(rel_xi, sd.rel_xi, sizeof(float) * 6 * (size_t)c.S, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (int s = 0; s < c.S; s++) {
+        if (was_keyframe) was_keyframe[s] = hv[s].was_keyframe;
+        if (n_keyframes) n_keyframes[s] = hv[s].n_kf;
+        if (valid_updates) valid_updates[s] = hm[s].valid_update;
+        if (n_iters) n_iters[s] = hv[s].n_iters;
+    }
+    return DVO_OK;
+}
+
+extern "C" int dvo_vo_ref_slot(dvo_ctx* ctx, int stream, int* slot)
+{
+    const Consts& c = ctx->c;
+    ARG(stream >= 0 && stream < c.S && slot, "bad stream");
+    VoState v;
+    CK(cudaMemcpyAsync(&v, ctx->d_vo + stream, sizeof(VoState), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    *slot = v.kf_slot;
+    return DVO_OK;
+}
+extern "C" int dvo_vo_last_slot(dvo_ctx* ctx, int* slot)
+{
+    ARG(slot, "null");
+    *slot = ctx->vo_last_slot;
+    return DVO_OK;
+}
+extern "C" int dvo_vo_error(dvo_ctx* ctx) { return map_error(ctx); }
+
+// ---- measurement ----------------------------------------------------------------------------
+extern "C" int dvo_timer_start(dvo_ctx* ctx)
+{
+    CK(cudaEventRecord(ctx->ev0, ctx->stream));
+    return DVO_OK;
+}
+extern "C" int dvo_timer_stop(dvo_ctx* ctx, float* ms)
+{
+    CK(cudaEventRecord(ctx->ev1, ctx->stream));
+    CK(cudaEventSynchronize(ctx->ev1));
+    CK(cudaEventElapsedTime(ms, ctx->ev0, ctx->ev1));
+    return DVO_OK;
+}

@@ -1,0 +1,87 @@
+// dvo_internal.cuh — device-visible data model shared by the kernels and the C-ABI layer.
+#pragma once
+#include "../../include/dvo_cuda.h"
+#include "dvo_device.cuh"
+
+namespace dvo {
+
+constexpr int MAXL = DVO_MAX_LEVELS;
+constexpr int GN_THREADS = 256;
+constexpr int NACC = 29; // 21 J^T J + 6 J^T (w r) + sum r^2 + valid count
+
+// Geometry + constants, passed to kernels by value (__grid_constant__).
+struct Consts {
+    int S, L;
+    int in_w, in_h, culls;
+    LevelGeom lv[MAXL];
+    int max_kf;
+    // tracking
+    int max_iter;
+    int roi_level, roi_x0, roi_x1, roi_y0, roi_y1;
+    float min_depth_f;  // smallest float >= (double)min_depth: (double)d < min_depth <=> d < min_depth_f
+    float sigma_lo, sigma_hi;
+    float step_default, step_level1, step_level2;
+    // mapping
+    int map_x0, map_x1, map_y0, map_y1;
+    float min_movement;
+    int max_forward;
+    float acc_d_lo, acc_d_hi, acc_s_hi;
+    unsigned int rng_table;
+};
+
+// One frame slot as the device sees it.  All images are stream-major: base + s * n_level.
+struct SlotDev {
+    float* gray[MAXL];   // plain gray pyramid            [S][n_l]
+    float4* tex[MAXL];   // {gray, gradX, gradY, 0}        [S][n_l]
+    float2* ds[MAXL];    // {depth, sigma}                 [S][n_l]
+    float* age;          // finest level                   [S][n_top]
+    float* xi;           // Frame::m_xi                    [S][6]
+    float* rel_xi;       // Frame::m_relative_xi           [S][6]
+};
+
+// Per-stream Gauss-Newton state machine (Tracker::track, src/track/tracker.cpp:22-85).
+struct TrackState {
+    int level, iter, done, n_total;
+    int mode;            // 0: full coarse-to-fine track; 1: single step (Track::optimize)
+    unsigned int ticket; // blocks finished in the current launch
+    float xi[6];
+    float Tn[12];        // exp(-xi), rows of [R|t]
+    double stop_update;
+    float stop_residual;
+    int pad;
+    const float* obj_gray[MAXL]; // pre-offset by stream
+    const float4* ref_tex[MAXL];
+    const float2* ref_ds[MAXL];
+};
+
+// Per-stream mapping work descriptor (filled by the host for the granular API, by k_vo_decide
+// for the device-resident VO loop).
+struct MapState {
+    int ref_slot, obj_slot, new_slot;
+    int n_hist;
+    int do_propagate, do_update, do_regularize;
+    int reg_slot;
+    float Trel[12];   // exp(rel_xi)
+    float rel_z;      // rel_xi[2]
+    int valid_update;
+    unsigned int n_reject;      // rejects of this update
+    unsigned int ticket;
+    unsigned long long rng_pos; // draws consumed so far
+    int err;
+    int pad;
+};
+
+// Per-stream VO state (System::VisualOdometry + FrameHistory).
+struct VoState {
+    int kf_slot, kf_frame_id, n_kf;
+    int need_new, was_keyframe;
+    int n_iters;
+};
+
+struct PoseTab { // per (stream, age): exp(-r_xi) and -r_xi[0:3] (src/map/mapper.cpp:107, implement.cpp:56-58,193)
+    float T[12];
+    float t[3];
+    float pad;
+};
+
+} // namespace dvo

@@ -1,0 +1,324 @@
+"""dvo_b200 — thin ctypes loader for libdvo_cuda.so (the C ABI declared in include/dvo_cuda.h).
+
+This module is plumbing for tests and bench.py only: the product is the CUDA library and the C++
+host classes in include/dvo/.  There is no CPU fallback: if the library is missing or no CUDA
+device is present, construction fails loudly.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+PKG_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB_PATH = os.path.join(PKG_ROOT, "libdvo_cuda.so")
+F32P = C.POINTER(C.c_float)
+I32P = C.POINTER(C.c_int)
+U8P = C.POINTER(C.c_uint8)
+
+IMG = {"gray": 0, "depth": 1, "sigma": 2, "gradx": 3, "grady": 4, "age": 5}
+
+
+class DvoParams(C.Structure):
+    _fields_ = [
+        ("n_streams", C.c_int), ("width", C.c_int), ("height", C.c_int), ("levels", C.c_int), ("culls", C.c_int),
+        ("K", C.c_float * 9), ("max_frames", C.c_int), ("max_keyframes", C.c_int),
+        ("min_residual", C.c_float), ("min_update", C.c_float), ("max_iterations", C.c_int),
+        ("roi_level", C.c_int), ("roi_x0", C.c_int), ("roi_x1", C.c_int), ("roi_y0", C.c_int), ("roi_y1", C.c_int),
+        ("min_depth", C.c_double), ("sigma_lo", C.c_float), ("sigma_hi", C.c_float),
+        ("step_default", C.c_float), ("step_level1", C.c_float), ("step_level2", C.c_float),
+        ("map_roi_x0", C.c_int), ("map_roi_x1", C.c_int), ("map_roi_y0", C.c_int), ("map_roi_y1", C.c_int),
+        ("min_movement", C.c_float), ("max_forward", C.c_int),
+        ("accept_depth_lo", C.c_float), ("accept_depth_hi", C.c_float), ("accept_sigma_hi", C.c_float),
+        ("rng_table", C.c_int),
+    ]
+
+
+class DvoIterLog(C.Structure):
+    _fields_ = [("level", C.c_int), ("iteration", C.c_int), ("valid_pixels", C.c_int), ("residual", C.c_float),
+                ("update", C.c_float * 6), ("xi_after", C.c_float * 6)]
+
+
+EXPORTS = [
+    "dvo_params_default", "dvo_create", "dvo_destroy", "dvo_last_error", "dvo_sync", "dvo_level_size", "dvo_level_K",
+    "dvo_host_alloc", "dvo_host_free", "dvo_frame_create", "dvo_frame_create_dev", "dvo_frame_release",
+    "dvo_frame_set_depth", "dvo_frame_download", "dvo_frame_set_xi", "dvo_frame_get_xi", "dvo_warp_image",
+    "dvo_gn_step", "dvo_track", "dvo_map_propagate", "dvo_map_update", "dvo_map_regularize", "dvo_rng_position",
+    "dvo_mask_compact", "dvo_vo_reset", "dvo_vo_push", "dvo_vo_push_dev", "dvo_vo_state", "dvo_vo_ref_slot",
+    "dvo_vo_last_slot", "dvo_vo_error", "dvo_timer_start", "dvo_timer_stop", "dvo_launch_count", "dvo_gn_timing",
+]
+
+
+def load_library(path=None):
+    path = path or LIB_PATH
+    if not os.path.exists(path):
+        raise RuntimeError("libdvo_cuda.so not built (%s): run `python -c 'import __graft_entry__ as g; g.build()'`; "
+                           "there is no CPU fallback" % path)
+    lib = C.CDLL(path)
+    lib.dvo_last_error.restype = C.c_char_p
+    lib.dvo_last_error.argtypes = [C.c_void_p]
+    lib.dvo_create.argtypes = [C.POINTER(C.c_void_p), C.POINTER(DvoParams)]
+    lib.dvo_destroy.argtypes = [C.c_void_p]
+    lib.dvo_sync.argtypes = [C.c_void_p]
+    lib.dvo_level_size.argtypes = [C.c_void_p, C.c_int, I32P, I32P]
+    lib.dvo_level_K.argtypes = [C.c_void_p, C.c_int, F32P]
+    lib.dvo_host_alloc.restype = C.c_void_p
+    lib.dvo_host_alloc.argtypes = [C.c_size_t]
+    lib.dvo_host_free.argtypes = [C.c_void_p]
+    lib.dvo_frame_create.argtypes = [C.c_void_p, I32P, C.c_void_p]
+    lib.dvo_frame_create_dev.argtypes = [C.c_void_p, I32P, C.c_void_p]
+    lib.dvo_frame_release.argtypes = [C.c_void_p, C.c_int]
+    lib.dvo_frame_set_depth.argtypes = [C.c_void_p, C.c_int, F32P, F32P, F32P, C.c_int]
+    lib.dvo_frame_download.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, F32P]
+    lib.dvo_frame_set_xi.argtypes = [C.c_void_p, C.c_int, F32P, F32P]
+    lib.dvo_frame_get_xi.argtypes = [C.c_void_p, C.c_int, F32P, F32P]
+    lib.dvo_warp_image.argtypes = [C.c_void_p, C.c_int, C.c_int, F32P, F32P]
+    lib.dvo_gn_step.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, F32P, F32P, F32P, I32P, U8P]
+    lib.dvo_track.argtypes = [C.c_void_p, C.c_int, C.c_int, F32P, C.POINTER(DvoIterLog), C.c_int, I32P, C.c_double,
+                              C.c_float]
+    lib.dvo_map_propagate.argtypes = [C.c_void_p, C.c_int, C.c_int, F32P]
+    lib.dvo_map_update.argtypes = [C.c_void_p, C.c_int, C.c_int, I32P, C.c_int, I32P, U8P]
+    lib.dvo_map_regularize.argtypes = [C.c_void_p, C.c_int]
+    lib.dvo_rng_position.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
+    lib.dvo_mask_compact.argtypes = [C.c_void_p, U8P, C.c_int, I32P, I32P]
+    lib.dvo_vo_reset.argtypes = [C.c_void_p]
+    lib.dvo_vo_push.argtypes = [C.c_void_p, C.c_void_p, F32P, F32P, F32P]
+    lib.dvo_vo_push_dev.argtypes = [C.c_void_p, C.c_void_p, F32P, F32P, F32P]
+    lib.dvo_vo_state.argtypes = [C.c_void_p, F32P, F32P, I32P, I32P, I32P, I32P]
+    lib.dvo_vo_ref_slot.argtypes = [C.c_void_p, C.c_int, I32P]
+    lib.dvo_vo_last_slot.argtypes = [C.c_void_p, I32P]
+    lib.dvo_vo_error.argtypes = [C.c_void_p]
+    lib.dvo_timer_start.argtypes = [C.c_void_p]
+    lib.dvo_timer_stop.argtypes = [C.c_void_p, F32P]
+    lib.dvo_launch_count.restype = C.c_uint64
+    lib.dvo_launch_count.argtypes = [C.c_void_p]
+    lib.dvo_gn_timing.argtypes = [C.c_void_p, C.c_int, F32P, I32P]
+    return lib
+
+
+def default_params(lib=None, **kw):
+    lib = lib or load_library()
+    p = DvoParams()
+    lib.dvo_params_default(C.byref(p))
+    for k, v in kw.items():
+        if k == "K":
+            v = np.asarray(v, np.float32).reshape(-1)
+            for i in range(9):
+                p.K[i] = float(v[i])
+        else:
+            setattr(p, k, v)
+    return p
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _p(a):
+    return a.ctypes.data_as(F32P) if a is not None else None
+
+
+class DvoError(RuntimeError):
+    pass
+
+
+class Dvo:
+    """One context = n_streams sequences in lock-step on the current CUDA device."""
+
+    def __init__(self, lib=None, **params):
+        self.lib = lib or load_library()
+        self.params = default_params(self.lib, **params)
+        self.ctx = C.c_void_p()
+        rc = self.lib.dvo_create(C.byref(self.ctx), C.byref(self.params))
+        if rc:
+            msg = self.lib.dvo_last_error(self.ctx).decode() if self.ctx else "dvo_create failed"
+            if self.ctx:
+                self.lib.dvo_destroy(self.ctx)
+                self.ctx = None
+            raise DvoError("dvo_create rc=%d: %s" % (rc, msg))
+        self.S = self.params.n_streams
+        self.L = self.params.levels
+
+    def close(self):
+        if getattr(self, "ctx", None):
+            self.lib.dvo_destroy(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        self.close()
+
+    def _ck(self, rc):
+        if rc:
+            raise DvoError("rc=%d: %s" % (rc, self.lib.dvo_last_error(self.ctx).decode()))
+
+    # ---- geometry
+    def level_size(self, level):
+        w = C.c_int(); h = C.c_int()
+        self._ck(self.lib.dvo_level_size(self.ctx, level, C.byref(w), C.byref(h)))
+        return w.value, h.value
+
+    def level_K(self, level):
+        K = np.empty(9, np.float32)
+        self._ck(self.lib.dvo_level_K(self.ctx, level, _p(K)))
+        return K.reshape(3, 3)
+
+    # ---- frames
+    def _stack(self, img, h, w):
+        a = _f32(img)
+        if a.ndim == 2:
+            a = a[None]
+        assert a.shape == (self.S, h, w), (a.shape, (self.S, h, w))
+        return np.ascontiguousarray(a)
+
+    def frame_create(self, gray):
+        g = self._stack(gray, self.params.height, self.params.width)
+        slot = C.c_int(-1)
+        self._ck(self.lib.dvo_frame_create(self.ctx, C.byref(slot), g.ctypes.data_as(C.c_void_p)))
+        self._ck(self.lib.dvo_sync(self.ctx))
+        return slot.value
+
+    def frame_release(self, slot):
+        self._ck(self.lib.dvo_frame_release(self.ctx, slot))
+
+    def frame_set_depth(self, slot, depth=None, sigma=None, age=None, full_res=False):
+        if full_res:
+            h, w = self.params.height, self.params.width
+        else:
+            w, h = self.level_size(self.L - 1)
+        arrs = [self._stack(a, h, w) if a is not None else None for a in (depth, sigma, age)]
+        self._ck(self.lib.dvo_frame_set_depth(self.ctx, slot, _p(arrs[0]), _p(arrs[1]), _p(arrs[2]), 1 if full_res else 0))
+
+    def frame_download(self, slot, level, kind):
+        w, h = self.level_size(level)
+        out = np.empty((self.S, h, w), np.float32)
+        self._ck(self.lib.dvo_frame_download(self.ctx, slot, level, IMG[kind], _p(out)))
+        return out
+
+    def frame_set_xi(self, slot, xi=None, rel_xi=None):
+        a = _f32(np.broadcast_to(np.asarray(xi, np.float32).reshape(-1, 6), (self.S, 6))) if xi is not None else None
+        b = _f32(np.broadcast_to(np.asarray(rel_xi, np.float32).reshape(-1, 6), (self.S, 6))) if rel_xi is not None else None
+        self._ck(self.lib.dvo_frame_set_xi(self.ctx, slot, _p(a), _p(b)))
+
+    def frame_get_xi(self, slot):
+        a = np.empty((self.S, 6), np.float32); b = np.empty((self.S, 6), np.float32)
+        self._ck(self.lib.dvo_frame_get_xi(self.ctx, slot, _p(a), _p(b)))
+        return a, b
+
+    # ---- tracking
+    def _xi(self, xi):
+        return _f32(np.broadcast_to(np.asarray(xi, np.float32).reshape(-1, 6), (self.S, 6)))
+
+    def warp_image(self, ref_slot, level, xi):
+        w, h = self.level_size(level)
+        out = np.empty((self.S, h, w), np.float32)
+        x = self._xi(xi)
+        self._ck(self.lib.dvo_warp_image(self.ctx, ref_slot, level, _p(x), _p(out)))
+        return out
+
+    def gn_step(self, obj_slot, ref_slot, level, xi, want_mask=True):
+        w, h = self.level_size(level)
+        x = self._xi(xi)
+        upd = np.empty((self.S, 6), np.float32); res = np.empty(self.S, np.float32); valid = np.empty(self.S, np.int32)
+        mask = np.empty((self.S, h, w), np.uint8) if want_mask else None
+        self._ck(self.lib.dvo_gn_step(self.ctx, obj_slot, ref_slot, level, _p(x), _p(upd), _p(res),
+                                      valid.ctypes.data_as(I32P), mask.ctypes.data_as(U8P) if want_mask else None))
+        return upd, res, valid, mask
+
+    def track(self, obj_slot, ref_slot, stop_update=-1.0, stop_residual=-1.0):
+        cap = self.L * self.params.max_iterations
+        xi = np.empty((self.S, 6), np.float32); n = np.empty(self.S, np.int32)
+        log = (DvoIterLog * (cap * self.S))()
+        self._ck(self.lib.dvo_track(self.ctx, obj_slot, ref_slot, _p(xi), log, cap, n.ctypes.data_as(I32P),
+                                    C.c_double(stop_update), C.c_float(stop_residual)))
+        logs = []
+        for s in range(self.S):
+            lst = []
+            for k in range(int(n[s])):
+                L = log[s * cap + k]
+                lst.append(dict(level=L.level, iteration=L.iteration, valid_pixels=L.valid_pixels, residual=L.residual,
+                                update=np.array(L.update[:], np.float32), xi_after=np.array(L.xi_after[:], np.float32)))
+            logs.append(lst)
+        return xi, logs
+
+    # ---- mapping
+    def map_propagate(self, ref_slot, new_slot, rel_xi):
+        x = self._xi(rel_xi)
+        self._ck(self.lib.dvo_map_propagate(self.ctx, ref_slot, new_slot, _p(x)))
+
+    def map_update(self, obj_slot, ref_slot, history_slots, want_mask=True):
+        w, h = self.level_size(self.L - 1)
+        hs = np.asarray(history_slots, np.int32)
+        vu = np.empty(self.S, np.int32)
+        mask = np.empty((self.S, h, w), np.uint8) if want_mask else None
+        self._ck(self.lib.dvo_map_update(self.ctx, obj_slot, ref_slot, hs.ctypes.data_as(I32P), len(hs),
+                                         vu.ctypes.data_as(I32P), mask.ctypes.data_as(U8P) if want_mask else None))
+        return vu, mask
+
+    def map_regularize(self, slot):
+        self._ck(self.lib.dvo_map_regularize(self.ctx, slot))
+
+    def rng_position(self):
+        pos = (C.c_uint64 * self.S)()
+        self._ck(self.lib.dvo_rng_position(self.ctx, pos))
+        return np.array(pos[:], np.uint64)
+
+    def mask_compact(self, mask):
+        m = np.ascontiguousarray(mask, np.uint8).reshape(-1)
+        idx = np.empty(m.size, np.int32); cnt = C.c_int(0)
+        self._ck(self.lib.dvo_mask_compact(self.ctx, m.ctypes.data_as(U8P), m.size, idx.ctypes.data_as(I32P), C.byref(cnt)))
+        return idx[:cnt.value].copy()
+
+    # ---- VO
+    def vo_reset(self):
+        self._ck(self.lib.dvo_vo_reset(self.ctx))
+
+    def vo_push(self, gray, init_depth=None, init_sigma=None, want_pose=True):
+        g = self._stack(gray, self.params.height, self.params.width)
+        w, h = self.level_size(self.L - 1)
+        d = self._stack(init_depth, h, w) if init_depth is not None else None
+        s = self._stack(init_sigma, h, w) if init_sigma is not None else None
+        T = np.empty((self.S, 4, 4), np.float32) if want_pose else None
+        self._ck(self.lib.dvo_vo_push(self.ctx, g.ctypes.data_as(C.c_void_p), _p(d), _p(s), _p(T)))
+        if not want_pose:
+            self._ck(self.lib.dvo_sync(self.ctx))  # g must outlive the async copy
+        return T
+
+    def vo_state(self):
+        xi = np.empty((self.S, 6), np.float32); rel = np.empty((self.S, 6), np.float32)
+        kf = np.empty(self.S, np.int32); nk = np.empty(self.S, np.int32); vu = np.empty(self.S, np.int32)
+        ni = np.empty(self.S, np.int32)
+        self._ck(self.lib.dvo_vo_state(self.ctx, _p(xi), _p(rel), kf.ctypes.data_as(I32P), nk.ctypes.data_as(I32P),
+                                       vu.ctypes.data_as(I32P), ni.ctypes.data_as(I32P)))
+        return dict(xi=xi, rel_xi=rel, was_keyframe=kf, n_keyframes=nk, valid_updates=vu, n_iters=ni)
+
+    def vo_ref_slot(self, stream=0):
+        s = C.c_int(-1)
+        self._ck(self.lib.dvo_vo_ref_slot(self.ctx, stream, C.byref(s)))
+        return s.value
+
+    def vo_last_slot(self):
+        s = C.c_int(-1)
+        self._ck(self.lib.dvo_vo_last_slot(self.ctx, C.byref(s)))
+        return s.value
+
+    def vo_error(self):
+        return self.lib.dvo_vo_error(self.ctx)
+
+    # ---- measurement
+    def sync(self):
+        self._ck(self.lib.dvo_sync(self.ctx))
+
+    def timer_start(self):
+        self._ck(self.lib.dvo_timer_start(self.ctx))
+
+    def timer_stop(self):
+        ms = C.c_float(0)
+        self._ck(self.lib.dvo_timer_stop(self.ctx, C.byref(ms)))
+        return ms.value
+
+    def launch_count(self):
+        return int(self.lib.dvo_launch_count(self.ctx))
+
+    def gn_timing(self, enable):
+        ms = C.c_float(0); n = C.c_int(0)
+        self._ck(self.lib.dvo_gn_timing(self.ctx, 1 if enable else 0, C.byref(ms), C.byref(n)))
+        return ms.value, n.value

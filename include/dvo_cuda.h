@@ -1,0 +1,175 @@
+/*
+ * dvo_cuda.h — C ABI of libdvo_cuda.so, the B200 (sm_100a) implementation of the per-pixel hot path
+ * of KYabuuchi/direct-visual-odometry (tracking + mapping).  Plain pointers and sizes only.
+ *
+ * The reference has no FFI/plugin registry: its boundary is the C++ class API in include/
+ * (SURVEY.md §8-b).  Each entry point below names the reference interface it replaces
+ * (file:line relative to the reference root).  The C++ classes in include/dvo/ keep the
+ * reference's names/signatures and forward to these functions.
+ *
+ * Conventions
+ *  - A context processes `n_streams` independent sequences in lock-step: every image argument is
+ *    an array of n_streams images, stream-major ([stream][row][col], float32, row-major).  With
+ *    n_streams == 1 the calls are exactly the reference's single-sequence operations.
+ *  - Host pointers unless the name ends in _dev.  The library owns device memory and one CUDA
+ *    stream per context; calls are asynchronous until an output pointer must be filled.
+ *  - A context is bound to the CUDA device current at dvo_create and is not thread-safe.
+ *  - Returns 0 on success, a negative dvo_status otherwise; never throws across the ABI.
+ *  - There is NO CPU fallback: without a CUDA device dvo_create fails with DVO_ERR_CUDA.
+ */
+#ifndef DVO_CUDA_H
+#define DVO_CUDA_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DVO_MAX_LEVELS 8
+#define DVO_INVALID (-2.0f) /* include/math/util.hpp:7 */
+
+typedef enum dvo_status {
+    DVO_OK = 0,
+    DVO_ERR_CUDA = -1,     /* CUDA runtime error (see dvo_last_error) */
+    DVO_ERR_ARG = -2,      /* bad argument */
+    DVO_ERR_SLOT = -3,     /* bad / exhausted frame slot */
+    DVO_ERR_HISTORY = -4,  /* age >= history size: std::vector::at would throw (frame.hpp:176) */
+    DVO_ERR_RNG = -5,      /* mt19937 replay table exhausted */
+    DVO_ERR_STATE = -6     /* call sequence error */
+} dvo_status;
+
+/* Geometry + the reference's compile-time constants (defaults = the reference's literals). */
+typedef struct dvo_params {
+    /* geometry: System::Frame ctor (include/system/frame.hpp:91-117) */
+    int n_streams;      /* independent sequences per call (>=1) */
+    int width, height;  /* input image size */
+    int levels, culls;  /* Frame(gray, K, levels, culls): 3,2 in odometrize (system.hpp:47); 4,1 in test/track.cpp:24 */
+    float K[9];         /* input intrinsics, row-major 3x3 */
+    int max_frames;     /* frame-slot capacity */
+    int max_keyframes;  /* per-stream history capacity (FrameHistory is never pruned, frame.hpp:179-185) */
+    /* Tracker::track constants (src/track/tracker.cpp:16-19); the 200 ms budget is never reached */
+    float min_residual; /* 5e-3 */
+    float min_update;   /* 5e-4 */
+    int max_iterations; /* 15 */
+    /* Track::optimize (src/track/optimize.cpp:22-39,83) */
+    int roi_level;                      /* 2 */
+    int roi_x0, roi_x1, roi_y0, roi_y1; /* 20,140,20,100 inclusive */
+    double min_depth;                   /* 0.20 (double literal) */
+    float sigma_lo, sigma_hi;           /* 0.01, 0.5 */
+    float step_default, step_level1, step_level2; /* 2.0, 1.5, 1.0 */
+    /* Mapper (src/map/mapper.cpp:12-13,90,122) */
+    int map_roi_x0, map_roi_x1, map_roi_y0, map_roi_y1; /* 16,144,12,108 inclusive */
+    float min_movement; /* 0.02 */
+    int max_forward;    /* 6 */
+    float accept_depth_lo, accept_depth_hi, accept_sigma_hi; /* 0.2, 6.0, 0.5 */
+    /* mt19937 replay table length (draws) for Gaussian::update's reset (src/math/gaussian.cpp:8-9,22) */
+    int rng_table;      /* default 1<<22 */
+} dvo_params;
+
+typedef struct dvo_ctx dvo_ctx;
+
+/* One Gauss-Newton iteration record (what Tracker::track prints, src/track/tracker.cpp:56-61). */
+typedef struct dvo_iter_log {
+    int level, iteration, valid_pixels;
+    float residual;
+    float update[6];
+    float xi_after[6];
+} dvo_iter_log;
+
+typedef enum dvo_image_kind {
+    DVO_IMG_GRAY = 0, DVO_IMG_DEPTH = 1, DVO_IMG_SIGMA = 2, DVO_IMG_GRADX = 3, DVO_IMG_GRADY = 4,
+    DVO_IMG_AGE = 5 /* finest level only */
+} dvo_image_kind;
+
+/* ---- context ------------------------------------------------------------------------------ */
+void dvo_params_default(dvo_params* p); /* geometry 640x480, levels 3, culls 2, n_streams 1 */
+int dvo_create(dvo_ctx** out, const dvo_params* p);
+void dvo_destroy(dvo_ctx* ctx);
+const char* dvo_last_error(const dvo_ctx* ctx);
+int dvo_sync(dvo_ctx* ctx);
+int dvo_level_size(const dvo_ctx* ctx, int level, int* w, int* h); /* Scene::cols/rows, frame.hpp:41-42 */
+int dvo_level_K(const dvo_ctx* ctx, int level, float K[9]);        /* Convert::cullIntrinsic, convert.cpp:22-29 */
+/* pinned host memory for zero-staging uploads / downloads */
+void* dvo_host_alloc(size_t bytes);
+void dvo_host_free(void* p);
+
+/* ---- frames: System::Frame (include/system/frame.hpp:72-144, src/system/frame.cpp) ---------- */
+/* Frame(gray, K, levels, culls): decimation pyramid (Convert::cullImage convert.cpp:7-20) +
+ * gradients (Convert::gradiate convert.cpp:41-75) built on device.  gray: [n_streams][height][width]. */
+int dvo_frame_create(dvo_ctx* ctx, int* slot, const float* gray);
+int dvo_frame_create_dev(dvo_ctx* ctx, int* slot, const float* gray_dev);
+int dvo_frame_release(dvo_ctx* ctx, int slot);
+/* full_res != 0: arrays are input-sized and culled like the 6-arg Frame ctor (frame.hpp:91-106);
+ * full_res == 0: arrays are finest-level sized (Frame::updateDepthSigmaAge, frame.cpp:47-54).
+ * Any of depth/sigma/age may be NULL (left unchanged).  The coarser levels are re-culled. */
+int dvo_frame_set_depth(dvo_ctx* ctx, int slot, const float* depth, const float* sigma, const float* age, int full_res);
+int dvo_frame_download(dvo_ctx* ctx, int slot, int level, int kind, float* out);
+int dvo_frame_set_xi(dvo_ctx* ctx, int slot, const float* xi /*[n_streams][6]*/, const float* rel_xi /*nullable*/);
+int dvo_frame_get_xi(dvo_ctx* ctx, int slot, float* xi, float* rel_xi /*nullable*/);
+
+/* ---- tracking ------------------------------------------------------------------------------- */
+/* Transform::warpImage(xi, gray, depth, K) (src/core/transform.cpp:35-51) of ref_slot at `level`.
+ * xi: [n_streams][6]; out: [n_streams][h][w]. */
+int dvo_warp_image(dvo_ctx* ctx, int ref_slot, int level, const float* xi, float* out);
+/* Track::optimize(Stuff{obj.at(level), ref.at(level), xi, level}) (src/track/optimize.cpp:10-99;
+ * the warped image of Stuff is computed in-register).  Outputs per stream: upd[6], residual, valid
+ * pixel count, and (optional) the contributing-pixel mask [n_streams][h][w]. */
+int dvo_gn_step(dvo_ctx* ctx, int obj_slot, int ref_slot, int level, const float* xi, float* upd,
+                float* residual, int* valid, uint8_t* mask);
+/* Tracker::track(obj, ref) (src/track/tracker.cpp:22-85), device resident: one kernel per
+ * Gauss-Newton iteration, solve + se3 composition + stop rules in the kernel tail, no host round
+ * trip.  stop_update/stop_residual < 0 select the reference constants.  log: [n_streams][log_cap]. */
+int dvo_track(dvo_ctx* ctx, int obj_slot, int ref_slot, float* xi_out, dvo_iter_log* log, int log_cap,
+              int* n_iters, double stop_update, float stop_residual);
+
+/* ---- mapping -------------------------------------------------------------------------------- */
+/* Mapper::propagate (src/map/mapper.cpp:62-74) = Implement::propagate (implement.cpp:217-256) +
+ * Frame::updateDepthSigmaAge on new_slot.  rel_xi: [n_streams][6]. */
+int dvo_map_propagate(dvo_ctx* ctx, int ref_slot, int new_slot, const float* rel_xi);
+/* Mapper::update (src/map/mapper.cpp:76-137): history_slots[age] = keyframe born `age` keyframes
+ * ago (FrameHistory::operator[], frame.hpp:176); poses are the slots' xi (dvo_frame_set_xi).
+ * Updates ref_slot's depth/sigma/age in place and re-culls.  mask (optional) per pixel:
+ * 1 candidate | 2 accepted by the gate | 4 fused | 8 reset.  valid_updates: [n_streams]. */
+int dvo_map_update(dvo_ctx* ctx, int obj_slot, int ref_slot, const int* history_slots, int n_hist,
+                   int* valid_updates, uint8_t* mask);
+/* Mapper::regularize (src/map/mapper.cpp:139-144) = Implement::regularize (implement.cpp:156-180)
+ * + Frame::updateDepth. */
+int dvo_map_regularize(dvo_ctx* ctx, int slot);
+/* mt19937 replay position (draws consumed so far by Gaussian::update resets), per stream. */
+int dvo_rng_position(dvo_ctx* ctx, uint64_t* pos /*[n_streams]*/);
+
+/* ---- mask compaction ----------------------------------------------------------- */
+/* Row-major compaction of a byte mask on device: idx receives the linear indices of non-zero
+ * entries in increasing order; returns their number in *count. */
+int dvo_mask_compact(dvo_ctx* ctx, const uint8_t* mask, int n, int32_t* idx, int* count);
+
+/* ---- full VO: System::VisualOdometry (include/system/system.hpp:12-104) --------------------- */
+int dvo_vo_reset(dvo_ctx* ctx);
+/* VisualOdometry::odometrize(gray) (system.hpp:44-74) for every stream; the whole frame (pyramid,
+ * <= levels*15 GN iterations, keyframe decision, propagate | update, regularize) is enqueued
+ * without host synchronisation.  init_depth/init_sigma ([n_streams][h_top][w_top], nullable
+ * after the first frame) replace the cv::randn prior of Scene's ctor (frame.hpp:18-21).
+ * T_out ([n_streams][16], nullable) = se3::exp(frame->m_xi); passing NULL keeps the call async. */
+int dvo_vo_push(dvo_ctx* ctx, const float* gray, const float* init_depth, const float* init_sigma, float* T_out);
+int dvo_vo_push_dev(dvo_ctx* ctx, const float* gray_dev, const float* init_depth, const float* init_sigma, float* T_out);
+/* per-stream state of the last pushed frame */
+int dvo_vo_state(dvo_ctx* ctx, float* xi /*[S][6]*/, float* rel_xi /*[S][6]*/, int* was_keyframe /*[S]*/,
+                 int* n_keyframes /*[S]*/, int* valid_updates /*[S]*/, int* n_iters /*[S]*/);
+/* slot of stream s's current keyframe / last frame (for dvo_frame_download) */
+int dvo_vo_ref_slot(dvo_ctx* ctx, int stream, int* slot);
+int dvo_vo_last_slot(dvo_ctx* ctx, int* slot);
+/* first error flagged on device by any stream (history overflow, rng exhaustion), 0 if none */
+int dvo_vo_error(dvo_ctx* ctx);
+
+/* ---- measurement helpers (CUDA events on the context's stream) -------------------------------- */
+int dvo_timer_start(dvo_ctx* ctx);
+int dvo_timer_stop(dvo_ctx* ctx, float* ms); /* synchronises */
+/* number of kernels this context has launched since creation */
+uint64_t dvo_launch_count(const dvo_ctx* ctx);
+/* cumulative device time (ms) of GN-iteration kernels between gn_timing(1) and gn_timing(0),
+ * measured with CUDA events around each launch; *launches = number of launches timed. */
+int dvo_gn_timing(dvo_ctx* ctx, int enable, float* total_ms, int* launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
