@@ -45,7 +45,9 @@ struct dvo_ctx {
     uint32_t* d_rng = nullptr;
     float* d_stage_in = nullptr;   // [S][in_h][in_w]
     float* d_stage[3] = {nullptr, nullptr, nullptr}; // depth/sigma/age uploads, download staging
-    float* d_small = nullptr;      // [S][32] small vectors (xi, poses)
+    float* d_small = nullptr;      // [S][64] small vectors (xi, poses)
+    float* d_forced = nullptr;     // [S][6] forced relative pose for the next dvo_vo_push
+    bool forced_pending = false;
     int* d_ismall = nullptr;       // small int scratch
     void* h_pinned = nullptr;      // pinned staging for small readbacks
     size_t h_pinned_bytes = 0;
@@ -57,7 +59,6 @@ struct dvo_ctx {
     size_t gn_ev_used = 0;
     // VO host mirror
     int vo_frame_id = -1;
-    int vo_last_slot = -1;
     std::mt19937 engine; // default seed 5489, src/math/gaussian.cpp:8
 };
 
@@ -160,6 +161,7 @@ extern "C" int dvo_create(dvo_ctx** out, const dvo_params* p)
         g.fx = Kb[0]; g.fy = Kb[1]; g.cx = Kb[2]; g.cy = Kb[3];
     }
     c.max_kf = p->max_keyframes;
+    c.vo_base = p->max_frames;
     c.max_iter = p->max_iterations;
     c.roi_level = p->roi_level; c.roi_x0 = p->roi_x0; c.roi_x1 = p->roi_x1; c.roi_y0 = p->roi_y0; c.roi_y1 = p->roi_y1;
     {   // (double)d < min_depth  <=>  d < smallest float >= min_depth
@@ -183,9 +185,12 @@ extern "C" int dvo_create(dvo_ctx** out, const dvo_params* p)
     for (int l = 0; l < c.L; l++) sb += rnd((size_t)S * c.lv[l].n * 16) + rnd((size_t)S * c.lv[l].n * 8) + rnd((size_t)S * c.lv[l].n * 4);
     sb += rnd((size_t)S * ntop * 4) + 2 * rnd((size_t)S * 24);
     ctx->slot_bytes = sb;
-    ctx->slots.resize(p->max_frames);
-    CK(cudaMalloc(&ctx->d_slots, sizeof(SlotDev) * p->max_frames));
-    CK(cudaMemset(ctx->d_slots, 0, sizeof(SlotDev) * p->max_frames));
+    // slot ids [0, max_frames): granular API; [max_frames, max_frames + max_keyframes]: the VO pool
+    // (entry k = keyframe k of every stream, entry n_kf = the stream's current frame)
+    const size_t n_slots = (size_t)p->max_frames + p->max_keyframes + 1;
+    ctx->slots.resize(n_slots);
+    CK(cudaMalloc(&ctx->d_slots, sizeof(SlotDev) * n_slots));
+    CK(cudaMemset(ctx->d_slots, 0, sizeof(SlotDev) * n_slots));
     CK(cudaMalloc(&ctx->d_ts, sizeof(TrackState) * S));
     CK(cudaMemset(ctx->d_ts, 0, sizeof(TrackState) * S));
     CK(cudaMalloc(&ctx->d_ms, sizeof(MapState) * S));
@@ -217,6 +222,7 @@ extern "C" int dvo_create(dvo_ctx** out, const dvo_params* p)
     CK(cudaMalloc(&ctx->d_stage_in, sizeof(float) * (size_t)S * c.in_w * c.in_h));
     for (int k = 0; k < 3; k++) CK(cudaMalloc(&ctx->d_stage[k], sizeof(float) * (size_t)S * c.in_w * c.in_h));
     CK(cudaMalloc(&ctx->d_small, sizeof(float) * (size_t)S * 64));
+    CK(cudaMalloc(&ctx->d_forced, sizeof(float) * (size_t)S * 6));
     CK(cudaMalloc(&ctx->d_ismall, sizeof(int) * (size_t)(S > 4096 ? S : 4096)));
     ctx->h_pinned_bytes = sizeof(float) * (size_t)S * 64 + sizeof(dvo_iter_log) * (size_t)S * ctx->log_cap + sizeof(TrackState) * (size_t)S;
     CK(cudaMallocHost(&ctx->h_pinned, ctx->h_pinned_bytes));
@@ -241,7 +247,7 @@ extern "C" void dvo_destroy(dvo_ctx* ctx)
     cudaFree(ctx->d_tab); cudaFree(ctx->d_partials); cudaFree(ctx->d_log); cudaFree(ctx->d_flags); cudaFree(ctx->d_mask);
     cudaFree(ctx->d_blockcnt); cudaFree(ctx->d_winner); cudaFree(ctx->d_tmp); cudaFree(ctx->d_rng); cudaFree(ctx->d_stage_in);
     for (int k = 0; k < 3; k++) cudaFree(ctx->d_stage[k]);
-    cudaFree(ctx->d_small); cudaFree(ctx->d_ismall);
+    cudaFree(ctx->d_small); cudaFree(ctx->d_ismall); cudaFree(ctx->d_forced);
     if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
     for (auto e : ctx->gn_ev) cudaEventDestroy(e);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
@@ -279,7 +285,7 @@ extern "C" void dvo_host_free(void* p) { if (p) cudaFreeHost(p); }
 // ---- frames ---------------------------------------------------------------------------------
 static int find_free_slot(dvo_ctx* ctx, int* slot)
 {
-    for (size_t i = 0; i < ctx->slots.size(); i++)
+    for (size_t i = 0; i < (size_t)ctx->P.max_frames; i++)
         if (!ctx->slots[i].in_use) {
             int rc = alloc_slot(ctx, (int)i);
             if (rc) return rc;
@@ -299,14 +305,15 @@ static int check_slot(dvo_ctx* ctx, int slot)
     return DVO_OK;
 }
 
+// slot >= 0: that slot for every stream; slot < 0: each stream's current VO slot (VoState::cur_slot)
 static int build_frame(dvo_ctx* ctx, int slot, const float* gray_dev)
 {
     const Consts& c = ctx->c;
-    const SlotDev& sd = ctx->slots[slot].dev;
+    const VoState* vo = slot < 0 ? ctx->d_vo : nullptr;
     dim3 grid(cdiv(c.lv[c.L - 1].n, 256), c.S, c.L);
-    k_cull_gray<<<grid, 256, 0, ctx->stream>>>(c, gray_dev, sd);
+    k_cull_gray<<<grid, 256, 0, ctx->stream>>>(c, gray_dev, ctx->d_slots, slot, vo);
     KCHECK();
-    k_build_tex<<<grid, 256, 0, ctx->stream>>>(c, sd);
+    k_build_tex<<<grid, 256, 0, ctx->stream>>>(c, ctx->d_slots, slot, vo);
     KCHECK();
     return DVO_OK;
 }
@@ -340,15 +347,14 @@ static int recull_ds(dvo_ctx* ctx, int slot)
     const Consts& c = ctx->c;
     if (c.L < 2) return DVO_OK;
     dim3 grid(cdiv(c.lv[c.L - 2].n, 256), c.S, c.L - 1);
-    k_cull_ds<<<grid, 256, 0, ctx->stream>>>(c, ctx->slots[slot].dev);
+    k_cull_ds<<<grid, 256, 0, ctx->stream>>>(c, ctx->d_slots, slot, slot < 0 ? ctx->d_vo : nullptr);
     KCHECK();
     return DVO_OK;
 }
 
-extern "C" int dvo_frame_set_depth(dvo_ctx* ctx, int slot, const float* depth, const float* sigma, const float* age, int full_res)
+static int set_depth_impl(dvo_ctx* ctx, int slot, const float* depth, const float* sigma, const float* age, int full_res)
 {
-    int rc = check_slot(ctx, slot);
-    if (rc) return rc;
+    int rc;
     const Consts& c = ctx->c;
     const LevelGeom& gt = c.lv[c.L - 1];
     const int sw = full_res ? c.in_w : gt.w, sh = full_res ? c.in_h : gt.h;
@@ -360,12 +366,20 @@ extern "C" int dvo_frame_set_depth(dvo_ctx* ctx, int slot, const float* depth, c
             dev[k] = ctx->d_stage[k];
         }
     dim3 grid(cdiv(gt.n, 256), c.S);
-    k_set_top<<<grid, 256, 0, ctx->stream>>>(c, ctx->slots[slot].dev, dev[0], dev[1], dev[2], sw, sh, full_res ? c.culls : 0);
+    k_set_top<<<grid, 256, 0, ctx->stream>>>(c, ctx->d_slots, slot, slot < 0 ? ctx->d_vo : nullptr, dev[0], dev[1], dev[2], sw, sh,
+                                              full_res ? c.culls : 0);
     KCHECK();
     rc = recull_ds(ctx, slot);
     if (rc) return rc;
     CK(cudaStreamSynchronize(ctx->stream)); // host buffers may be pageable: do not return before the copies finish
     return DVO_OK;
+}
+
+extern "C" int dvo_frame_set_depth(dvo_ctx* ctx, int slot, const float* depth, const float* sigma, const float* age, int full_res)
+{
+    int rc = check_slot(ctx, slot);
+    if (rc) return rc;
+    return set_depth_impl(ctx, slot, depth, sigma, age, full_res);
 }
 
 extern "C" int dvo_frame_download(dvo_ctx* ctx, int slot, int level, int kind, float* out)
@@ -727,7 +741,7 @@ __global__ void k_vo_reset(Consts c, VoState* vo, MapState* mst)
 {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= c.S) return;
-    vo[s].kf_slot = -1; vo[s].kf_frame_id = -1; vo[s].n_kf = 0; vo[s].need_new = 0; vo[s].was_keyframe = 0; vo[s].n_iters = 0;
+    vo[s].kf_slot = -1; vo[s].kf_frame_id = -1; vo[s].n_kf = 0; vo[s].need_new = 0; vo[s].was_keyframe = 0; vo[s].n_iters = 0; vo[s].cur_slot = c.vo_base;
     mst[s].rng_pos = 0; mst[s].err = 0; mst[s].valid_update = 0; mst[s].ticket = 0;
 }
 
@@ -736,40 +750,69 @@ extern "C" int dvo_vo_reset(dvo_ctx* ctx)
     const Consts& c = ctx->c;
     for (auto& s : ctx->slots) s.in_use = false;
     ctx->vo_frame_id = -1;
-    ctx->vo_last_slot = -1;
+    ctx->forced_pending = false;
     k_vo_reset<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_vo, ctx->d_ms);
     KCHECK();
+    return DVO_OK;
+}
+
+extern "C" int dvo_vo_force_pose(dvo_ctx* ctx, const float* rel_xi)
+{
+    if (!rel_xi) {
+        ctx->forced_pending = false;
+        return DVO_OK;
+    }
+    CK(cudaMemcpyAsync(ctx->d_forced, rel_xi, sizeof(float) * 6 * (size_t)ctx->c.S, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->forced_pending = true;
     return DVO_OK;
 }
 
 extern "C" int dvo_vo_push_dev(dvo_ctx* ctx, const float* gray_dev, const float* init_depth, const float* init_sigma, float* T_out)
 {
     const Consts& c = ctx->c;
-    int cur = -1;
-    int rc = dvo_frame_create_dev(ctx, &cur, gray_dev); // make_shared<Frame>(gray, K, 3, 2), system.hpp:47
-    if (rc) return rc;
+    ARG(gray_dev, "null gray");
     const int frame_id = ++ctx->vo_frame_id; // Frame::latest_id, frame.cpp:5
+    // After f pushed frames a stream owns at most f keyframes: pool entries 0..min(f, max_kf) can be
+    // touched by this push.  Entries are allocated on first need and never freed (FrameHistory is
+    // never pruned, frame.hpp:179-185).
+    {
+        const int need = (frame_id < c.max_kf ? frame_id : c.max_kf);
+        for (int k = 0; k <= need; k++) {
+            SlotHost& sh = ctx->slots[c.vo_base + k];
+            if (!sh.base) {
+                int rc = alloc_slot(ctx, c.vo_base + k);
+                if (rc) return rc;
+            }
+            sh.in_use = true;
+        }
+    }
+    k_vo_begin<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_vo, ctx->d_ms);
+    KCHECK();
+    int rc = build_frame(ctx, -1, gray_dev); // make_shared<Frame>(gray, K, 3, 2), system.hpp:47
+    if (rc) return rc;
     if (init_depth || init_sigma) {
-        rc = dvo_frame_set_depth(ctx, cur, init_depth, init_sigma, nullptr, 0);
+        rc = set_depth_impl(ctx, -1, init_depth, init_sigma, nullptr, 0);
         if (rc) return rc;
     }
     // Tracking (system.hpp:57): against each stream's current keyframe; no-op on the first frame
-    rc = enqueue_track(ctx, cur, cur, true, -1.0, -1.0f);
+    rc = enqueue_track(ctx, -1, -1, true, -1.0, -1.0f);
     if (rc) return rc;
-    k_vo_decide<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ts, ctx->d_vo, ctx->d_ms, cur, frame_id);
+    k_vo_decide<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ts, ctx->d_vo, ctx->d_ms, frame_id,
+                                                       ctx->forced_pending ? ctx->d_forced : nullptr);
     KCHECK();
+    ctx->forced_pending = false;
     // Mapping (system.hpp:67, mapper.cpp:16-33): per stream either propagate or update
     rc = enqueue_propagate(ctx);
     if (rc) return rc;
     rc = enqueue_update(ctx);
     if (rc) return rc;
-    k_vo_commit<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_vo, ctx->d_ms, ctx->d_hist, cur, frame_id);
+    k_vo_commit<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_vo, ctx->d_ms, ctx->d_hist, frame_id);
     KCHECK();
     rc = enqueue_regularize(ctx);
     if (rc) return rc;
-    ctx->vo_last_slot = cur;
     if (T_out) {
-        k_pose_out<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->slots[cur].dev, ctx->d_small);
+        k_pose_out<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_vo, ctx->d_small);
         KCHECK();
         CK(cudaMemcpyAsync(T_out, ctx->d_small, sizeof(float) * 16 * (size_t)c.S, cudaMemcpyDeviceToHost, ctx->stream));
         CK(cudaStreamSynchronize(ctx->stream));
@@ -788,20 +831,39 @@ extern "C" int dvo_vo_push(dvo_ctx* ctx, const float* gray, const float* init_de
 extern "C" int dvo_vo_state(dvo_ctx* ctx, float* xi, float* rel_xi, int* was_keyframe, int* n_keyframes, int* valid_updates, int* n_iters)
 {
     const Consts& c = ctx->c;
-    ARG(ctx->vo_last_slot >= 0, "no frame pushed");
+    ARG(ctx->vo_frame_id >= 0, "no frame pushed");
     std::vector<VoState> hv(c.S);
     std::vector<MapState> hm(c.S);
+    std::vector<float> hx((size_t)c.S * 12);
+    k_vo_gather_xi<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_vo, ctx->d_small);
+    KCHECK();
     CK(cudaMemcpyAsync(hv.data(), ctx->d_vo, sizeof(VoState) * (size_t)c.S, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaMemcpyAsync(hm.data(), ctx->d_ms, sizeof(MapState) * (size_t)c.S, cudaMemcpyDeviceToHost, ctx->stream));
-    const SlotDev& sd = ctx->slots[ctx->vo_last_slot].dev;
-    if (xi) CK(cudaMemcpyAsync(xi, sd.xi, sizeof(float) * 6 * (size_t)c.S, cudaMemcpyDeviceToHost, ctx->stream));
-    if (rel_xi) CK(cudaMemcpyAsync(rel_xi, sd.rel_xi, sizeof(float) * 6 * (size_t)c.S, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(hx.data(), ctx->d_small, sizeof(float) * 12 * (size_t)c.S, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     for (int s = 0; s < c.S; s++) {
+        if (xi) memcpy(xi + 6 * s, &hx[12 * s], sizeof(float) * 6);
+        if (rel_xi) memcpy(rel_xi + 6 * s, &hx[12 * s + 6], sizeof(float) * 6);
         if (was_keyframe) was_keyframe[s] = hv[s].was_keyframe;
         if (n_keyframes) n_keyframes[s] = hv[s].n_kf;
         if (valid_updates) valid_updates[s] = hm[s].valid_update;
         if (n_iters) n_iters[s] = hv[s].n_iters;
+    }
+    return DVO_OK;
+}
+
+extern "C" int dvo_vo_last_log(dvo_ctx* ctx, dvo_iter_log* log, int log_cap, int* n_iters)
+{
+    const Consts& c = ctx->c;
+    ARG(log && log_cap > 0, "bad argument");
+    TrackState* hts = (TrackState*)((char*)ctx->h_pinned + sizeof(dvo_iter_log) * (size_t)c.S * ctx->log_cap);
+    dvo_iter_log* hl = (dvo_iter_log*)ctx->h_pinned;
+    CK(cudaMemcpyAsync(hts, ctx->d_ts, sizeof(TrackState) * (size_t)c.S, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(hl, ctx->d_log, sizeof(dvo_iter_log) * (size_t)c.S * ctx->log_cap, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (int s = 0; s < c.S; s++) {
+        if (n_iters) n_iters[s] = hts[s].n_total;
+        for (int k = 0; k < hts[s].n_total && k < log_cap && k < ctx->log_cap; k++) log[(size_t)s * log_cap + k] = hl[(size_t)s * ctx->log_cap + k];
     }
     return DVO_OK;
 }
@@ -816,10 +878,14 @@ extern "C" int dvo_vo_ref_slot(dvo_ctx* ctx, int stream, int* slot)
     *slot = v.kf_slot;
     return DVO_OK;
 }
-extern "C" int dvo_vo_last_slot(dvo_ctx* ctx, int* slot)
+extern "C" int dvo_vo_last_slot(dvo_ctx* ctx, int stream, int* slot)
 {
-    ARG(slot, "null");
-    *slot = ctx->vo_last_slot;
+    const Consts& c = ctx->c;
+    ARG(stream >= 0 && stream < c.S && slot, "bad stream");
+    VoState v;
+    CK(cudaMemcpyAsync(&v, ctx->d_vo + stream, sizeof(VoState), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    *slot = v.cur_slot;
     return DVO_OK;
 }
 extern "C" int dvo_vo_error(dvo_ctx* ctx) { return map_error(ctx); }

@@ -15,6 +15,7 @@ struct Consts {
     int in_w, in_h, culls;
     LevelGeom lv[MAXL];
     int max_kf;
+    int vo_base; // first slot id of the VO keyframe pool (= dvo_params.max_frames)
     // tracking
     int max_iter;
     int roi_level, roi_x0, roi_x1, roi_y0, roi_y1;
@@ -76,6 +77,8 @@ struct VoState {
     int kf_slot, kf_frame_id, n_kf;
     int need_new, was_keyframe;
     int n_iters;
+    int cur_slot; // slot holding this stream's current frame: vo_base + n_kf (see k_vo_begin)
+    int pad;
 };
 
 struct PoseTab { // per (stream, age): exp(-r_xi) and -r_xi[0:3] (src/map/mapper.cpp:107, implement.cpp:56-58,193)

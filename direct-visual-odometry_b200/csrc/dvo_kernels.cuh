@@ -9,9 +9,19 @@ namespace dvo {
 // Frame construction: Convert::cullImage (convert.cpp:7-20), Convert::gradiate (convert.cpp:41-75),
 // Frame::createScenePyramid (frame.cpp:30-37).  grid = (ceil(n_top/256), S, L)
 // =============================================================================================
-__global__ void __launch_bounds__(256) k_cull_gray(const __grid_constant__ Consts c, const float* __restrict__ in, SlotDev slot)
+// Slot of stream s for the frame-construction kernels: a fixed slot (granular API) or, in the VO
+// loop, the stream's own current slot (streams take keyframes at different times, so the current
+// frame of each stream lives in the pool entry after its newest keyframe).
+__device__ __forceinline__ const SlotDev& slot_of(const SlotDev* __restrict__ slots, int fixed, const VoState* __restrict__ vo, int s)
+{
+    return slots[vo ? vo[s].cur_slot : fixed];
+}
+
+__global__ void __launch_bounds__(256) k_cull_gray(const __grid_constant__ Consts c, const float* __restrict__ in,
+                                                   const SlotDev* __restrict__ slots, int fixed, const VoState* __restrict__ vo)
 {
     const int l = blockIdx.z, s = blockIdx.y;
+    const SlotDev& slot = slot_of(slots, fixed, vo, s);
     const LevelGeom g = c.lv[l];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= g.n) return;
@@ -22,9 +32,11 @@ __global__ void __launch_bounds__(256) k_cull_gray(const __grid_constant__ Const
     slot.gray[l][(size_t)s * g.n + i] = (sh == 0) ? v : get_pixel_value(v);
 }
 
-__global__ void __launch_bounds__(256) k_build_tex(const __grid_constant__ Consts c, SlotDev slot)
+__global__ void __launch_bounds__(256) k_build_tex(const __grid_constant__ Consts c, const SlotDev* __restrict__ slots, int fixed,
+                                                   const VoState* __restrict__ vo)
 {
     const int l = blockIdx.z, s = blockIdx.y;
+    const SlotDev& slot = slot_of(slots, fixed, vo, s);
     const LevelGeom g = c.lv[l];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= g.n) return;
@@ -45,11 +57,13 @@ __global__ void __launch_bounds__(256) k_build_tex(const __grid_constant__ Const
 
 // depth / sigma / age upload (Frame 6-arg ctor frame.hpp:91-106, updateDepthSigmaAge frame.cpp:47-54).
 // src arrays are [S][sh][sw]; shift = culls when full-res, 0 otherwise.  grid = (ceil(n_top/256), S)
-__global__ void __launch_bounds__(256) k_set_top(const __grid_constant__ Consts c, SlotDev slot, const float* __restrict__ depth,
+__global__ void __launch_bounds__(256) k_set_top(const __grid_constant__ Consts c, const SlotDev* __restrict__ slots, int fixed,
+                                                 const VoState* __restrict__ vo, const float* __restrict__ depth,
                                                  const float* __restrict__ sigma, const float* __restrict__ age, int sw, int sh_,
                                                  int shift)
 {
     const int s = blockIdx.y;
+    const SlotDev& slot = slot_of(slots, fixed, vo, s);
     const LevelGeom g = c.lv[c.L - 1];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= g.n) return;
@@ -65,9 +79,11 @@ __global__ void __launch_bounds__(256) k_set_top(const __grid_constant__ Consts 
 
 // Re-cull the coarser depth/sigma levels from the finest (frame.cpp:39-61).
 // grid = (ceil(n_{L-2}/256), S, L-1)
-__global__ void __launch_bounds__(256) k_cull_ds(const __grid_constant__ Consts c, SlotDev slot)
+__global__ void __launch_bounds__(256) k_cull_ds(const __grid_constant__ Consts c, const SlotDev* __restrict__ slots, int fixed,
+                                                 const VoState* __restrict__ vo)
 {
     const int l = blockIdx.z, s = blockIdx.y;
+    const SlotDev& slot = slot_of(slots, fixed, vo, s);
     const LevelGeom g = c.lv[l];
     const LevelGeom gt = c.lv[c.L - 1];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -448,6 +464,7 @@ __global__ void k_track_init(const __grid_constant__ Consts c, TrackState* st, c
     if (s >= c.S) return;
     TrackState* t = st + s;
     const int rs = vo ? vo[s].kf_slot : ref_slot;
+    if (vo) obj_slot = vo[s].cur_slot;
     const SlotDev o = slots[obj_slot];
     const SlotDev r = slots[rs < 0 ? obj_slot : rs];
     for (int l = 0; l < c.L; l++) {
@@ -847,12 +864,13 @@ __global__ void __launch_bounds__(256) k_ds_rebuild(const __grid_constant__ Cons
 // =============================================================================================
 // After tracking: Frame::updateXi (frame.cpp:7-14), Mapper::needNewFrame (mapper.cpp:45-60).
 __global__ void k_vo_decide(const __grid_constant__ Consts c, const SlotDev* __restrict__ slots, const TrackState* __restrict__ ts,
-                            VoState* __restrict__ vo, MapState* __restrict__ mst, int cur_slot, int frame_id)
+                            VoState* __restrict__ vo, MapState* __restrict__ mst, int frame_id, const float* __restrict__ forced_rel)
 {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= c.S) return;
     VoState* v = vo + s;
     MapState* m = mst + s;
+    const int cur_slot = v->cur_slot;
     const SlotDev cur = slots[cur_slot];
     m->valid_update = 0; m->n_reject = 0; m->ticket = 0;
     if (v->kf_slot < 0) { // first frame: m_history.setRefFrame(frame); return identity (system.hpp:49-54)
@@ -863,7 +881,9 @@ __global__ void k_vo_decide(const __grid_constant__ Consts c, const SlotDev* __r
     }
     float rel[6], kxi[6], xi[6];
     const SlotDev kf = slots[v->kf_slot];
-    for (int q = 0; q < 6; q++) { rel[q] = ts[s].xi[q]; kxi[q] = kf.xi[6 * s + q]; }
+    // forced_rel: the caller supplies the relative pose (teacher-forced parity runs, external pose
+    // priors); the tracker's own result stays available in the iteration log.
+    for (int q = 0; q < 6; q++) { rel[q] = forced_rel ? forced_rel[6 * s + q] : ts[s].xi[q]; kxi[q] = kf.xi[6 * s + q]; }
     se3_concatenate(kxi, rel, xi);
     for (int q = 0; q < 6; q++) { cur.xi[6 * s + q] = xi[q]; cur.rel_xi[6 * s + q] = rel[q]; }
     v->n_iters = ts[s].n_total;
@@ -885,12 +905,13 @@ __global__ void k_vo_decide(const __grid_constant__ Consts c, const SlotDev* __r
 
 // FrameHistory::setRefFrame (frame.hpp:151-157) after propagate; regularize target = newest keyframe.
 __global__ void k_vo_commit(const __grid_constant__ Consts c, VoState* __restrict__ vo, MapState* __restrict__ mst, int* __restrict__ hist,
-                            int cur_slot, int frame_id)
+                            int frame_id)
 {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= c.S) return;
     VoState* v = vo + s;
     MapState* m = mst + s;
+    const int cur_slot = v->cur_slot;
     if (v->need_new) {
         if (v->n_kf >= c.max_kf) {
             atomicCAS(&m->err, 0, (int)DVO_ERR_HISTORY);
@@ -905,13 +926,35 @@ __global__ void k_vo_commit(const __grid_constant__ Consts c, VoState* __restric
 }
 
 // se3::exp(frame->m_xi) for odometrize's return value (system.hpp:73)
-__global__ void k_pose_out(const __grid_constant__ Consts c, SlotDev cur, float* __restrict__ T_out)
+__global__ void k_pose_out(const __grid_constant__ Consts c, const SlotDev* __restrict__ slots, const VoState* __restrict__ vo,
+                           float* __restrict__ T_out)
 {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= c.S) return;
     float T[16];
-    se3_exp(cur.xi + 6 * s, T);
+    se3_exp(slots[vo[s].cur_slot].xi + 6 * s, T);
     for (int q = 0; q < 16; q++) T_out[16 * s + q] = T[q];
+}
+
+// Start of a VO frame: the stream's current frame goes into the pool entry after its newest
+// keyframe (entry k of the pool holds keyframe k of every stream: FrameHistory::m_history[k]).
+__global__ void k_vo_begin(const __grid_constant__ Consts c, VoState* __restrict__ vo, MapState* __restrict__ mst)
+{
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= c.S) return;
+    int k = vo[s].n_kf;
+    if (k > c.max_kf) k = c.max_kf;
+    vo[s].cur_slot = c.vo_base + k;
+}
+
+// xi / rel_xi of every stream's current frame, gathered for dvo_vo_state.  out: [S][12]
+__global__ void k_vo_gather_xi(const __grid_constant__ Consts c, const SlotDev* __restrict__ slots, const VoState* __restrict__ vo,
+                               float* __restrict__ out)
+{
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= c.S) return;
+    const SlotDev& sd = slots[vo[s].cur_slot];
+    for (int q = 0; q < 6; q++) { out[12 * s + q] = sd.xi[6 * s + q]; out[12 * s + 6 + q] = sd.rel_xi[6 * s + q]; }
 }
 
 // =============================================================================================

@@ -43,8 +43,8 @@ EXPORTS = [
     "dvo_host_alloc", "dvo_host_free", "dvo_frame_create", "dvo_frame_create_dev", "dvo_frame_release",
     "dvo_frame_set_depth", "dvo_frame_download", "dvo_frame_set_xi", "dvo_frame_get_xi", "dvo_warp_image",
     "dvo_gn_step", "dvo_track", "dvo_map_propagate", "dvo_map_update", "dvo_map_regularize", "dvo_rng_position",
-    "dvo_mask_compact", "dvo_vo_reset", "dvo_vo_push", "dvo_vo_push_dev", "dvo_vo_state", "dvo_vo_ref_slot",
-    "dvo_vo_last_slot", "dvo_vo_error", "dvo_timer_start", "dvo_timer_stop", "dvo_launch_count", "dvo_gn_timing",
+    "dvo_mask_compact", "dvo_vo_reset", "dvo_vo_force_pose", "dvo_vo_push", "dvo_vo_push_dev", "dvo_vo_state", "dvo_vo_ref_slot",
+    "dvo_vo_last_slot", "dvo_vo_last_log", "dvo_vo_error", "dvo_timer_start", "dvo_timer_stop", "dvo_launch_count", "dvo_gn_timing",
 ]
 
 
@@ -85,8 +85,10 @@ def load_library(path=None):
     lib.dvo_vo_push_dev.argtypes = [C.c_void_p, C.c_void_p, F32P, F32P, F32P]
     lib.dvo_vo_state.argtypes = [C.c_void_p, F32P, F32P, I32P, I32P, I32P, I32P]
     lib.dvo_vo_ref_slot.argtypes = [C.c_void_p, C.c_int, I32P]
-    lib.dvo_vo_last_slot.argtypes = [C.c_void_p, I32P]
+    lib.dvo_vo_last_slot.argtypes = [C.c_void_p, C.c_int, I32P]
+    lib.dvo_vo_force_pose.argtypes = [C.c_void_p, F32P]
     lib.dvo_vo_error.argtypes = [C.c_void_p]
+    lib.dvo_vo_last_log.argtypes = [C.c_void_p, C.POINTER(DvoIterLog), C.c_int, I32P]
     lib.dvo_timer_start.argtypes = [C.c_void_p]
     lib.dvo_timer_stop.argtypes = [C.c_void_p, F32P]
     lib.dvo_launch_count.restype = C.c_uint64
@@ -295,10 +297,25 @@ class Dvo:
         self._ck(self.lib.dvo_vo_ref_slot(self.ctx, stream, C.byref(s)))
         return s.value
 
-    def vo_last_slot(self):
+    def vo_last_slot(self, stream=0):
         s = C.c_int(-1)
-        self._ck(self.lib.dvo_vo_last_slot(self.ctx, C.byref(s)))
+        self._ck(self.lib.dvo_vo_last_slot(self.ctx, stream, C.byref(s)))
         return s.value
+
+    def vo_force_pose(self, rel_xi):
+        x = self._xi(rel_xi) if rel_xi is not None else None
+        self._ck(self.lib.dvo_vo_force_pose(self.ctx, _p(x)))
+
+    def vo_last_log(self):
+        cap = self.L * self.params.max_iterations
+        n = np.empty(self.S, np.int32)
+        log = (DvoIterLog * (cap * self.S))()
+        self._ck(self.lib.dvo_vo_last_log(self.ctx, log, cap, n.ctypes.data_as(I32P)))
+        return [[dict(level=log[s * cap + k].level, iteration=log[s * cap + k].iteration,
+                      valid_pixels=log[s * cap + k].valid_pixels, residual=log[s * cap + k].residual,
+                      update=np.array(log[s * cap + k].update[:], np.float32),
+                      xi_after=np.array(log[s * cap + k].xi_after[:], np.float32)) for k in range(int(n[s]))]
+                for s in range(self.S)]
 
     def vo_error(self):
         return self.lib.dvo_vo_error(self.ctx)

@@ -151,12 +151,21 @@ int dvo_vo_reset(dvo_ctx* ctx);
  * T_out ([n_streams][16], nullable) = se3::exp(frame->m_xi); passing NULL keeps the call async. */
 int dvo_vo_push(dvo_ctx* ctx, const float* gray, const float* init_depth, const float* init_sigma, float* T_out);
 int dvo_vo_push_dev(dvo_ctx* ctx, const float* gray_dev, const float* init_depth, const float* init_sigma, float* T_out);
+/* Supply the relative pose (frame-from-keyframe twist, [n_streams][6]) the NEXT dvo_vo_push uses for
+ * Frame::updateXi (frame.cpp:7-14) and mapping instead of its own tracking result; the tracker still
+ * runs and its iterations stay readable through dvo_vo_last_log.  Used for teacher-forced parity
+ * runs (the reference's iteration is chaotic at keyframe switches) and external pose
+ * priors.  NULL cancels. */
+int dvo_vo_force_pose(dvo_ctx* ctx, const float* rel_xi);
 /* per-stream state of the last pushed frame */
 int dvo_vo_state(dvo_ctx* ctx, float* xi /*[S][6]*/, float* rel_xi /*[S][6]*/, int* was_keyframe /*[S]*/,
                  int* n_keyframes /*[S]*/, int* valid_updates /*[S]*/, int* n_iters /*[S]*/);
+/* Gauss-Newton iteration records of the last pushed frame's tracking (what Tracker::track prints,
+ * src/track/tracker.cpp:56-61).  log: [n_streams][log_cap]; n_iters: [n_streams]. */
+int dvo_vo_last_log(dvo_ctx* ctx, dvo_iter_log* log, int log_cap, int* n_iters);
 /* slot of stream s's current keyframe / last frame (for dvo_frame_download) */
 int dvo_vo_ref_slot(dvo_ctx* ctx, int stream, int* slot);
-int dvo_vo_last_slot(dvo_ctx* ctx, int* slot);
+int dvo_vo_last_slot(dvo_ctx* ctx, int stream, int* slot);
 /* first error flagged on device by any stream (history overflow, rng exhaustion), 0 if none */
 int dvo_vo_error(dvo_ctx* ctx);
 

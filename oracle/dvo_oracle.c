@@ -1063,6 +1063,8 @@ struct orc_vo {
     int last_was_keyframe, last_valid_update;
     uint8_t* upd_mask;
     size_t upd_mask_n;
+    orc_iter_log log[256]; /* Gauss-Newton iterations of the last frame's tracking */
+    int n_log;
 };
 
 orc_vo* orc_vo_create(const float K[9], int levels, int culls, const orc_params* P)
@@ -1100,6 +1102,12 @@ int orc_vo_last_was_keyframe(const orc_vo* vo) { return vo->last_was_keyframe; }
 int orc_vo_last_valid_update(const orc_vo* vo) { return vo->last_valid_update; }
 uint64_t orc_vo_rng_draws(const orc_vo* vo) { return vo->rng.draws; }
 const uint8_t* orc_vo_last_update_mask(const orc_vo* vo) { return vo->upd_mask; }
+int orc_vo_last_log(const orc_vo* vo, orc_iter_log* out, int cap)
+{
+    int n = vo->n_log < cap ? vo->n_log : cap;
+    memcpy(out, vo->log, (size_t)n * sizeof(orc_iter_log));
+    return vo->n_log;
+}
 
 int orc_vo_odometrize(orc_vo* vo, const float* gray, int w, int h, const float* init_depth,
                       const float* init_sigma, float T_out[16])
@@ -1111,6 +1119,7 @@ int orc_vo_odometrize(orc_vo* vo, const float* gray, int w, int h, const float* 
     vo->last = frame;
     vo->last_was_keyframe = 0;
     vo->last_valid_update = 0;
+    vo->n_log = 0;
     orc_frame* ref = orc_vo_ref_frame(vo);
     if (!ref) { /* :49-54 */
         vo_push_history(vo, frame);
@@ -1120,7 +1129,8 @@ int orc_vo_odometrize(orc_vo* vo, const float* gray, int w, int h, const float* 
     }
     /* Tracking :57-58 */
     float rel[6];
-    orc_track(frame, ref, &vo->P, rel, NULL, 0, (double)vo->P.min_update, vo->P.min_residual);
+    vo->n_log = orc_track(frame, ref, &vo->P, rel, vo->log, 256, (double)vo->P.min_update, vo->P.min_residual);
+    if (vo->n_log > 256) vo->n_log = 256;
     memcpy(frame->rel_xi, rel, sizeof rel); /* Frame::updateXi frame.cpp:7-14 */
     frame->ref = ref;
     orc_se3_concatenate(ref->xi, rel, frame->xi);

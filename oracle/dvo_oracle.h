@@ -135,6 +135,8 @@ uint64_t orc_vo_rng_draws(const orc_vo* vo);
 /* masks of the last Mapper::update: 1 candidate (entered Implement::update), 2 accepted gate,
  * 4 fused ok, 8 reset.  Size = finest w*h. */
 const uint8_t* orc_vo_last_update_mask(const orc_vo* vo);
+/* Gauss-Newton iteration records of the last frame's tracking; returns their number */
+int orc_vo_last_log(const orc_vo* vo, orc_iter_log* out, int cap);
 /* Mapper::update as a standalone op (src/map/mapper.cpp:76-137) on explicit arrays.
  * born_* are arrays of n_hist pointers indexed by age; hist_xi is n_hist x 6 (index = age). */
 int orc_mapper_update(float* depth, float* sigma, float* age, int w, int h, const float* obj_gray,

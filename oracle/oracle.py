@@ -101,6 +101,7 @@ class Oracle:
         L.orc_vo_rng_draws.argtypes = [C.c_void_p]
         L.orc_vo_last_update_mask.restype = U8P
         L.orc_vo_last_update_mask.argtypes = [C.c_void_p]
+        L.orc_vo_last_log.argtypes = [C.c_void_p, C.POINTER(OrcIterLog), C.c_int]
         L.orc_mapper_update.argtypes = [F32P, F32P, F32P, C.c_int, C.c_int, F32P, C.POINTER(F32P), C.POINTER(F32P),
                                         C.POINTER(F32P), F32P, C.c_int, F32P, F32P, F32P, C.POINTER(OrcParams),
                                         C.POINTER(OrcRng), U8P, C.POINTER(C.c_int)]
@@ -370,6 +371,13 @@ class OrcVO:
 
     def rng_draws(self):
         return int(self.orc.lib.orc_vo_rng_draws(self.h))
+
+    def last_log(self):
+        log = (OrcIterLog * 256)()
+        n = self.orc.lib.orc_vo_last_log(self.h, log, 256)
+        return [dict(level=L.level, iteration=L.iteration, valid_pixels=L.valid_pixels, residual=L.residual,
+                     update=np.array(L.update[:], np.float32), xi_before=np.array(L.xi_before[:], np.float32),
+                     xi_after=np.array(L.xi_after[:], np.float32)) for L in log[:min(n, 256)]]
 
     def last_update_mask(self):
         f = self.ref_frame()
