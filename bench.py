@@ -1,0 +1,435 @@
+#!/usr/bin/env python
+"""bench.py — VO frames/s (track + map) of the B200 hot path, and the reference's CPU path beside it.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+Workload (BASELINE.json: "VO frames/sec (track+map) at 640x480", config C5 "batched multi-stream"
+at main.cpp's geometry, configs[1]): every GPU runs `--streams` (256) independent synthetic 640x480
+sequences in lock-step through System::VisualOdometry::odometrize semantics — Frame(gray, K, 3, 2),
+Tracker::track, Mapper::estimate (needNewFrame -> propagate | update, regularize).  One STEP = one
+new frame of every stream (dvo_vo_push over the whole batch).  Sequences are independent, so N GPUs
+run N x 256 streams with no data-path collective ("scaling": "weak").
+
+  value      frames/s with the frames already resident in HBM (dvo_vo_push_dev), CUDA events
+  e2e        the same through dvo_vo_push with pinned HOST frames: the H2D copy of the step's input and
+             the D2H read of the step's poses are inside the timed region
+  roofline   the Gauss-Newton iteration kernel (k_gn_step): algorithmic bytes 16 B x pixels swept
+              / its device time (CUDA events around every launch, separate pass)
+  cpu_baseline  the CPU oracle (oracle/, a C restatement of the reference; or oracle/_ref = the
+             reference's own sources when built) on the host cores, one sequence per core
+
+`--impl reference` times only the CPU arm (rank 0), same metric / config.
+"""
+import argparse
+import json
+import multiprocessing as mp
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "direct-visual-odometry_b200")
+for p in (ROOT, PKG):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+W_IN, H_IN, LEVELS, CULLS = 640, 480, 3, 2      # main.cpp: Frame(gray, K, 3, 2) on 640x480 (system.hpp:47)
+TRANS_STEP, ROT_STEP_DEG = 0.004, 0.15          # per-frame motion of the synthetic trajectories
+GN_BYTES_PER_PX = 16                            # depth, sigma, obj gray, ref gray read once
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks: nvidia-smi sampled DURING the timed region (B200_PROFILING.md)
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            f = tempfile.NamedTemporaryFile("w", suffix=".csv", delete=False)
+            self.path = f.name
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if not self.proc:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm = []; mx = []; reasons = set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        try:
+            for line in open(self.path):
+                f = [x.strip() for x in line.split(",")]
+                if len(f) < 9:
+                    continue
+                try:
+                    sm.append(float(f[1])); mx.append(float(f[2]))
+                except ValueError:
+                    continue
+                for n, v in zip(names, f[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            os.unlink(self.path)
+        except Exception:
+            pass
+        if sm:
+            hi = [x for x in sm if x >= 0.5 * max(sm)]   # samples under load
+            out.update(sm_mhz=statistics.median(hi), sm_max_mhz=max(mx), samples=len(sm))
+        out["reasons"] = sorted(reasons)
+        return out
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle (or oracle/_ref) on the host cores, one independent sequence per worker process
+# ------------------------------------------------------------------------------------------------
+def _build_cpu_lib():
+    """Compile the CPU arm's library ON THIS HOST (-march=native must match the cores it runs on)."""
+    from oracle import oracle as O
+    d = tempfile.mkdtemp(prefix="dvo_cpu_")
+    return O.build(fast=True, out_dir=d)
+
+
+def _cpu_worker(conn, frames, K, d0, s0, lib_path):
+    """frames: [n][h][w] float32 (shared, fork).  Protocol: ("run", first, count) -> seconds."""
+    try:
+        os.sched_setaffinity(0, os.sched_getaffinity(0))
+    except Exception:
+        pass
+    from oracle.oracle import Oracle
+    orc = Oracle(path=lib_path)   # reference release flags: -Ofast -march=native (CMakeLists.txt:43)
+    vo = orc.vo_create(K, LEVELS, CULLS)
+    vo.odometrize(frames[0], d0, s0)
+    conn.send("ready")
+    while True:
+        msg = conn.recv()
+        if msg[0] == "quit":
+            break
+        _, first, count = msg
+        t0 = time.perf_counter()
+        for i in range(first, first + count):
+            vo.odometrize(frames[i])
+        conn.send(time.perf_counter() - t0)
+
+
+class CpuArm:
+    """cores worker processes, each running the CPU VO on its own synthetic sequence."""
+
+    def __init__(self, frames, K, d0, s0):
+        # frames: [cores][n][h][w]
+        self.cores = frames.shape[0]
+        ctx = mp.get_context("fork")
+        lib_path = _build_cpu_lib()
+        self.kind = "port"   # oracle/dvo_oracle.c; "reference" once oracle/_ref is wired in
+        self.pipes = []; self.procs = []
+        for c in range(self.cores):
+            a, b = ctx.Pipe()
+            p = ctx.Process(target=_cpu_worker, args=(b, frames[c], K, d0[c], s0[c], lib_path), daemon=True)
+            p.start()
+            self.pipes.append(a); self.procs.append(p)
+        for a in self.pipes:
+            assert a.recv() == "ready"
+
+    def step(self, first, count):
+        """every worker processes frames [first, first+count) of its sequence; returns wall seconds"""
+        t0 = time.perf_counter()
+        for a in self.pipes:
+            a.send(("run", first, count))
+        for a in self.pipes:
+            a.recv()
+        return time.perf_counter() - t0
+
+    def close(self):
+        for a in self.pipes:
+            try:
+                a.send(("quit",))
+            except Exception:
+                pass
+        for p in self.procs:
+            p.join(timeout=5)
+
+
+# ------------------------------------------------------------------------------------------------
+# inputs
+# ------------------------------------------------------------------------------------------------
+def default_K():
+    return np.array([[0.82 * W_IN, 0, 0.5 * W_IN - 0.5], [0, 0.82 * W_IN, 0.5 * H_IN - 0.5], [0, 0, 1]], np.float32)
+
+
+def depth_prior(n_streams, seed):
+    """Scene's ctor prior (frame.hpp:18-21): max(randn(1.5, 0.5), 0.5), sigma 0.5 — supplied as an
+    input to both arms, one independent draw per stream."""
+    rng = np.random.default_rng(seed)
+    h, w = H_IN >> CULLS, W_IN >> CULLS
+    d = np.maximum(rng.normal(1.5, 0.5, size=(n_streams, h, w)), 0.5).astype(np.float32)
+    return d, np.full_like(d, 0.5)
+
+
+def render_host_frames(n_streams, n_frames, seed0):
+    """[n_streams][n_frames][h][w] float32 frames for the CPU arm: rendered by the device renderer
+    when a GPU is present (input generation only), else by the numpy renderer."""
+    import dvo_b200
+    out = np.empty((n_streams, n_frames, H_IN, W_IN), np.float32)
+    lib = dvo_b200.load_library()
+    if lib.dvo_device_count() > 0:
+        dv = dvo_b200.Dvo(lib=lib, n_streams=n_streams, width=W_IN, height=H_IN, levels=LEVELS, culls=CULLS, K=default_K(),
+                          max_frames=2, max_keyframes=1)
+        buf = dv.dev_alloc(n_streams * H_IN * W_IN * 4)
+        tmp = np.empty((n_streams, H_IN, W_IN), np.float32)
+        for i in range(n_frames):
+            dv.synth_render_dev(buf, None, i, seed0, TRANS_STEP, ROT_STEP_DEG)
+            dv.copy_to_host(tmp, buf)
+            out[:, i] = tmp
+        dv.dev_free(buf)
+        dv.close()
+        return out, "device renderer"
+    from dvo_b200 import synth
+    for s in range(n_streams):
+        g, _, _, _ = synth.sequence(n_frames, W_IN, H_IN, K=default_K(), seed=seed0 + s, trans_step=TRANS_STEP, rot_step_deg=ROT_STEP_DEG)
+        out[s] = g
+    return out, "numpy renderer"
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def run_cpu_arm(steps, warmup, frames_per_step, cores=None):
+    """Times the CPU VO: every step, each of `cores` workers pushes frames_per_step frames of its own
+    sequence.  Returns (frames_per_s, ms_per_step, info)."""
+    cores = cores or host_cores()
+    n_frames = 1 + (steps + warmup) * frames_per_step
+    frames, how = render_host_frames(cores, n_frames, seed0=900000)
+    d0, s0 = depth_prior(cores, seed=4321)
+    arm = CpuArm(frames, default_K(), d0, s0)
+    pos = 1
+    for _ in range(warmup):
+        arm.step(pos, frames_per_step); pos += frames_per_step
+    t = 0.0
+    for _ in range(steps):
+        t += arm.step(pos, frames_per_step); pos += frames_per_step
+    arm.close()
+    total = cores * frames_per_step * steps
+    info = dict(kind=arm.kind, cores=cores,
+                sample="%d sequences x %d frames of the 640x480 workload (one per core, %s), %d frames per step" % (
+                    cores, steps * frames_per_step, how, cores * frames_per_step))
+    return total / t, 1e3 * t / steps, info
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def peak_hbm():
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def run_gpu_arm(args, rank, world, local_rank, dist):
+    import dvo_b200
+    lib = dvo_b200.load_library()
+    if lib.dvo_device_count() <= 0:
+        raise SystemExit("bench.py: no CUDA device — libdvo_cuda has no CPU fallback")
+    lib.dvo_set_device(local_rank)
+    S, K_, W_ = args.streams, args.steps, args.warmup
+    E = min(args.e2e_steps, K_)           # end-to-end steps (host frames)
+    R = args.roofline_steps               # extra pass with events around every GN launch
+    n_total = 1 + W_ + K_ + R             # frames pushed from HBM; frame 0 = first keyframe
+    # Resident frames: the camera path is traversed forwards then backwards (still one continuous
+    # motion), so a bounded set of distinct frames serves any number of steps.
+    n_dev_frames = min(n_total, args.resident_frames)
+    dv = dvo_b200.Dvo(lib=lib, n_streams=S, width=W_IN, height=H_IN, levels=LEVELS, culls=CULLS, K=default_K(), max_frames=2,
+                      max_keyframes=n_total + W_ + E + 4)
+    dv.vo_reserve(n_total + W_ + E + 2)
+    frame_bytes = S * H_IN * W_IN * 4
+    seed0 = 1000 + rank * S
+    # --- inputs: rendered on device, resident in HBM before the timed region starts
+    dev = dv.dev_alloc(frame_bytes * n_dev_frames)
+    for i in range(n_dev_frames):
+        dv.synth_render_dev(dev + i * frame_bytes, None, i, seed0, TRANS_STEP, ROT_STEP_DEG)
+    # host frames for the end-to-end pass: the frames that follow, in pinned memory
+    import ctypes as C
+    host = []
+    # the e2e pass continues the motion from wherever the ping-pong traversal stops
+    period = 2 * (n_dev_frames - 1)
+    jl = (n_total - 1) % period if period else 0
+    last = jl if jl < n_dev_frames else period - jl
+    e2e_first = last + 1
+    tmpd = dv.dev_alloc(frame_bytes)
+    for i in range(W_ + E):
+        hp = lib.dvo_host_alloc(frame_bytes)
+        if not hp:
+            raise SystemExit("bench.py: pinned host allocation failed")
+        arr = np.ctypeslib.as_array(C.cast(hp, C.POINTER(C.c_float)), shape=(S, H_IN, W_IN))
+        dv.synth_render_dev(tmpd, None, e2e_first + i, seed0, TRANS_STEP, ROT_STEP_DEG)
+        dv.copy_to_host(arr, tmpd)
+        host.append((hp, arr))
+    dv.dev_free(tmpd)
+    d0, s0 = depth_prior(S, seed=4321 + rank)
+    dv.sync()
+
+    def barrier():
+        dv.sync()
+        if dist is not None:
+            dist.barrier()
+
+    def maxrank(x):
+        if dist is None:
+            return x
+        import torch
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # --- first keyframe + warm-up
+    def fptr(i):  # ping-pong over the resident frames
+        period = 2 * (n_dev_frames - 1)
+        j = i % period if period else 0
+        return dev + (j if j < n_dev_frames else period - j) * frame_bytes
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    dv.vo_push_dev(dev, d0, s0)
+    f = 1
+    for _ in range(W_):
+        dv.vo_push_dev(fptr(f)); f += 1
+    c0 = dv.vo_counters()
+    # --- timed: K steps, inputs resident in HBM, CUDA events on the library's stream
+    barrier()
+    l0 = dv.launch_count()
+    dv.timer_start()
+    for _ in range(K_):
+        dv.vo_push_dev(fptr(f)); f += 1
+    ms = dv.timer_stop()
+    l1 = dv.launch_count()
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms = maxrank(ms)
+    c1 = dv.vo_counters()
+    if dv.vo_error() != 0:
+        raise SystemExit("bench.py: device-side VO error")
+    gn_iters = int((c1["gn_iters"] - c0["gn_iters"]).sum())
+    n_prop = int((c1["n_propagate"] - c0["n_propagate"]).sum()); n_upd = int((c1["n_update"] - c0["n_update"]).sum())
+    # --- roofline pass: events around every Gauss-Newton launch (perturbs the step, so it is separate)
+    dv.gn_timing(True)
+    for _ in range(R):
+        dv.vo_push_dev(fptr(f)); f += 1
+    gn_ms, gn_launches = dv.gn_timing(False)
+    c2 = dv.vo_counters()
+    gn_px = int((c2["gn_pixels"] - c1["gn_pixels"]).sum())
+    # --- end-to-end: host frames through dvo_vo_push, H2D of the input and D2H of the poses inside
+    T = np.empty((S, 4, 4), np.float32)
+    Tp = T.ctypes.data_as(C.POINTER(C.c_float))
+    for i in range(W_):
+        dv._ck(lib.dvo_vo_push(dv.ctx, host[i][0], None, None, Tp))
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(W_, W_ + E):
+        dv._ck(lib.dvo_vo_push(dv.ctx, host[i][0], None, None, Tp))
+    dv.sync()
+    e2e_s = maxrank(time.perf_counter() - t0)
+    barrier()
+    for hp, _ in host:
+        lib.dvo_host_free(hp)
+    dv.dev_free(dev)
+    dv.close()
+    peak, peak_src = peak_hbm()
+    gn_gbs = (GN_BYTES_PER_PX * gn_px / (gn_ms * 1e-3) / 1e9) if gn_ms > 0 else 0.0
+    res = dict(
+        value=world * S * K_ / (ms * 1e-3), ms_per_step=ms / K_,
+        e2e=dict(value=world * S * E / e2e_s, unit="frames/s", h2d_bytes_per_step=frame_bytes, d2h_bytes_per_step=S * 64, steps=E),
+        gpu_launches=int(l1 - l0), clocks=clocks,
+        roofline=dict(kernel="k_gn_step (fused warp + residual + Jacobian + 6x6 reduction, one launch per GN iteration)",
+                      bound="hbm", achieved=gn_gbs, peak=peak, unit="GB/s", frac=gn_gbs / peak, traffic=None, peak_source=peak_src,
+                      launches=gn_launches, avg_launch_us=(1e3 * gn_ms / gn_launches) if gn_launches else None,
+                      algorithmic_bytes_per_launch=(GN_BYTES_PER_PX * gn_px / gn_launches) if gn_launches else None),
+        gn_iters_per_s=world * gn_iters / (ms * 1e-3), gn_iters_per_frame=gn_iters / float(S * K_),
+        frames_propagate=n_prop, frames_update=n_upd)
+    return res
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--streams", type=int, default=256, help="independent sequences per GPU")
+    ap.add_argument("--e2e-steps", type=int, default=8)
+    ap.add_argument("--roofline-steps", type=int, default=4)
+    ap.add_argument("--resident-frames", type=int, default=48, help="distinct frames per stream kept in HBM")
+    ap.add_argument("--cpu-frames-per-step", type=int, default=2)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else max(args.warmup, 1)
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    config = dict(workload="C5/configs[1]: %d independent synthetic 640x480 sequences per GPU, full VO loop (track + propagate|update + "
+                           "regularize), Frame(gray,K,levels=3,culls=2), random depth prior (frame.hpp:18-21)" % args.streams,
+                  streams_per_gpu=args.streams, width=W_IN, height=H_IN, levels=LEVELS, culls=CULLS,
+                  l2="each step reads a new %.0f MB input batch (> 126 MB L2); no explicit flush" % (args.streams * W_IN * H_IN * 4 / 1e6))
+    base = dict(metric="VO frames/sec (track+map) at 640x480", unit="frames/s", n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
+                higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32", data="synthetic", config=config)
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        fps, ms_step, info = run_cpu_arm(args.steps, args.warmup, args.cpu_frames_per_step)
+        info["value"] = fps
+        line = dict(base, impl="reference", value=fps, ms_per_step=ms_step, cpu_baseline=info, gpu_launches=0,
+                    e2e=dict(value=fps, unit="frames/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
+        print(json.dumps(line), flush=True)
+        return
+
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as td
+        torch.cuda.set_device(local_rank)
+        td.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        dist = td
+    res = run_gpu_arm(args, rank, world, local_rank, dist)
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        fps, ms_step, info = run_cpu_arm(steps=12, warmup=1, frames_per_step=args.cpu_frames_per_step)
+        info["value"] = fps; info["unit"] = "frames/s"
+        cpu = info
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        line = dict(base, impl="b200", **res)
+        line["cpu_baseline"] = cpu
+        print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -2,6 +2,7 @@
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false -lineinfo -O3 -shared
 // No CPU fallback: every entry point needs a CUDA device.
 #include "dvo_kernels.cuh"
+#include "dvo_synth.cuh"
 
 #include <cmath>
 #include <cstdio>
@@ -88,6 +89,14 @@ struct dvo_ctx {
     } while (0)
 
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+extern "C" int dvo_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+extern "C" int dvo_set_device(int device) { return cudaSetDevice(device) == cudaSuccess ? DVO_OK : DVO_ERR_CUDA; }
 
 extern "C" void dvo_params_default(dvo_params* p)
 {
@@ -742,6 +751,7 @@ __global__ void k_vo_reset(Consts c, VoState* vo, MapState* mst)
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= c.S) return;
     vo[s].kf_slot = -1; vo[s].kf_frame_id = -1; vo[s].n_kf = 0; vo[s].need_new = 0; vo[s].was_keyframe = 0; vo[s].n_iters = 0; vo[s].cur_slot = c.vo_base;
+    vo[s].gn_iters = 0; vo[s].gn_pixels = 0; vo[s].n_propagate = 0; vo[s].n_update = 0;
     mst[s].rng_pos = 0; mst[s].err = 0; mst[s].valid_update = 0; mst[s].ticket = 0;
 }
 
@@ -753,6 +763,21 @@ extern "C" int dvo_vo_reset(dvo_ctx* ctx)
     ctx->forced_pending = false;
     k_vo_reset<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_vo, ctx->d_ms);
     KCHECK();
+    return DVO_OK;
+}
+
+extern "C" int dvo_vo_reserve(dvo_ctx* ctx, int n_keyframes)
+{
+    const Consts& c = ctx->c;
+    ARG(n_keyframes >= 0, "bad argument");
+    const int need = n_keyframes < c.max_kf ? n_keyframes : c.max_kf;
+    for (int k = 0; k <= need; k++) {
+        if (!ctx->slots[c.vo_base + k].base) {
+            int rc = alloc_slot(ctx, c.vo_base + k);
+            if (rc) return rc;
+        }
+    }
+    CK(cudaStreamSynchronize(ctx->stream));
     return DVO_OK;
 }
 
@@ -852,6 +877,21 @@ extern "C" int dvo_vo_state(dvo_ctx* ctx, float* xi, float* rel_xi, int* was_key
     return DVO_OK;
 }
 
+extern "C" int dvo_vo_counters(dvo_ctx* ctx, uint64_t* gn_iters, uint64_t* gn_pixels, uint64_t* n_propagate, uint64_t* n_update)
+{
+    const Consts& c = ctx->c;
+    std::vector<VoState> hv(c.S);
+    CK(cudaMemcpyAsync(hv.data(), ctx->d_vo, sizeof(VoState) * (size_t)c.S, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (int s = 0; s < c.S; s++) {
+        if (gn_iters) gn_iters[s] = hv[s].gn_iters;
+        if (gn_pixels) gn_pixels[s] = hv[s].gn_pixels;
+        if (n_propagate) n_propagate[s] = hv[s].n_propagate;
+        if (n_update) n_update[s] = hv[s].n_update;
+    }
+    return DVO_OK;
+}
+
 extern "C" int dvo_vo_last_log(dvo_ctx* ctx, dvo_iter_log* log, int log_cap, int* n_iters)
 {
     const Consts& c = ctx->c;
@@ -889,6 +929,41 @@ extern "C" int dvo_vo_last_slot(dvo_ctx* ctx, int stream, int* slot)
     return DVO_OK;
 }
 extern "C" int dvo_vo_error(dvo_ctx* ctx) { return map_error(ctx); }
+
+// ---- synthetic inputs -----------------------------------------------------------------------
+extern "C" int dvo_synth_render_dev(dvo_ctx* ctx, float* gray_dev, float* depth_dev, int frame, uint64_t seed0, float trans_step,
+                                    float rot_step_deg)
+{
+    ARG(gray_dev && frame >= 0, "bad argument");
+    const Consts& c = ctx->c;
+    SynthParams P;
+    P.w = c.in_w; P.h = c.in_h;
+    P.fx = ctx->P.K[0]; P.fy = ctx->P.K[4]; P.cx = ctx->P.K[2]; P.cy = ctx->P.K[5];
+    P.seed0 = seed0; P.trans_step = trans_step; P.rot_step = rot_step_deg * 0.017453292519943295f; P.frame = frame;
+    dim3 grid(cdiv(P.w * P.h, 256), c.S);
+    k_synth_render<<<grid, 256, 0, ctx->stream>>>(P, gray_dev, depth_dev);
+    KCHECK();
+    return DVO_OK;
+}
+extern "C" void* dvo_dev_alloc(size_t bytes)
+{
+    void* p = nullptr;
+    if (cudaMalloc(&p, bytes) != cudaSuccess) return nullptr;
+    return p;
+}
+extern "C" void dvo_dev_free(void* p) { if (p) cudaFree(p); }
+extern "C" int dvo_copy_to_host(dvo_ctx* ctx, void* host, const void* dev, size_t bytes)
+{
+    CK(cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return DVO_OK;
+}
+extern "C" int dvo_copy_to_dev(dvo_ctx* ctx, void* dev, const void* host, size_t bytes)
+{
+    CK(cudaMemcpyAsync(dev, host, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return DVO_OK;
+}
 
 // ---- measurement ----------------------------------------------------------------------------
 extern "C" int dvo_timer_start(dvo_ctx* ctx)

@@ -49,7 +49,7 @@ struct TrackState {
     float Tn[12];        // exp(-xi), rows of [R|t]
     double stop_update;
     float stop_residual;
-    int pad;
+    int px_total; // pixels swept by this track (sum of level sizes over iterations)
     const float* obj_gray[MAXL]; // pre-offset by stream
     const float4* ref_tex[MAXL];
     const float2* ref_ds[MAXL];
@@ -79,6 +79,9 @@ struct VoState {
     int n_iters;
     int cur_slot; // slot holding this stream's current frame: vo_base + n_kf (see k_vo_begin)
     int pad;
+    unsigned long long gn_iters;  // Gauss-Newton iterations since dvo_vo_reset
+    unsigned long long gn_pixels; // pixels swept by those iterations (sum of level sizes)
+    unsigned long long n_propagate, n_update; // frames mapped by propagate / update
 };
 
 struct PoseTab { // per (stream, age): exp(-r_xi) and -r_xi[0:3] (src/map/mapper.cpp:107, implement.cpp:56-58,193)

@@ -433,6 +433,7 @@ __global__ void __launch_bounds__(GN_THREADS) k_gn_step(const __grid_constant__ 
         for (int q = 0; q < 6; q++) { L->update[q] = upd[q]; L->xi_after[q] = xi[q]; }
     }
     st->n_total = n_total + 1;
+    st->px_total += g.n;
     st->ticket = 0;
     if (!advance_pose) {
         st->done = 1;
@@ -479,7 +480,7 @@ __global__ void k_track_init(const __grid_constant__ Consts c, TrackState* st, c
     float Tn[12];
     se3_exp_neg12(xi, Tn);
     for (int q = 0; q < 12; q++) t->Tn[q] = Tn[q];
-    t->level = level; t->iter = 0; t->n_total = 0; t->mode = mode; t->ticket = 0;
+    t->level = level; t->iter = 0; t->n_total = 0; t->px_total = 0; t->mode = mode; t->ticket = 0;
     t->done = (vo && rs < 0) ? 1 : 0;
     t->stop_update = stop_update; t->stop_residual = stop_residual;
 }
@@ -887,10 +888,13 @@ __global__ void k_vo_decide(const __grid_constant__ Consts c, const SlotDev* __r
     se3_concatenate(kxi, rel, xi);
     for (int q = 0; q < 6; q++) { cur.xi[6 * s + q] = xi[q]; cur.rel_xi[6 * s + q] = rel[q]; }
     v->n_iters = ts[s].n_total;
+    v->gn_iters += (unsigned long long)ts[s].n_total;
+    v->gn_pixels += (unsigned long long)ts[s].px_total;
     bool need = false;
     if (norm_n(rel, 3) > (double)c.min_movement) need = true;       // mapper.cpp:48-52
     else if (frame_id - v->kf_frame_id >= c.max_forward) need = true; // mapper.cpp:53-56
     v->need_new = need ? 1 : 0;
+    if (need) v->n_propagate++; else v->n_update++;
     v->was_keyframe = need ? 1 : 0;
     m->ref_slot = v->kf_slot; m->obj_slot = cur_slot; m->new_slot = cur_slot;
     m->n_hist = v->n_kf;

@@ -39,12 +39,13 @@ class DvoIterLog(C.Structure):
 
 
 EXPORTS = [
-    "dvo_params_default", "dvo_create", "dvo_destroy", "dvo_last_error", "dvo_sync", "dvo_level_size", "dvo_level_K",
+    "dvo_device_count", "dvo_set_device", "dvo_params_default", "dvo_create", "dvo_destroy", "dvo_last_error", "dvo_sync", "dvo_level_size", "dvo_level_K",
     "dvo_host_alloc", "dvo_host_free", "dvo_frame_create", "dvo_frame_create_dev", "dvo_frame_release",
     "dvo_frame_set_depth", "dvo_frame_download", "dvo_frame_set_xi", "dvo_frame_get_xi", "dvo_warp_image",
     "dvo_gn_step", "dvo_track", "dvo_map_propagate", "dvo_map_update", "dvo_map_regularize", "dvo_rng_position",
-    "dvo_mask_compact", "dvo_vo_reset", "dvo_vo_force_pose", "dvo_vo_push", "dvo_vo_push_dev", "dvo_vo_state", "dvo_vo_ref_slot",
-    "dvo_vo_last_slot", "dvo_vo_last_log", "dvo_vo_error", "dvo_timer_start", "dvo_timer_stop", "dvo_launch_count", "dvo_gn_timing",
+    "dvo_mask_compact", "dvo_vo_reset", "dvo_vo_reserve", "dvo_vo_force_pose", "dvo_vo_push", "dvo_vo_push_dev", "dvo_vo_state", "dvo_vo_ref_slot",
+    "dvo_vo_last_slot", "dvo_vo_last_log", "dvo_vo_counters", "dvo_vo_error", "dvo_synth_render_dev", "dvo_dev_alloc", "dvo_dev_free",
+    "dvo_copy_to_host", "dvo_copy_to_dev", "dvo_timer_start", "dvo_timer_stop", "dvo_launch_count", "dvo_gn_timing",
 ]
 
 
@@ -56,6 +57,7 @@ def load_library(path=None):
     lib = C.CDLL(path)
     lib.dvo_last_error.restype = C.c_char_p
     lib.dvo_last_error.argtypes = [C.c_void_p]
+    lib.dvo_set_device.argtypes = [C.c_int]
     lib.dvo_create.argtypes = [C.POINTER(C.c_void_p), C.POINTER(DvoParams)]
     lib.dvo_destroy.argtypes = [C.c_void_p]
     lib.dvo_sync.argtypes = [C.c_void_p]
@@ -81,6 +83,7 @@ def load_library(path=None):
     lib.dvo_rng_position.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
     lib.dvo_mask_compact.argtypes = [C.c_void_p, U8P, C.c_int, I32P, I32P]
     lib.dvo_vo_reset.argtypes = [C.c_void_p]
+    lib.dvo_vo_reserve.argtypes = [C.c_void_p, C.c_int]
     lib.dvo_vo_push.argtypes = [C.c_void_p, C.c_void_p, F32P, F32P, F32P]
     lib.dvo_vo_push_dev.argtypes = [C.c_void_p, C.c_void_p, F32P, F32P, F32P]
     lib.dvo_vo_state.argtypes = [C.c_void_p, F32P, F32P, I32P, I32P, I32P, I32P]
@@ -88,7 +91,15 @@ def load_library(path=None):
     lib.dvo_vo_last_slot.argtypes = [C.c_void_p, C.c_int, I32P]
     lib.dvo_vo_force_pose.argtypes = [C.c_void_p, F32P]
     lib.dvo_vo_error.argtypes = [C.c_void_p]
+    U64P = C.POINTER(C.c_uint64)
+    lib.dvo_vo_counters.argtypes = [C.c_void_p, U64P, U64P, U64P, U64P]
     lib.dvo_vo_last_log.argtypes = [C.c_void_p, C.POINTER(DvoIterLog), C.c_int, I32P]
+    lib.dvo_synth_render_dev.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_uint64, C.c_float, C.c_float]
+    lib.dvo_dev_alloc.restype = C.c_void_p
+    lib.dvo_dev_alloc.argtypes = [C.c_size_t]
+    lib.dvo_dev_free.argtypes = [C.c_void_p]
+    lib.dvo_copy_to_host.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
+    lib.dvo_copy_to_dev.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
     lib.dvo_timer_start.argtypes = [C.c_void_p]
     lib.dvo_timer_stop.argtypes = [C.c_void_p, F32P]
     lib.dvo_launch_count.restype = C.c_uint64
@@ -273,6 +284,9 @@ class Dvo:
     def vo_reset(self):
         self._ck(self.lib.dvo_vo_reset(self.ctx))
 
+    def vo_reserve(self, n_keyframes):
+        self._ck(self.lib.dvo_vo_reserve(self.ctx, n_keyframes))
+
     def vo_push(self, gray, init_depth=None, init_sigma=None, want_pose=True):
         g = self._stack(gray, self.params.height, self.params.width)
         w, h = self.level_size(self.L - 1)
@@ -317,8 +331,42 @@ class Dvo:
                       xi_after=np.array(log[s * cap + k].xi_after[:], np.float32)) for k in range(int(n[s]))]
                 for s in range(self.S)]
 
+    def vo_counters(self):
+        arrs = [np.zeros(self.S, np.uint64) for _ in range(4)]
+        self._ck(self.lib.dvo_vo_counters(self.ctx, *[a.ctypes.data_as(C.POINTER(C.c_uint64)) for a in arrs]))
+        return dict(gn_iters=arrs[0], gn_pixels=arrs[1], n_propagate=arrs[2], n_update=arrs[3])
+
     def vo_error(self):
         return self.lib.dvo_vo_error(self.ctx)
+
+    # ---- synthetic inputs / resident device buffers
+    def dev_alloc(self, nbytes):
+        p = self.lib.dvo_dev_alloc(nbytes)
+        if not p:
+            raise DvoError("dvo_dev_alloc(%d) failed" % nbytes)
+        return p
+
+    def dev_free(self, p):
+        self.lib.dvo_dev_free(p)
+
+    def synth_render_dev(self, gray_dev, depth_dev, frame, seed0=1, trans_step=0.004, rot_step_deg=0.15):
+        self._ck(self.lib.dvo_synth_render_dev(self.ctx, gray_dev, depth_dev, frame, seed0, trans_step, rot_step_deg))
+
+    def copy_to_host(self, arr, dev_ptr):
+        self._ck(self.lib.dvo_copy_to_host(self.ctx, arr.ctypes.data_as(C.c_void_p), dev_ptr, arr.nbytes))
+        return arr
+
+    def copy_to_dev(self, dev_ptr, arr):
+        arr = np.ascontiguousarray(arr)
+        self._ck(self.lib.dvo_copy_to_dev(self.ctx, dev_ptr, arr.ctypes.data_as(C.c_void_p), arr.nbytes))
+
+    def vo_push_dev(self, gray_dev, init_depth=None, init_sigma=None, want_pose=False):
+        w, h = self.level_size(self.L - 1)
+        d = self._stack(init_depth, h, w) if init_depth is not None else None
+        s = self._stack(init_sigma, h, w) if init_sigma is not None else None
+        T = np.empty((self.S, 4, 4), np.float32) if want_pose else None
+        self._ck(self.lib.dvo_vo_push_dev(self.ctx, gray_dev, _p(d), _p(s), _p(T)))
+        return T
 
     # ---- measurement
     def sync(self):

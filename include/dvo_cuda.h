@@ -81,6 +81,8 @@ typedef enum dvo_image_kind {
 } dvo_image_kind;
 
 /* ---- context ------------------------------------------------------------------------------ */
+int dvo_device_count(void);
+int dvo_set_device(int device); /* cudaSetDevice for the calling thread; call before dvo_create */
 void dvo_params_default(dvo_params* p); /* geometry 640x480, levels 3, culls 2, n_streams 1 */
 int dvo_create(dvo_ctx** out, const dvo_params* p);
 void dvo_destroy(dvo_ctx* ctx);
@@ -144,6 +146,9 @@ int dvo_mask_compact(dvo_ctx* ctx, const uint8_t* mask, int n, int32_t* idx, int
 
 /* ---- full VO: System::VisualOdometry (include/system/system.hpp:12-104) --------------------- */
 int dvo_vo_reset(dvo_ctx* ctx);
+/* Pre-allocate the keyframe pool for n_keyframes keyframes per stream (otherwise entries are
+ * allocated on first need inside dvo_vo_push, which synchronises the device). */
+int dvo_vo_reserve(dvo_ctx* ctx, int n_keyframes);
 /* VisualOdometry::odometrize(gray) (system.hpp:44-74) for every stream; the whole frame (pyramid,
  * <= levels*15 GN iterations, keyframe decision, propagate | update, regularize) is enqueued
  * without host synchronisation.  init_depth/init_sigma ([n_streams][h_top][w_top], nullable
@@ -160,6 +165,10 @@ int dvo_vo_force_pose(dvo_ctx* ctx, const float* rel_xi);
 /* per-stream state of the last pushed frame */
 int dvo_vo_state(dvo_ctx* ctx, float* xi /*[S][6]*/, float* rel_xi /*[S][6]*/, int* was_keyframe /*[S]*/,
                  int* n_keyframes /*[S]*/, int* valid_updates /*[S]*/, int* n_iters /*[S]*/);
+/* cumulative per-stream work counters since dvo_vo_reset (any pointer may be NULL), [n_streams] each:
+ * Gauss-Newton iterations, pixels swept by them (sum of level sizes), frames mapped by
+ * Mapper::propagate and by Mapper::update. */
+int dvo_vo_counters(dvo_ctx* ctx, uint64_t* gn_iters, uint64_t* gn_pixels, uint64_t* n_propagate, uint64_t* n_update);
 /* Gauss-Newton iteration records of the last pushed frame's tracking (what Tracker::track prints,
  * src/track/tracker.cpp:56-61).  log: [n_streams][log_cap]; n_iters: [n_streams]. */
 int dvo_vo_last_log(dvo_ctx* ctx, dvo_iter_log* log, int log_cap, int* n_iters);
@@ -168,6 +177,18 @@ int dvo_vo_ref_slot(dvo_ctx* ctx, int stream, int* slot);
 int dvo_vo_last_slot(dvo_ctx* ctx, int stream, int* slot);
 /* first error flagged on device by any stream (history overflow, rng exhaustion), 0 if none */
 int dvo_vo_error(dvo_ctx* ctx);
+
+/* ---- synthetic inputs (no reference counterpart: the reference reads PNGs) ---- */
+/* Renders frame `frame` of n_streams synthetic sequences (analytic textured box room, smooth 6-DoF
+ * trajectory; stream s uses seed0 + s) at the context's input size and intrinsics, on device.
+ * gray_dev: [n_streams][height][width] device floats in [0,1]; depth_dev (nullable): ground-truth z. */
+int dvo_synth_render_dev(dvo_ctx* ctx, float* gray_dev, float* depth_dev, int frame, uint64_t seed0, float trans_step,
+                         float rot_step_deg);
+/* plain device memory for inputs that stay resident (benchmarks), and copies on the context's stream */
+void* dvo_dev_alloc(size_t bytes);
+void dvo_dev_free(void* p);
+int dvo_copy_to_host(dvo_ctx* ctx, void* host, const void* dev, size_t bytes);   /* synchronises */
+int dvo_copy_to_dev(dvo_ctx* ctx, void* dev, const void* host, size_t bytes);    /* synchronises */
 
 /* ---- measurement helpers (CUDA events on the context's stream) -------------------------------- */
 int dvo_timer_start(dvo_ctx* ctx);

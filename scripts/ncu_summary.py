@@ -1,0 +1,48 @@
+#!/usr/bin/env python
+"""Summaries of ncu output for profiles/ (run here, no GPU needed).
+  launches <launches.csv>            per-kernel count / total / average / share of device time
+  full <prof.ncu-rep>                selected raw metrics per profiled launch
+"""
+import collections
+import csv
+import io
+import subprocess
+import sys
+
+KEYS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "lts__t_bytes.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+        "sm__throughput.avg.pct_of_peak_sustained_elapsed", "l1tex__throughput.avg.pct_of_peak_sustained_elapsed", "lts__throughput.avg.pct_of_peak_sustained_elapsed",
+        "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread", "launch__grid_size", "launch__block_size",
+        "launch__occupancy_limit_registers", "smsp__inst_executed.sum", "sm__inst_executed_pipe_fp64.sum", "smsp__warp_issue_stalled_long_scoreboard_per_warp_active.pct",
+        "smsp__cycles_active.avg", "l1tex__t_sector_hit_rate.pct", "lts__t_sector_hit_rate.pct"]
+
+
+def launches(path):
+    lines = [l for l in open(path) if not l.startswith("==")]
+    agg = collections.OrderedDict()
+    for row in csv.DictReader(lines):
+        k = row["Kernel Name"].split("(")[0]
+        v = float(row["Metric Value"].replace(",", ""))
+        a = agg.setdefault(k, [0, 0.0, 0.0])
+        a[0] += 1; a[1] += v; a[2] = max(a[2], v)
+    tot = sum(a[1] for a in agg.values())
+    print("%-28s %7s %12s %10s %10s %7s" % ("kernel", "count", "total_us", "avg_us", "max_us", "share"))
+    for k, (n, t, m) in sorted(agg.items(), key=lambda x: -x[1][1]):
+        print("%-28s %7d %12.1f %10.2f %10.2f %6.1f%%" % (k[:28], n, t / 1e3, t / n / 1e3, m / 1e3, 100 * t / tot))
+    print("total device time of the %d captured launches: %.1f us" % (sum(a[0] for a in agg.values()), tot / 1e3))
+
+
+def full(path):
+    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(out)))
+    hdr = rows[0]
+    idx = {h: i for i, h in enumerate(hdr)}
+    name_i = idx.get("Kernel Name")
+    for r in rows[2:]:
+        print("== %s  (ID %s)" % (r[name_i].split("(")[0], r[0]))
+        for k in KEYS:
+            if k in idx:
+                print("   %-70s %s %s" % (k, r[idx[k]], rows[1][idx[k]]))
+
+
+if __name__ == "__main__":
+    {"launches": launches, "full": full}[sys.argv[1]](sys.argv[2])
