@@ -189,12 +189,18 @@ __device__ inline void se3_exp(const float* xi, float* T)
         float d = wl * wl * wl;
         float w_hat2[9], V[9];
         mat3_mul(w_hat, w_hat, w_hat2);
+        // `eye + w_hat*a/b + (w_hat*w_hat)*c/d` is a lazy cv::MatExpr in the reference: `/ s` folds
+        // 1.0/s into a double alpha, the first sum is cv::scaleAdd, the scaled product is cv::gemm's
+        // (float)(t*alpha) in double, the last sum cv::add (oracle/shim/opencv2/opencv.hpp "MatExpr").
+        const double alpha1 = __dmul_rn((double)a, __ddiv_rn(1.0, (double)b));
+        const double alpha2 = __dmul_rn((double)c, __ddiv_rn(1.0, (double)d));
+        const float alpha1f = (float)alpha1;
 #pragma unroll
         for (int k = 0; k < 9; k++) {
             float eye = (k == 0 || k == 4 || k == 8) ? 1.0f : 0.0f;
-            float e1 = (w_hat[k] * a) / b;
-            float e2 = (w_hat2[k] * c) / d;
-            V[k] = (eye + e1) + e2;
+            float m1 = w_hat[k] * alpha1f + eye;
+            float m2 = (float)__dmul_rn((double)w_hat2[k], alpha2);
+            V[k] = m1 + m2;
         }
         mat3_vec(V, v, t);
     } else {
@@ -215,8 +221,9 @@ __device__ inline void so3_log(const float* R, float* w)
     if (wl > 1e-6f) {
         float tmp[3] = {R[7] - R[5], R[2] - R[6], R[3] - R[1]};
         float k = 1.0f / (2.0f * sinf_ref(wl));
+        const float alpha = (float)__dmul_rn((double)k, (double)wl); // lazy MatExpr: k * tmp * wl -> tmp * (float)(k*wl)
 #pragma unroll
-        for (int i = 0; i < 3; i++) w[i] = (k * tmp[i]) * wl;
+        for (int i = 0; i < 3; i++) w[i] = tmp[i] * alpha;
     }
 }
 // se3::log (se3.cpp:101-124)
@@ -235,12 +242,13 @@ __device__ inline void se3_log(const float* T, float* xi)
         float b = wl * wl;
         float w_hat2[9];
         mat3_mul(w_hat, w_hat, w_hat2);
+        const double alpha2 = __dmul_rn((double)k, __ddiv_rn(1.0, (double)b)); // lazy MatExpr, see se3_exp
 #pragma unroll
         for (int i = 0; i < 9; i++) {
             float eye = (i == 0 || i == 4 || i == 8) ? 1.0f : 0.0f;
-            float e1 = 0.5f * w_hat[i];
-            float e2 = (k * w_hat2[i]) / b;
-            V_inv[i] = (eye - e1) + e2;
+            float m1 = w_hat[i] * -0.5f + eye;
+            float m2 = (float)__dmul_rn((double)w_hat2[i], alpha2);
+            V_inv[i] = m1 + m2;
         }
     }
     float v[3];

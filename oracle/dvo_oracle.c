@@ -139,8 +139,11 @@ void orc_so3_log(const float R[9], float w[3])
     float w_length = (float)acos((tr - 1.0f) * 0.5f);
     if (w_length > 1e-6f) {
         float tmp[3] = {R[7] - R[5], R[2] - R[6], R[3] - R[1]};
+        /* `k * tmp * w_length` is a lazy cv::MatExpr: the two scalars fold into one double alpha
+         * (matop.cpp MatOp_AddEx::multiply) applied by convertTo as src * (float)alpha. */
         float k = 1.0f / (2.0f * sinf(w_length));
-        for (int i = 0; i < 3; i++) w[i] = (k * tmp[i]) * w_length;
+        float alpha = (float)((double)k * (double)w_length);
+        for (int i = 0; i < 3; i++) w[i] = tmp[i] * alpha;
     }
 }
 
@@ -162,11 +165,17 @@ void orc_se3_exp(const float xi[6], float T[16])
         float d = w_length * w_length * w_length;
         float w_hat2[9], V[9];
         mat3_mul(w_hat, w_hat, w_hat2);
+        /* eye + w_hat*a/b + (w_hat*w_hat)*c/d as OpenCV evaluates the lazy MatExpr (matop.cpp):
+         * `/ s` multiplies alpha by 1.0/s in double; eye + alpha1*w_hat is cv::scaleAdd
+         * (w_hat*(float)alpha1 + eye); the scaled product is cv::gemm's (float)(t*alpha2) with the
+         * fp32 dot product t promoted to double; the final sum is cv::add. */
+        const double alpha1 = (double)a * (1.0 / (double)b);
+        const double alpha2 = (double)c * (1.0 / (double)d);
         for (int k = 0; k < 9; k++) {
             float eye = (k == 0 || k == 4 || k == 8) ? 1.0f : 0.0f;
-            float e1 = (w_hat[k] * a) / b;
-            float e2 = (w_hat2[k] * c) / d;
-            V[k] = (eye + e1) + e2;
+            float m1 = w_hat[k] * (float)alpha1 + eye;
+            float m2 = (float)((double)w_hat2[k] * alpha2);
+            V[k] = m1 + m2;
         }
         mat3_vec(V, v, t);
     } else {
@@ -194,11 +203,13 @@ void orc_se3_log(const float T[16], float xi[6])
         float b = w_length * w_length;
         float w_hat2[9];
         mat3_mul(w_hat, w_hat, w_hat2);
+        /* eye - 0.5f*w_hat + k*(w_hat*w_hat)/b: scaleAdd(w_hat, -0.5, eye) + gemm(alpha = k*(1/b)) */
+        const double alpha2 = (double)k * (1.0 / (double)b);
         for (int i = 0; i < 9; i++) {
             float eye = (i == 0 || i == 4 || i == 8) ? 1.0f : 0.0f;
-            float e1 = 0.5f * w_hat[i];
-            float e2 = (k * w_hat2[i]) / b;
-            V_inv[i] = (eye - e1) + e2;
+            float m1 = w_hat[i] * -0.5f + eye;
+            float m2 = (float)((double)w_hat2[i] * alpha2);
+            V_inv[i] = m1 + m2;
         }
     }
     float v[3];
@@ -917,11 +928,12 @@ void orc_map_update_pixel(const float* obj_gray, const float* ref_gray, const fl
         mat3_mul(K, R, KR);
         mat3_vec(KR, x_q, KRq);
         mat3_vec(K, t, Kt);
+        /* `s*x_i - (K*R)*x_q` and `t(2)*x_i - K*t` fold into cv::gemm(A, B, -1, x_i, s)
+         * (MatOp_GEMM::subtract): d = (float)(t*alpha + c*beta) evaluated in double. */
         float a[3], b[3];
-        float r3q_f = (float)r3q;
         for (int i = 0; i < 3; i++) {
-            a[i] = r3q_f * x_i[i] - KRq[i];
-            b[i] = t[2] * x_i[i] - Kt[i];
+            a[i] = (float)((double)KRq[i] * -1.0 + (double)x_i[i] * r3q);
+            b[i] = (float)((double)Kt[i] * -1.0 + (double)x_i[i] * (double)t[2]);
         }
         double ab = 0, aa = 0;
         for (int i = 0; i < 3; i++) { ab += (double)a[i] * b[i]; aa += (double)a[i] * a[i]; }
