@@ -191,7 +191,7 @@ __device__ inline void se3_exp(const float* xi, float* T)
         mat3_mul(w_hat, w_hat, w_hat2);
         // `eye + w_hat*a/b + (w_hat*w_hat)*c/d` is a lazy cv::MatExpr in the reference: `/ s` folds
         // 1.0/s into a double alpha, the first sum is cv::scaleAdd, the scaled product is cv::gemm's
-        // (float)(t*alpha) in double, the last sum cv::add (oracle/shim/opencv2/opencv.hpp "MatExpr").
+        // (float)(t*(float)alpha), the last sum cv::add (DESIGN.md "third-party arithmetic").
         const double alpha1 = __dmul_rn((double)a, __ddiv_rn(1.0, (double)b));
         const double alpha2 = __dmul_rn((double)c, __ddiv_rn(1.0, (double)d));
         const float alpha1f = (float)alpha1;
@@ -199,7 +199,7 @@ __device__ inline void se3_exp(const float* xi, float* T)
         for (int k = 0; k < 9; k++) {
             float eye = (k == 0 || k == 4 || k == 8) ? 1.0f : 0.0f;
             float m1 = w_hat[k] * alpha1f + eye;
-            float m2 = (float)__dmul_rn((double)w_hat2[k], alpha2);
+            float m2 = w_hat2[k] * (float)alpha2;
             V[k] = m1 + m2;
         }
         mat3_vec(V, v, t);
@@ -247,7 +247,7 @@ __device__ inline void se3_log(const float* T, float* xi)
         for (int i = 0; i < 9; i++) {
             float eye = (i == 0 || i == 4 || i == 8) ? 1.0f : 0.0f;
             float m1 = w_hat[i] * -0.5f + eye;
-            float m2 = (float)__dmul_rn((double)w_hat2[i], alpha2);
+            float m2 = w_hat2[i] * (float)alpha2;
             V_inv[i] = m1 + m2;
         }
     }

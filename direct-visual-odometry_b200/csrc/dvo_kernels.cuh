@@ -561,8 +561,8 @@ __device__ inline void implement_update(const float* __restrict__ born_gray, con
 #pragma unroll
         for (int i = 0; i < 3; i++) {
             // `s*x_i - (K*R)*x_q`, `t(2)*x_i - K*t`: folded by MatOp_GEMM::subtract into
-            // cv::gemm(A, B, -1, x_i, s) = (float)(t*(-1) + c*s) evaluated in double
-            const float av = (float)__dadd_rn(__dmul_rn((double)KRq[i], -1.0), __dmul_rn((double)xi3[i], r3q));
+            // cv::gemm(A, B, -1, x_i, s) = (float)(t*(-1) + c*(float)s) evaluated in double
+            const float av = (float)__dadd_rn(__dmul_rn((double)KRq[i], -1.0), __dmul_rn((double)xi3[i], (double)(float)r3q));
             const float bv = (float)__dadd_rn(__dmul_rn((double)Kt[i], -1.0), __dmul_rn((double)xi3[i], (double)tneg[2]));
             ab = __dadd_rn(ab, __dmul_rn((double)av, (double)bv));
             aa = __dadd_rn(aa, __dmul_rn((double)av, (double)av));

@@ -167,14 +167,14 @@ void orc_se3_exp(const float xi[6], float T[16])
         mat3_mul(w_hat, w_hat, w_hat2);
         /* eye + w_hat*a/b + (w_hat*w_hat)*c/d as OpenCV evaluates the lazy MatExpr (matop.cpp):
          * `/ s` multiplies alpha by 1.0/s in double; eye + alpha1*w_hat is cv::scaleAdd
-         * (w_hat*(float)alpha1 + eye); the scaled product is cv::gemm's (float)(t*alpha2) with the
-         * fp32 dot product t promoted to double; the final sum is cv::add. */
+         * (w_hat*(float)alpha1 + eye); the scaled product is cv::gemm's (float)(t*(float)alpha2) with
+         * the fp32 dot product t; the final sum is cv::add. */
         const double alpha1 = (double)a * (1.0 / (double)b);
         const double alpha2 = (double)c * (1.0 / (double)d);
         for (int k = 0; k < 9; k++) {
             float eye = (k == 0 || k == 4 || k == 8) ? 1.0f : 0.0f;
             float m1 = w_hat[k] * (float)alpha1 + eye;
-            float m2 = (float)((double)w_hat2[k] * alpha2);
+            float m2 = w_hat2[k] * (float)alpha2; /* gemm: (float)(t * (float)alpha) */
             V[k] = m1 + m2;
         }
         mat3_vec(V, v, t);
@@ -208,7 +208,7 @@ void orc_se3_log(const float T[16], float xi[6])
         for (int i = 0; i < 9; i++) {
             float eye = (i == 0 || i == 4 || i == 8) ? 1.0f : 0.0f;
             float m1 = w_hat[i] * -0.5f + eye;
-            float m2 = (float)((double)w_hat2[i] * alpha2);
+            float m2 = w_hat2[i] * (float)alpha2;
             V_inv[i] = m1 + m2;
         }
     }
@@ -929,10 +929,10 @@ void orc_map_update_pixel(const float* obj_gray, const float* ref_gray, const fl
         mat3_vec(KR, x_q, KRq);
         mat3_vec(K, t, Kt);
         /* `s*x_i - (K*R)*x_q` and `t(2)*x_i - K*t` fold into cv::gemm(A, B, -1, x_i, s)
-         * (MatOp_GEMM::subtract): d = (float)(t*alpha + c*beta) evaluated in double. */
+         * (MatOp_GEMM::subtract): d = (float)(t*(float)alpha + c*(float)beta) evaluated in double. */
         float a[3], b[3];
         for (int i = 0; i < 3; i++) {
-            a[i] = (float)((double)KRq[i] * -1.0 + (double)x_i[i] * r3q);
+            a[i] = (float)((double)KRq[i] * -1.0 + (double)x_i[i] * (double)(float)r3q);
             b[i] = (float)((double)Kt[i] * -1.0 + (double)x_i[i] * (double)t[2]);
         }
         double ab = 0, aa = 0;

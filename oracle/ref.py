@@ -210,6 +210,30 @@ class Ref:
         arr = (C.c_void_p * len(hist_frames))(*[f.h for f in hist_frames])
         return self.lib.ref_mapper_update(arr, len(hist_frames), obj_frame.h)
 
+    # ---- shim self-checks (restated OpenCV pieces)
+    def shim_randn(self, seed, n, mean, stddev):
+        out = np.empty(n, np.float32)
+        self.lib.ref_shim_randn(C.c_ulonglong(seed), C.c_int(n), C.c_double(mean), C.c_double(stddev), _p(out))
+        return out
+
+    def shim_gemm(self, A, B, alpha=1.0, Cm=None, beta=0.0):
+        A = _f32(A); B = _f32(B); m, k = A.shape; n = B.shape[1]
+        Cm = _f32(Cm) if Cm is not None else None
+        out = np.empty((m, n), np.float32)
+        self.lib.ref_shim_gemm(_p(A), m, k, _p(B), n, C.c_double(alpha), _p(Cm), C.c_double(beta), _p(out))
+        return out
+
+    def shim_solve_svd(self, A, b):
+        A = _f32(A); b = _f32(b).reshape(-1); m, n = A.shape; x = np.empty(n, np.float32)
+        self.lib.ref_shim_solve_svd(_p(A), _p(b), m, n, _p(x))
+        return x
+
+    def shim_addex(self, A, B, alpha, beta):
+        A = _f32(A).reshape(-1); B = _f32(B).reshape(-1) if B is not None else None
+        out = np.empty_like(A)
+        self.lib.ref_shim_addex(_p(A), _p(B), A.size, C.c_double(alpha), C.c_double(beta), _p(out))
+        return out
+
     def vo_create(self, K):
         K = _f32(K).reshape(-1)
         return RefVO(self, self.lib.ref_vo_create(_p(K)))

@@ -352,4 +352,30 @@ ref_frame* ref_vo_history_frame(ref_vo* v, int age)
     return r;
 }
 
+// ---- shim self-checks: the restated OpenCV pieces, exposed so that tests can compare them with
+// opencv-python known answers (tests/test_oracle_known_answers.py) -------------------------------
+void ref_shim_randn(unsigned long long seed, int n, double mean, double stddev, float* out)
+{
+    cv::theRNG().state = seed;
+    cv::Mat m(1, n);
+    cv::randn(m, mean, stddev);
+    put(m, out);
+}
+void ref_shim_gemm(const float* A, int m, int k, const float* B, int n, double alpha, const float* Cm, double beta, float* out)
+{
+    const cv::Mat1f c = Cm ? wrap(Cm, n, m) : cv::Mat1f();
+    put(cv::shim::gemm(wrap(A, k, m), wrap(B, n, k), alpha, Cm ? &c : nullptr, beta), out);
+}
+void ref_shim_solve_svd(const float* A, const float* b, int m, int n, float* x)
+{
+    cv::Mat X;
+    cv::solve(wrap(A, n, m), wrap(b, 1, m), X, cv::DECOMP_SVD);
+    put(X, x);
+}
+// MatExpr lowering of `A*alpha + B*beta` (cv::add / subtract / scaleAdd / addWeighted)
+void ref_shim_addex(const float* A, const float* B, int n, double alpha, double beta, float* out)
+{
+    put(cv::MatExpr::addex(wrap(A, n, 1), B ? wrap(B, n, 1) : cv::Mat1f(), alpha, beta).eval(), out);
+}
+
 } // extern "C"

@@ -14,7 +14,7 @@
 //   * MatExpr is LAZY like OpenCV's: scale factors fold into a double alpha/beta and are applied at
 //     assignment (convertTo / scaleAdd / addWeighted / gemm semantics), see "MatExpr" below;
 //   * small cv::gemm (2..4 inner length): fp32 dot products left to right, no FMA, then
-//     (float)(t*alpha + c*beta) in double;
+//     (float)(t*(float)alpha + c*(float)beta) evaluated in double;
 //   * Point_<float> -> Point_<int> = saturate_cast = cvRound (round half to even, SSE cvtss2si);
 //   * cv::norm / cv::trace / Mat::dot accumulate in double, sequentially;
 //   * cv::Rodrigues, cv::solve(DECOMP_SVD) (JacobiSVDImpl_<float> + SVBkSb), cv::randn (MWC +
@@ -340,9 +340,10 @@ template <typename T> inline Mat_<T>::Mat_(const MatCommaInitializer_<T>& ci) : 
 namespace shim
 {
 // cv::gemm for float (modules/core/src/matmul.dispatch.cpp): inner lengths 2..4 take the unrolled
-// path: float t = a0*b0 + a1*b1 + ... (fp32, left to right), d = (float)(t*alpha + c*beta) with the
-// second line in double.  Other shapes: GEMMSingleMul<float,double> (double accumulation).
-inline Mat gemm(const Mat& A, const Mat& B, double alpha, const Mat* C, double beta)
+// path: float t = a0*b0 + a1*b1 + ... (fp32, left to right), d = (float)(t*alpha + c*beta) with
+// alpha, beta rounded to float and that line evaluated in double (bit-exact against cv2.gemm 4.13,
+// tests/test_oracle_known_answers.py).  Other shapes: GEMMSingleMul<float,double> (double accumulation).
+inline Mat gemm(const Mat& A, const Mat& B, double alpha_, const Mat* C, double beta)
 {
     assert(A.cols == B.rows);
     const int M = A.rows, N = B.cols, len = A.cols;
@@ -351,7 +352,8 @@ inline Mat gemm(const Mat& A, const Mat& B, double alpha, const Mat* C, double b
     for (int i = 0; i < M; i++)
         for (int j = 0; j < N; j++) {
             const double c = C ? (double)C->data[(size_t)i * C->step + j] : 0.0;
-            const double be = C ? beta : 0.0;
+            const double be = C ? (double)(float)beta : 0.0;
+            const double alpha = (double)(float)alpha_; // alpha/beta are rounded to float first (checked against cv2.gemm)
             if (small) {
                 float t = A.data[(size_t)i * A.step] * B.data[j];
                 for (int k = 1; k < len; k++) t = t + A.data[(size_t)i * A.step + k] * B.data[(size_t)k * B.step + j];
@@ -468,10 +470,13 @@ public:
                 float r;
                 if (alpha == 1 && beta == 1) r = va + vb;                   // cv::add
                 else if (alpha == 1 && beta == -1) r = va - vb;             // cv::subtract
-                else if (alpha == 1) r = vb * (float)beta + va;             // cv::scaleAdd(b, beta, a)
+                // cv::scaleAdd is v_muladd(src1, (float)alpha, src2): fused on FMA3 hardware (as measured
+                // with cv2 4.13 here).  In the reference's hot path its operands have disjoint non-zeros
+                // (eye + alpha*hat(w), se3.cpp:85,114), where fused and unfused results coincide.
+                else if (alpha == 1) r = std::fmaf(vb, (float)beta, va);    // cv::scaleAdd(b, beta, a)
                 else if (beta == 1 && alpha == -1) r = vb - va;             // cv::subtract(b, a)
-                else if (beta == 1) r = va * (float)alpha + vb;             // cv::scaleAdd(a, alpha, b)
-                else r = va * (float)alpha + vb * (float)beta;              // cv::addWeighted (gamma 0)
+                else if (beta == 1) r = std::fmaf(va, (float)alpha, vb);    // cv::scaleAdd(a, alpha, b)
+                else r = (float)((double)va * alpha + (double)vb * beta);   // cv::addWeighted (gamma 0): double
                 if (s != 0) r = r + sf;
                 m.data[(size_t)y * m.step + x] = r;
             }
