@@ -106,22 +106,36 @@ class ClockSampler:
 # CPU arm: the oracle (or oracle/_ref) on the host cores, one independent sequence per worker process
 # ------------------------------------------------------------------------------------------------
 def _build_cpu_lib():
-    """Compile the CPU arm's library ON THIS HOST (-march=native must match the cores it runs on)."""
+    """Compile the CPU port's library ON THIS HOST (-march=native must match the cores it runs on)."""
     from oracle import oracle as O
     d = tempfile.mkdtemp(prefix="dvo_cpu_")
     return O.build(fast=True, out_dir=d)
 
 
-def _cpu_worker(conn, frames, K, d0, s0, lib_path):
-    """frames: [n][h][w] float32 (shared, fork).  Protocol: ("run", first, count) -> seconds."""
+def _ref_lib():
+    """oracle/_ref/libdvo_ref_fast.so: the reference's OWN translation units (unmodified, compiled in
+    the build container from /root/reference over the OpenCV-API shim) with its release optimisation
+    level (-Ofast, CMakeLists.txt:43; -march=x86-64-v3 instead of native so the prebuilt file runs on
+    the GPU box's host).  None when it was never built."""
+    from oracle import ref as R
     try:
-        os.sched_setaffinity(0, os.sched_getaffinity(0))
+        return R.build(fast=True)
     except Exception:
-        pass
-    from oracle.oracle import Oracle
-    orc = Oracle(path=lib_path)   # reference release flags: -Ofast -march=native (CMakeLists.txt:43)
-    vo = orc.vo_create(K, LEVELS, CULLS)
-    vo.odometrize(frames[0], d0, s0)
+        return None
+
+
+def _cpu_worker(conn, frames, K, d0, s0, kind, lib_path):
+    """frames: [n][h][w] float32 (shared, fork).  Protocol: ("run", first, count) -> seconds."""
+    os.environ["OMP_NUM_THREADS"] = "1"   # one sequence per core; forEach stays serial inside a worker
+    if kind == "reference":
+        from oracle.ref import Ref
+        vo = Ref(path=lib_path).vo_create(K)           # System::VisualOdometry(K), Frame(gray, K, 3, 2)
+        vo.odometrize(frames[0], d0)
+    else:
+        from oracle.oracle import Oracle
+        orc = Oracle(path=lib_path)   # reference release flags: -Ofast -march=native (CMakeLists.txt:43)
+        vo = orc.vo_create(K, LEVELS, CULLS)
+        vo.odometrize(frames[0], d0, s0)
     conn.send("ready")
     while True:
         msg = conn.recv()
@@ -137,16 +151,18 @@ def _cpu_worker(conn, frames, K, d0, s0, lib_path):
 class CpuArm:
     """cores worker processes, each running the CPU VO on its own synthetic sequence."""
 
-    def __init__(self, frames, K, d0, s0):
+    def __init__(self, frames, K, d0, s0, kind="reference"):
         # frames: [cores][n][h][w]
         self.cores = frames.shape[0]
         ctx = mp.get_context("fork")
-        lib_path = _build_cpu_lib()
-        self.kind = "port"   # oracle/dvo_oracle.c; "reference" once oracle/_ref is wired in
+        lib_path = _ref_lib() if kind == "reference" else None
+        if lib_path is None:   # oracle/_ref absent: fall back to the C restatement (oracle/dvo_oracle.c)
+            kind, lib_path = "port", _build_cpu_lib()
+        self.kind = kind
         self.pipes = []; self.procs = []
         for c in range(self.cores):
             a, b = ctx.Pipe()
-            p = ctx.Process(target=_cpu_worker, args=(b, frames[c], K, d0[c], s0[c], lib_path), daemon=True)
+            p = ctx.Process(target=_cpu_worker, args=(b, frames[c], K, d0[c], s0[c], kind, lib_path), daemon=True)
             p.start()
             self.pipes.append(a); self.procs.append(p)
         for a in self.pipes:
@@ -219,14 +235,14 @@ def host_cores():
         return os.cpu_count() or 1
 
 
-def run_cpu_arm(steps, warmup, frames_per_step, cores=None):
+def run_cpu_arm(steps, warmup, frames_per_step, cores=None, kind="reference"):
     """Times the CPU VO: every step, each of `cores` workers pushes frames_per_step frames of its own
     sequence.  Returns (frames_per_s, ms_per_step, info)."""
     cores = cores or host_cores()
     n_frames = 1 + (steps + warmup) * frames_per_step
     frames, how = render_host_frames(cores, n_frames, seed0=900000)
     d0, s0 = depth_prior(cores, seed=4321)
-    arm = CpuArm(frames, default_K(), d0, s0)
+    arm = CpuArm(frames, default_K(), d0, s0, kind)
     pos = 1
     for _ in range(warmup):
         arm.step(pos, frames_per_step); pos += frames_per_step
@@ -235,9 +251,11 @@ def run_cpu_arm(steps, warmup, frames_per_step, cores=None):
         t += arm.step(pos, frames_per_step); pos += frames_per_step
     arm.close()
     total = cores * frames_per_step * steps
+    what = ("the reference's own sources (oracle/_ref, -Ofast)" if arm.kind == "reference" else
+            "C restatement of the reference (oracle/dvo_oracle.c, -Ofast -march=native)")
     info = dict(kind=arm.kind, cores=cores,
-                sample="%d sequences x %d frames of the 640x480 workload (one per core, %s), %d frames per step" % (
-                    cores, steps * frames_per_step, how, cores * frames_per_step))
+                sample="%d sequences x %d frames of the 640x480 workload (one single-threaded process per core, %s; input: %s), "
+                       "%d frames per step" % (cores, steps * frames_per_step, what, how, cores * frames_per_step))
     return total / t, 1e3 * t / steps, info
 
 
@@ -386,7 +404,9 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=8)
     ap.add_argument("--roofline-steps", type=int, default=4)
     ap.add_argument("--resident-frames", type=int, default=48, help="distinct frames per stream kept in HBM")
-    ap.add_argument("--cpu-frames-per-step", type=int, default=2)
+    ap.add_argument("--cpu-frames-per-step", type=int, default=1)
+    ap.add_argument("--cpu-kind", default="reference", choices=["reference", "port"],
+                    help="CPU arm: the reference's own sources (oracle/_ref) or the C restatement (oracle/dvo_oracle.c)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else max(args.warmup, 1)
@@ -402,7 +422,7 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return
-        fps, ms_step, info = run_cpu_arm(args.steps, args.warmup, args.cpu_frames_per_step)
+        fps, ms_step, info = run_cpu_arm(args.steps, args.warmup, args.cpu_frames_per_step, kind=args.cpu_kind)
         info["value"] = fps
         line = dict(base, impl="reference", value=fps, ms_per_step=ms_step, cpu_baseline=info, gpu_launches=0,
                     e2e=dict(value=fps, unit="frames/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
@@ -419,9 +439,12 @@ def main():
     res = run_gpu_arm(args, rank, world, local_rank, dist)
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        fps, ms_step, info = run_cpu_arm(steps=12, warmup=1, frames_per_step=args.cpu_frames_per_step)
+        fps, ms_step, info = run_cpu_arm(steps=12, warmup=1, frames_per_step=args.cpu_frames_per_step, kind=args.cpu_kind)
         info["value"] = fps; info["unit"] = "frames/s"
         cpu = info
+        if info["kind"] == "reference":   # the restatement beside it: what the same algorithm costs without per-pixel se3::exp
+            fps2, _, info2 = run_cpu_arm(steps=12, warmup=1, frames_per_step=4, kind="port")
+            cpu["port_value"] = fps2; cpu["port_sample"] = info2["sample"]
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
