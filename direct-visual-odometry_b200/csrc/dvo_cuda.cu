@@ -34,7 +34,9 @@ struct dvo_ctx {
     int* d_hist = nullptr;
     PoseTab* d_tab = nullptr;
     double* d_partials = nullptr;
-    int max_blocks = 0, ppt = 1;
+    int trk_B = 1;          // CTAs per stream of the tracking kernel (1: no inter-CTA barrier)
+    int trk_capacity = 0;   // co-resident tracking CTAs on this device
+    MapRoi roi{};           // Mapper::update's ROI clipped to the finest level
     dvo_iter_log* d_log = nullptr;
     int log_cap = 0;
     uint8_t* d_flags = nullptr;
@@ -54,10 +56,12 @@ struct dvo_ctx {
     size_t h_pinned_bytes = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     uint64_t launches = 0;
-    // gn timing
-    bool gn_timing = false;
-    std::vector<cudaEvent_t> gn_ev;
-    size_t gn_ev_used = 0;
+    // per-kernel device timing (CUDA events around every launch of the timed kernels)
+    bool ktiming = false;
+    std::vector<cudaEvent_t> k_ev;
+    std::vector<int> k_ev_id;
+    size_t k_ev_used = 0;
+    bool rows_only_staged = false; // d_stage_in holds only the sampled input rows (host path)
     // VO host mirror
     int vo_frame_id = -1;
     std::mt19937 engine; // default seed 5489, src/math/gaussian.cpp:8
@@ -126,11 +130,11 @@ static int alloc_slot(dvo_ctx* ctx, int idx)
     CK(cudaMemsetAsync(sh.base, 0, ctx->slot_bytes, ctx->stream));
     char* p = (char*)sh.base;
     const Consts& c = ctx->c;
+    const size_t ntop = (size_t)c.lv[c.L - 1].n;
     auto take = [&](size_t bytes) { char* r = p; p += (bytes + 255) & ~(size_t)255; return r; };
-    for (int l = 0; l < c.L; l++) sh.dev.tex[l] = (float4*)take((size_t)c.S * c.lv[l].n * sizeof(float4));
-    for (int l = 0; l < c.L; l++) sh.dev.ds[l] = (float2*)take((size_t)c.S * c.lv[l].n * sizeof(float2));
-    for (int l = 0; l < c.L; l++) sh.dev.gray[l] = (float*)take((size_t)c.S * c.lv[l].n * sizeof(float));
-    sh.dev.age = (float*)take((size_t)c.S * c.lv[c.L - 1].n * sizeof(float));
+    sh.dev.ds = (float2*)take((size_t)c.S * ntop * sizeof(float2));
+    sh.dev.gray = (float*)take((size_t)c.S * ntop * sizeof(float));
+    sh.dev.age = (float*)take((size_t)c.S * ntop * sizeof(float));
     sh.dev.xi = (float*)take((size_t)c.S * 6 * sizeof(float));
     sh.dev.rel_xi = (float*)take((size_t)c.S * 6 * sizeof(float));
     CK(cudaMemcpyAsync(ctx->d_slots + idx, &sh.dev, sizeof(SlotDev), cudaMemcpyHostToDevice, ctx->stream));
@@ -191,8 +195,7 @@ extern "C" int dvo_create(dvo_ctx** out, const dvo_params* p)
     const int S = c.S, ntop = c.lv[c.L - 1].n;
     size_t sb = 0;
     auto rnd = [](size_t b) { return (b + 255) & ~(size_t)255; };
-    for (int l = 0; l < c.L; l++) sb += rnd((size_t)S * c.lv[l].n * 16) + rnd((size_t)S * c.lv[l].n * 8) + rnd((size_t)S * c.lv[l].n * 4);
-    sb += rnd((size_t)S * ntop * 4) + 2 * rnd((size_t)S * 24);
+    sb += rnd((size_t)S * ntop * 8) + 2 * rnd((size_t)S * ntop * 4) + 2 * rnd((size_t)S * 24);
     ctx->slot_bytes = sb;
     // slot ids [0, max_frames): granular API; [max_frames, max_frames + max_keyframes]: the VO pool
     // (entry k = keyframe k of every stream, entry n_kf = the stream's current frame)
@@ -207,16 +210,22 @@ extern "C" int dvo_create(dvo_ctx** out, const dvo_params* p)
     CK(cudaMalloc(&ctx->d_vo, sizeof(VoState) * S));
     CK(cudaMalloc(&ctx->d_hist, sizeof(int) * (size_t)S * c.max_kf));
     CK(cudaMalloc(&ctx->d_tab, sizeof(PoseTab) * (size_t)S * c.max_kf));
-    // GN launch shape: enough blocks to fill 148 SMs several times over, few enough that the
-    // fixed-order reduction of block partials in the kernel tail stays short.
+    // Tracking launch shape: one CTA per stream when the streams alone fill the GPU; otherwise a
+    // stream's pixels are split over B co-resident CTAs (cooperative launch, global barrier).
     {
-        const double total = (double)S * ntop;
-        int ppt = 1;
-        while (ppt < 8 && total / (256.0 * ppt) > 148.0 * 16) ppt *= 2;
-        ctx->ppt = ppt;
-        ctx->max_blocks = cdiv(ntop, GN_THREADS * ppt);
+        int per_sm = 0, n_sm = 0;
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_track, TRK_THREADS, 0));
+        CK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, ctx->device));
+        ctx->trk_capacity = per_sm * n_sm;
+        int coop = 0;
+        CK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, ctx->device));
+        int B = coop ? ctx->trk_capacity / S : 1;
+        const int useful = cdiv(ntop, TRK_THREADS * 4); // >= 4 pixels per thread at the finest level
+        if (B > useful) B = useful;
+        if (B < 1) B = 1;
+        ctx->trk_B = B;
     }
-    CK(cudaMalloc(&ctx->d_partials, sizeof(double) * 32 * (size_t)S * ctx->max_blocks));
+    CK(cudaMalloc(&ctx->d_partials, sizeof(double) * 32 * (size_t)S * ctx->trk_B));
     ctx->log_cap = c.L * c.max_iter;
     CK(cudaMalloc(&ctx->d_log, sizeof(dvo_iter_log) * (size_t)S * ctx->log_cap));
     CK(cudaMemset(ctx->d_log, 0, sizeof(dvo_iter_log) * (size_t)S * ctx->log_cap));
@@ -224,9 +233,21 @@ extern "C" int dvo_create(dvo_ctx** out, const dvo_params* p)
     for (int l = 0; l < c.L; l++) nmax = nmax > (size_t)c.lv[l].n ? nmax : (size_t)c.lv[l].n;
     CK(cudaMalloc(&ctx->d_flags, (size_t)S * ntop));
     CK(cudaMalloc(&ctx->d_mask, (size_t)S * nmax));
-    ctx->nblk_top = cdiv(ntop, 256);
+    CK(cudaMemset(ctx->d_flags, 0, (size_t)S * ntop));
+    {   // Mapper::update's ROI (mapper.cpp:90) clipped to the finest level
+        const LevelGeom& gt = c.lv[c.L - 1];
+        MapRoi& r = ctx->roi;
+        r.x0 = c.map_x0 > 0 ? c.map_x0 : 0; r.y0 = c.map_y0 > 0 ? c.map_y0 : 0;
+        const int x1 = c.map_x1 < gt.w - 1 ? c.map_x1 : gt.w - 1, y1 = c.map_y1 < gt.h - 1 ? c.map_y1 : gt.h - 1;
+        r.w = x1 - r.x0 + 1 > 0 ? x1 - r.x0 + 1 : 0; r.h = y1 - r.y0 + 1 > 0 ? y1 - r.y0 + 1 : 0;
+        r.n = r.w * r.h;
+        r.nblk = cdiv(r.n > 0 ? r.n : 1, 256);
+        if (r.w == 0) r.w = 1;
+    }
+    ctx->nblk_top = ctx->roi.nblk;
     CK(cudaMalloc(&ctx->d_blockcnt, sizeof(unsigned) * (size_t)S * ctx->nblk_top));
     CK(cudaMalloc(&ctx->d_winner, sizeof(int) * (size_t)S * ntop));
+    CK(cudaMemset(ctx->d_winner, 0xFF, sizeof(int) * (size_t)S * ntop));
     CK(cudaMalloc(&ctx->d_tmp, sizeof(float) * (size_t)S * ntop));
     CK(cudaMalloc(&ctx->d_stage_in, sizeof(float) * (size_t)S * c.in_w * c.in_h));
     for (int k = 0; k < 3; k++) CK(cudaMalloc(&ctx->d_stage[k], sizeof(float) * (size_t)S * c.in_w * c.in_h));
@@ -258,7 +279,7 @@ extern "C" void dvo_destroy(dvo_ctx* ctx)
     for (int k = 0; k < 3; k++) cudaFree(ctx->d_stage[k]);
     cudaFree(ctx->d_small); cudaFree(ctx->d_ismall); cudaFree(ctx->d_forced);
     if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
-    for (auto e : ctx->gn_ev) cudaEventDestroy(e);
+    for (auto e : ctx->k_ev) cudaEventDestroy(e);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -314,16 +335,60 @@ static int check_slot(dvo_ctx* ctx, int slot)
     return DVO_OK;
 }
 
-// slot >= 0: that slot for every stream; slot < 0: each stream's current VO slot (VoState::cur_slot)
-static int build_frame(dvo_ctx* ctx, int slot, const float* gray_dev)
+// ---- per-kernel device timing --------------------------------------------------------------------
+enum KernelId { K_CULL = 0, K_TRACK, K_PROP_SCATTER, K_PROP_GATHER, K_MAP_UPDATE, K_MAP_APPLY, K_REGULARIZE, K_REG_COMMIT, K_COUNT };
+static const char* const kernel_names[K_COUNT] = {"k_cull_gray", "k_track", "k_propagate_scatter", "k_propagate_gather", "k_map_update",
+                                                  "k_map_update_apply", "k_regularize", "k_regularize_commit"};
+struct KTimer { // records an event pair around one launch when timing is on
+    dvo_ctx* ctx;
+    cudaEvent_t e1 = nullptr;
+    KTimer(dvo_ctx* c, int id) : ctx(c)
+    {
+        if (!ctx->ktiming) return;
+        if (ctx->k_ev_used + 2 > ctx->k_ev.size())
+            for (int k = 0; k < 2; k++) {
+                cudaEvent_t e;
+                if (cudaEventCreate(&e) != cudaSuccess) return;
+                ctx->k_ev.push_back(e);
+            }
+        ctx->k_ev_id.resize(ctx->k_ev.size() / 2);
+        ctx->k_ev_id[ctx->k_ev_used / 2] = id;
+        cudaEvent_t e0 = ctx->k_ev[ctx->k_ev_used++];
+        e1 = ctx->k_ev[ctx->k_ev_used++];
+        cudaEventRecord(e0, ctx->stream);
+    }
+    ~KTimer() { if (e1) cudaEventRecord(e1, ctx->stream); }
+};
+
+// slot >= 0: that slot for every stream; slot < 0: each stream's current VO slot.
+// rows_only: gray_dev holds only the input rows that Convert::cullImage samples (host staging path).
+static int build_frame(dvo_ctx* ctx, int slot, const float* gray_dev, bool rows_only)
 {
     const Consts& c = ctx->c;
     const VoState* vo = slot < 0 ? ctx->d_vo : nullptr;
-    dim3 grid(cdiv(c.lv[c.L - 1].n, 256), c.S, c.L);
-    k_cull_gray<<<grid, 256, 0, ctx->stream>>>(c, gray_dev, ctx->d_slots, slot, vo);
+    const LevelGeom& gt = c.lv[c.L - 1];
+    dim3 grid(cdiv(gt.n, 1024), c.S);
+    KTimer t(ctx, K_CULL);
+    k_cull_gray<<<grid, 256, 0, ctx->stream>>>(c, gray_dev, rows_only ? gt.h : c.in_h, rows_only ? 0 : c.culls, ctx->d_slots, slot, vo);
     KCHECK();
-    k_build_tex<<<grid, 256, 0, ctx->stream>>>(c, ctx->d_slots, slot, vo);
-    KCHECK();
+    return DVO_OK;
+}
+
+// Host frame -> device staging.  Convert::cullImage only samples rows that are multiples of 2^culls,
+// so when the geometry allows one uniform pitch only those rows cross PCIe (1/2^culls of the bytes).
+static int stage_gray(dvo_ctx* ctx, const float* gray, bool* rows_only)
+{
+    const Consts& c = ctx->c;
+    const int step = 1 << c.culls;
+    const LevelGeom& gt = c.lv[c.L - 1];
+    if (c.culls > 0 && c.in_h % step == 0 && gt.h == c.in_h / step) {
+        CK(cudaMemcpy2DAsync(ctx->d_stage_in, sizeof(float) * (size_t)c.in_w, gray, sizeof(float) * (size_t)c.in_w * step,
+                             sizeof(float) * (size_t)c.in_w, (size_t)c.S * gt.h, cudaMemcpyHostToDevice, ctx->stream));
+        *rows_only = true;
+    } else {
+        CK(cudaMemcpyAsync(ctx->d_stage_in, gray, sizeof(float) * (size_t)c.S * c.in_w * c.in_h, cudaMemcpyHostToDevice, ctx->stream));
+        *rows_only = false;
+    }
     return DVO_OK;
 }
 
@@ -332,15 +397,18 @@ extern "C" int dvo_frame_create_dev(dvo_ctx* ctx, int* slot, const float* gray_d
     ARG(slot && gray_dev, "null argument");
     int rc = find_free_slot(ctx, slot);
     if (rc) return rc;
-    return build_frame(ctx, *slot, gray_dev);
+    return build_frame(ctx, *slot, gray_dev, false);
 }
 
 extern "C" int dvo_frame_create(dvo_ctx* ctx, int* slot, const float* gray)
 {
     ARG(slot && gray, "null argument");
-    const Consts& c = ctx->c;
-    CK(cudaMemcpyAsync(ctx->d_stage_in, gray, sizeof(float) * (size_t)c.S * c.in_w * c.in_h, cudaMemcpyHostToDevice, ctx->stream));
-    return dvo_frame_create_dev(ctx, slot, ctx->d_stage_in);
+    bool rows_only = false;
+    int rc = stage_gray(ctx, gray, &rows_only);
+    if (rc) return rc;
+    rc = find_free_slot(ctx, slot);
+    if (rc) return rc;
+    return build_frame(ctx, *slot, ctx->d_stage_in, rows_only);
 }
 
 extern "C" int dvo_frame_release(dvo_ctx* ctx, int slot)
@@ -351,19 +419,8 @@ extern "C" int dvo_frame_release(dvo_ctx* ctx, int slot)
     return DVO_OK;
 }
 
-static int recull_ds(dvo_ctx* ctx, int slot)
-{
-    const Consts& c = ctx->c;
-    if (c.L < 2) return DVO_OK;
-    dim3 grid(cdiv(c.lv[c.L - 2].n, 256), c.S, c.L - 1);
-    k_cull_ds<<<grid, 256, 0, ctx->stream>>>(c, ctx->d_slots, slot, slot < 0 ? ctx->d_vo : nullptr);
-    KCHECK();
-    return DVO_OK;
-}
-
 static int set_depth_impl(dvo_ctx* ctx, int slot, const float* depth, const float* sigma, const float* age, int full_res)
 {
-    int rc;
     const Consts& c = ctx->c;
     const LevelGeom& gt = c.lv[c.L - 1];
     const int sw = full_res ? c.in_w : gt.w, sh = full_res ? c.in_h : gt.h;
@@ -378,8 +435,6 @@ static int set_depth_impl(dvo_ctx* ctx, int slot, const float* depth, const floa
     k_set_top<<<grid, 256, 0, ctx->stream>>>(c, ctx->d_slots, slot, slot < 0 ? ctx->d_vo : nullptr, dev[0], dev[1], dev[2], sw, sh,
                                               full_res ? c.culls : 0);
     KCHECK();
-    rc = recull_ds(ctx, slot);
-    if (rc) return rc;
     CK(cudaStreamSynchronize(ctx->stream)); // host buffers may be pageable: do not return before the copies finish
     return DVO_OK;
 }
@@ -446,55 +501,71 @@ extern "C" int dvo_warp_image(dvo_ctx* ctx, int ref_slot, int level, const float
     return DVO_OK;
 }
 
-static int launch_gn(dvo_ctx* ctx, uint8_t* mask)
+// One k_track launch = a whole Tracker::track (or one Track::optimize step) for every stream.
+static int launch_track(dvo_ctx* ctx, TrackArgs a)
 {
     const Consts& c = ctx->c;
-    GnArgs a;
-    a.st = ctx->d_ts; a.partials = ctx->d_partials; a.max_blocks = ctx->max_blocks;
-    a.log = ctx->d_log; a.log_cap = ctx->log_cap; a.mask = mask; a.ppt = ctx->ppt;
-    dim3 grid(ctx->max_blocks, c.S);
-    cudaEvent_t e0 = nullptr, e1 = nullptr;
-    if (ctx->gn_timing) {
-        if (ctx->gn_ev_used + 2 > ctx->gn_ev.size()) {
-            for (int k = 0; k < 2; k++) {
-                cudaEvent_t e;
-                CK(cudaEventCreate(&e));
-                ctx->gn_ev.push_back(e);
-            }
-        }
-        e0 = ctx->gn_ev[ctx->gn_ev_used++];
-        e1 = ctx->gn_ev[ctx->gn_ev_used++];
-        CK(cudaEventRecord(e0, ctx->stream));
+    a.st = ctx->d_ts; a.partials = ctx->d_partials; a.B = ctx->trk_B;
+    a.log = ctx->d_log; a.log_cap = ctx->log_cap;
+    a.slots = ctx->d_slots;
+    dim3 grid(ctx->trk_B, c.S);
+    KTimer t(ctx, K_TRACK);
+    if (ctx->trk_B > 1) { // CTAs of a stream meet at a global barrier: they must be co-resident
+        Consts cc = c;
+        void* params[] = {(void*)&cc, (void*)&a};
+        CK(cudaLaunchCooperativeKernel((const void*)k_track, grid, dim3(TRK_THREADS), params, 0, ctx->stream));
+        ctx->launches++;
+    } else {
+        k_track<<<grid, TRK_THREADS, 0, ctx->stream>>>(c, a);
+        KCHECK();
     }
-    switch (ctx->ppt) {
-    case 1: k_gn_step<1><<<grid, GN_THREADS, 0, ctx->stream>>>(c, a); break;
-    case 2: k_gn_step<2><<<grid, GN_THREADS, 0, ctx->stream>>>(c, a); break;
-    case 4: k_gn_step<4><<<grid, GN_THREADS, 0, ctx->stream>>>(c, a); break;
-    default: k_gn_step<8><<<grid, GN_THREADS, 0, ctx->stream>>>(c, a); break;
+    return DVO_OK;
+}
+
+extern "C" int dvo_kernel_timing(dvo_ctx* ctx, int enable, dvo_kernel_time* out, int cap, int* n_out)
+{
+    if (enable) {
+        ctx->ktiming = true;
+        ctx->k_ev_used = 0;
+        return DVO_OK;
     }
-    KCHECK();
-    if (e1) CK(cudaEventRecord(e1, ctx->stream));
+    ctx->ktiming = false;
+    CK(cudaStreamSynchronize(ctx->stream));
+    float tot[K_COUNT] = {0};
+    int cnt[K_COUNT] = {0};
+    for (size_t k = 0; k + 1 < ctx->k_ev_used; k += 2) {
+        float ms = 0;
+        CK(cudaEventElapsedTime(&ms, ctx->k_ev[k], ctx->k_ev[k + 1]));
+        const int id = ctx->k_ev_id[k / 2];
+        tot[id] += ms; cnt[id]++;
+    }
+    int n = 0;
+    for (int id = 0; id < K_COUNT && out && n < cap; id++) {
+        if (!cnt[id]) continue;
+        memset(&out[n], 0, sizeof(out[n]));
+        strncpy(out[n].name, kernel_names[id], sizeof(out[n].name) - 1);
+        out[n].total_ms = tot[id]; out[n].launches = cnt[id];
+        n++;
+    }
+    if (n_out) *n_out = n;
+    ctx->k_ev_used = 0;
     return DVO_OK;
 }
 
 extern "C" int dvo_gn_timing(dvo_ctx* ctx, int enable, float* total_ms, int* launches)
 {
-    if (enable) {
-        ctx->gn_timing = true;
-        ctx->gn_ev_used = 0;
-        return DVO_OK;
-    }
-    ctx->gn_timing = false;
-    CK(cudaStreamSynchronize(ctx->stream));
-    float tot = 0;
-    for (size_t k = 0; k + 1 < ctx->gn_ev_used; k += 2) {
-        float ms = 0;
-        CK(cudaEventElapsedTime(&ms, ctx->gn_ev[k], ctx->gn_ev[k + 1]));
-        tot += ms;
-    }
-    if (total_ms) *total_ms = tot;
-    if (launches) *launches = (int)(ctx->gn_ev_used / 2);
-    ctx->gn_ev_used = 0;
+    if (enable) return dvo_kernel_timing(ctx, 1, nullptr, 0, nullptr);
+    dvo_kernel_time kt[K_COUNT];
+    int n = 0;
+    int rc = dvo_kernel_timing(ctx, 0, kt, K_COUNT, &n);
+    if (rc) return rc;
+    if (total_ms) *total_ms = 0;
+    if (launches) *launches = 0;
+    for (int k = 0; k < n; k++)
+        if (!strcmp(kt[k].name, "k_track")) {
+            if (total_ms) *total_ms = kt[k].total_ms;
+            if (launches) *launches = kt[k].launches;
+        }
     return DVO_OK;
 }
 
@@ -509,10 +580,11 @@ extern "C" int dvo_gn_step(dvo_ctx* ctx, int obj_slot, int ref_slot, int level, 
     ARG(level >= 0 && level < c.L && xi, "bad argument");
     const LevelGeom& g = c.lv[level];
     CK(cudaMemcpyAsync(ctx->d_small, xi, sizeof(float) * 6 * (size_t)c.S, cudaMemcpyHostToDevice, ctx->stream));
-    k_track_init<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_ts, ctx->d_slots, obj_slot, ref_slot, nullptr, 1, level, ctx->d_small,
-                                                        0.0, 0.0f);
-    KCHECK();
-    rc = launch_gn(ctx, mask ? ctx->d_mask : nullptr);
+    if (mask) CK(cudaMemsetAsync(ctx->d_mask, 0, (size_t)c.S * g.n, ctx->stream));
+    TrackArgs a{};
+    a.mask = mask ? ctx->d_mask : nullptr;
+    a.obj_slot = obj_slot; a.ref_slot = ref_slot; a.mode = 1; a.level0 = level; a.xi0 = ctx->d_small;
+    rc = launch_track(ctx, a);
     if (rc) return rc;
     dvo_iter_log* hl = (dvo_iter_log*)ctx->h_pinned;
     CK(cudaMemcpy2DAsync(hl, sizeof(dvo_iter_log), ctx->d_log, sizeof(dvo_iter_log) * ctx->log_cap, sizeof(dvo_iter_log), c.S,
@@ -527,20 +599,19 @@ extern "C" int dvo_gn_step(dvo_ctx* ctx, int obj_slot, int ref_slot, int level, 
     return DVO_OK;
 }
 
-static int enqueue_track(dvo_ctx* ctx, int obj_slot, int ref_slot, bool use_vo, double stop_update, float stop_residual)
+static int enqueue_track(dvo_ctx* ctx, int obj_slot, int ref_slot, bool use_vo, double stop_update, float stop_residual, int frame_id,
+                         const float* forced_rel)
 {
-    const Consts& c = ctx->c;
     if (stop_update < 0) stop_update = (double)ctx->P.min_update; // cv::norm(...) < MINIMUM_UPDATE: float promoted
     if (stop_residual < 0) stop_residual = ctx->P.min_residual;
-    k_track_init<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_ts, ctx->d_slots, obj_slot, ref_slot, use_vo ? ctx->d_vo : nullptr, 0, 0,
-                                                        nullptr, stop_update, stop_residual);
-    KCHECK();
-    const int n = c.L * c.max_iter;
-    for (int k = 0; k < n; k++) {
-        int rc = launch_gn(ctx, nullptr);
-        if (rc) return rc;
+    TrackArgs a{};
+    a.obj_slot = obj_slot; a.ref_slot = ref_slot; a.mode = 0; a.level0 = 0; a.xi0 = nullptr;
+    a.stop_update = stop_update; a.stop_residual = stop_residual;
+    if (use_vo) {
+        a.vo = ctx->d_vo; a.ms = ctx->d_ms; a.hist = ctx->d_hist; a.tab = ctx->d_tab;
+        a.frame_id = frame_id; a.forced_rel = forced_rel;
     }
-    return DVO_OK;
+    return launch_track(ctx, a);
 }
 
 extern "C" int dvo_track(dvo_ctx* ctx, int obj_slot, int ref_slot, float* xi_out, dvo_iter_log* log, int log_cap, int* n_iters,
@@ -551,7 +622,7 @@ extern "C" int dvo_track(dvo_ctx* ctx, int obj_slot, int ref_slot, float* xi_out
     rc = check_slot(ctx, ref_slot);
     if (rc) return rc;
     const Consts& c = ctx->c;
-    rc = enqueue_track(ctx, obj_slot, ref_slot, false, stop_update, stop_residual);
+    rc = enqueue_track(ctx, obj_slot, ref_slot, false, stop_update, stop_residual, 0, nullptr);
     if (rc) return rc;
     TrackState* hts = (TrackState*)((char*)ctx->h_pinned + sizeof(dvo_iter_log) * (size_t)c.S * ctx->log_cap);
     CK(cudaMemcpyAsync(hts, ctx->d_ts, sizeof(TrackState) * (size_t)c.S, cudaMemcpyDeviceToHost, ctx->stream));
@@ -588,37 +659,56 @@ static int enqueue_propagate(dvo_ctx* ctx)
     const Consts& c = ctx->c;
     const int ntop = c.lv[c.L - 1].n;
     dim3 grid(cdiv(ntop, 256), c.S);
-    CK(cudaMemsetAsync(ctx->d_winner, 0xFF, sizeof(int) * (size_t)c.S * ntop, ctx->stream));
-    k_propagate_scatter<<<grid, 256, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ms, ctx->d_winner);
-    KCHECK();
-    k_propagate_gather<<<grid, 256, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ms, ctx->d_winner);
-    KCHECK();
+    {
+        KTimer t(ctx, K_PROP_SCATTER);
+        k_propagate_scatter<<<grid, 256, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ms, ctx->d_winner);
+        KCHECK();
+    }
+    {
+        KTimer t(ctx, K_PROP_GATHER);
+        k_propagate_gather<<<grid, 256, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ms, ctx->d_winner);
+        KCHECK();
+    }
     return DVO_OK;
 }
-static int enqueue_update(dvo_ctx* ctx)
+// tables: the granular entry point computes Mapper::update's pose table here; in the VO loop the
+// tracking kernel's epilogue already did.
+static int enqueue_update(dvo_ctx* ctx, bool tables)
 {
     const Consts& c = ctx->c;
-    const int ntop = c.lv[c.L - 1].n;
-    dim3 tgrid(cdiv(c.max_kf, 64), c.S);
-    k_pose_tables<<<tgrid, 64, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ms, ctx->d_hist, ctx->d_tab);
-    KCHECK();
-    dim3 grid(cdiv(ntop, 256), c.S);
-    k_map_update<<<grid, 256, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ms, ctx->d_hist, ctx->d_tab, ctx->d_flags, ctx->d_blockcnt, ctx->nblk_top);
-    KCHECK();
-    k_map_update_apply<<<grid, 256, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ms, ctx->d_flags, ctx->d_blockcnt, ctx->nblk_top, ctx->d_rng);
-    KCHECK();
+    if (tables) {
+        dim3 tgrid(cdiv(c.max_kf, 64), c.S);
+        k_pose_tables<<<tgrid, 64, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ms, ctx->d_hist, ctx->d_tab);
+        KCHECK();
+    }
+    if (ctx->roi.n <= 0) return DVO_OK;
+    dim3 grid(ctx->roi.nblk, c.S);
+    {
+        KTimer t(ctx, K_MAP_UPDATE);
+        k_map_update<<<grid, 256, 0, ctx->stream>>>(c, ctx->roi, ctx->d_slots, ctx->d_ms, ctx->d_hist, ctx->d_tab, ctx->d_flags, ctx->d_blockcnt);
+        KCHECK();
+    }
+    {
+        KTimer t(ctx, K_MAP_APPLY);
+        k_map_update_apply<<<grid, 256, 0, ctx->stream>>>(c, ctx->roi, ctx->d_slots, ctx->d_ms, ctx->d_flags, ctx->d_blockcnt, ctx->d_rng);
+        KCHECK();
+    }
     return DVO_OK;
 }
 static int enqueue_regularize(dvo_ctx* ctx)
 {
     const Consts& c = ctx->c;
     const int ntop = c.lv[c.L - 1].n;
-    dim3 grid(cdiv(ntop, 256), c.S);
-    k_regularize<<<grid, 256, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ms, ctx->d_tmp);
-    KCHECK();
-    dim3 grid3(cdiv(ntop, 256), c.S, c.L);
-    k_ds_rebuild<<<grid3, 256, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ms, ctx->d_tmp);
-    KCHECK();
+    {
+        KTimer t(ctx, K_REGULARIZE);
+        k_regularize<<<dim3(cdiv(ntop, 256), c.S), 256, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ms, ctx->d_tmp);
+        KCHECK();
+    }
+    {
+        KTimer t(ctx, K_REG_COMMIT);
+        k_regularize_commit<<<dim3(cdiv(ntop, 512), c.S), 256, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ms, ctx->d_tmp);
+        KCHECK();
+    }
     return DVO_OK;
 }
 
@@ -652,8 +742,6 @@ extern "C" int dvo_map_propagate(dvo_ctx* ctx, int ref_slot, int new_slot, const
     KCHECK();
     rc = enqueue_propagate(ctx);
     if (rc) return rc;
-    rc = recull_ds(ctx, new_slot);
-    if (rc) return rc;
     CK(cudaStreamSynchronize(ctx->stream));
     return DVO_OK;
 }
@@ -682,9 +770,7 @@ extern "C" int dvo_map_update(dvo_ctx* ctx, int obj_slot, int ref_slot, const in
     KCHECK();
     k_map_prepare<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_ms, ctx->slots[obj_slot].dev.rel_xi);
     KCHECK();
-    rc = enqueue_update(ctx);
-    if (rc) return rc;
-    rc = recull_ds(ctx, ref_slot); // ref->updateDepthSigma, mapper.cpp:135
+    rc = enqueue_update(ctx, true); // ref->updateDepthSigma (mapper.cpp:135) is implicit: coarser levels are views
     if (rc) return rc;
     const int ntop = c.lv[c.L - 1].n;
     if (mask) CK(cudaMemcpyAsync(mask, ctx->d_flags, (size_t)c.S * ntop, cudaMemcpyDeviceToHost, ctx->stream));
@@ -812,30 +898,27 @@ extern "C" int dvo_vo_push_dev(dvo_ctx* ctx, const float* gray_dev, const float*
             sh.in_use = true;
         }
     }
-    k_vo_begin<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_vo, ctx->d_ms);
-    KCHECK();
-    int rc = build_frame(ctx, -1, gray_dev); // make_shared<Frame>(gray, K, 3, 2), system.hpp:47
+    int rc = build_frame(ctx, -1, gray_dev, ctx->rows_only_staged); // make_shared<Frame>(gray, K, 3, 2), system.hpp:47
+    ctx->rows_only_staged = false;
     if (rc) return rc;
     if (init_depth || init_sigma) {
         rc = set_depth_impl(ctx, -1, init_depth, init_sigma, nullptr, 0);
         if (rc) return rc;
     }
-    // Tracking (system.hpp:57): against each stream's current keyframe; no-op on the first frame
-    rc = enqueue_track(ctx, -1, -1, true, -1.0, -1.0f);
+    // Tracking (system.hpp:57) against each stream's current keyframe (no-op on the first frame), then
+    // Frame::updateXi + Mapper::needNewFrame + setRefFrame in the same kernel's epilogue
+    rc = enqueue_track(ctx, -1, -1, true, -1.0, -1.0f, frame_id, ctx->forced_pending ? ctx->d_forced : nullptr);
     if (rc) return rc;
-    k_vo_decide<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ts, ctx->d_vo, ctx->d_ms, frame_id,
-                                                       ctx->forced_pending ? ctx->d_forced : nullptr);
-    KCHECK();
     ctx->forced_pending = false;
-    // Mapping (system.hpp:67, mapper.cpp:16-33): per stream either propagate or update
-    rc = enqueue_propagate(ctx);
-    if (rc) return rc;
-    rc = enqueue_update(ctx);
-    if (rc) return rc;
-    k_vo_commit<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_vo, ctx->d_ms, ctx->d_hist, frame_id);
-    KCHECK();
-    rc = enqueue_regularize(ctx);
-    if (rc) return rc;
+    // Mapping (system.hpp:67, mapper.cpp:16-33): per stream either propagate or update, then regularize
+    if (frame_id > 0) {
+        rc = enqueue_propagate(ctx);
+        if (rc) return rc;
+        rc = enqueue_update(ctx, false);
+        if (rc) return rc;
+        rc = enqueue_regularize(ctx);
+        if (rc) return rc;
+    }
     if (T_out) {
         k_pose_out<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_vo, ctx->d_small);
         KCHECK();
@@ -849,7 +932,10 @@ extern "C" int dvo_vo_push(dvo_ctx* ctx, const float* gray, const float* init_de
 {
     ARG(gray, "null gray");
     const Consts& c = ctx->c;
-    CK(cudaMemcpyAsync(ctx->d_stage_in, gray, sizeof(float) * (size_t)c.S * c.in_w * c.in_h, cudaMemcpyHostToDevice, ctx->stream));
+    bool rows_only = false;
+    int rc = stage_gray(ctx, gray, &rows_only);
+    if (rc) return rc;
+    ctx->rows_only_staged = rows_only;
     return dvo_vo_push_dev(ctx, ctx->d_stage_in, init_depth, init_sigma, T_out);
 }
 

@@ -1,4 +1,12 @@
 // dvo_internal.cuh — device-visible data model shared by the kernels and the C-ABI layer.
+//
+// HBM layout.  A frame slot keeps ONLY the finest pyramid level of every stream:
+//   gray [S][n_top] float, ds [S][n_top] float2 {depth, sigma}, age [S][n_top] float, xi/rel_xi [S][6].
+// Coarser levels are never materialised: Convert::cullImage is top-left point sampling through
+// Convert::getPixel (convert.cpp:7-20,107-125), and the reference re-culls depth/sigma from the
+// finest map after every map step (frame.cpp:39-61), so level l pixel (x, y) is exactly
+// getPixel(top[(y << t) * W + (x << t)]) with t = L-1-l.  Gradients (Convert::gradiate,
+// convert.cpp:41-75) are two-tap differences of that gray and are recomputed where sampled.
 #pragma once
 #include "../../include/dvo_cuda.h"
 #include "dvo_device.cuh"
@@ -6,8 +14,8 @@
 namespace dvo {
 
 constexpr int MAXL = DVO_MAX_LEVELS;
-constexpr int GN_THREADS = 256;
-constexpr int NACC = 29; // 21 J^T J + 6 J^T (w r) + sum r^2 + valid count
+constexpr int TRK_THREADS = 256; // threads per tracking CTA
+constexpr int NACC = 29;         // 21 J^T J + 6 J^T (w r) + sum r^2 + valid count
 
 // Geometry + constants, passed to kernels by value (__grid_constant__).
 struct Consts {
@@ -30,33 +38,41 @@ struct Consts {
     unsigned int rng_table;
 };
 
-// One frame slot as the device sees it.  All images are stream-major: base + s * n_level.
+// One frame slot as the device sees it.  All images are stream-major: base + s * n_top.
 struct SlotDev {
-    float* gray[MAXL];   // plain gray pyramid            [S][n_l]
-    float4* tex[MAXL];   // {gray, gradX, gradY, 0}        [S][n_l]
-    float2* ds[MAXL];    // {depth, sigma}                 [S][n_l]
-    float* age;          // finest level                   [S][n_top]
-    float* xi;           // Frame::m_xi                    [S][6]
-    float* rel_xi;       // Frame::m_relative_xi           [S][6]
+    float* gray;   // finest-level gray                    [S][n_top]
+    float2* ds;    // finest-level {depth, sigma}          [S][n_top]
+    float* age;    // finest level                         [S][n_top]
+    float* xi;     // Frame::m_xi                          [S][6]
+    float* rel_xi; // Frame::m_relative_xi                 [S][6]
 };
 
-// Per-stream Gauss-Newton state machine (Tracker::track, src/track/tracker.cpp:22-85).
+// A pyramid level seen through the finest-level image: pixel (x, y) -> top[(y << t) * W + (x << t)].
+struct LevelView {
+    int w, h;     // level size
+    int t;        // shift to the finest level
+    int W;        // finest-level row pitch (elements)
+};
+
+// Per-stream Gauss-Newton state (Tracker::track, src/track/tracker.cpp:22-85).
 struct TrackState {
     int level, iter, done, n_total;
     int mode;            // 0: full coarse-to-fine track; 1: single step (Track::optimize)
-    unsigned int ticket; // blocks finished in the current launch
     float xi[6];
     float Tn[12];        // exp(-xi), rows of [R|t]
     double stop_update;
     float stop_residual;
-    int px_total; // pixels swept by this track (sum of level sizes over iterations)
-    const float* obj_gray[MAXL]; // pre-offset by stream
-    const float4* ref_tex[MAXL];
-    const float2* ref_ds[MAXL];
+    int px_total;        // pixels swept by this track (sum of level sizes over iterations)
+    const float* obj_gray;  // finest level, pre-offset by stream
+    const float* ref_gray;
+    const float2* ref_ds;
+    // inter-CTA barrier of the stream's CTA group (only used when a stream is split over > 1 CTA)
+    unsigned int arrive; // monotonic: CTAs that finished accumulating, summed over iterations
+    unsigned int gen;    // iterations whose tail has been published
 };
 
-// Per-stream mapping work descriptor (filled by the host for the granular API, by k_vo_decide
-// for the device-resident VO loop).
+// Per-stream mapping work descriptor (filled by the host for the granular API, by the tracking
+// kernel's epilogue for the device-resident VO loop).
 struct MapState {
     int ref_slot, obj_slot, new_slot;
     int n_hist;
@@ -77,10 +93,10 @@ struct VoState {
     int kf_slot, kf_frame_id, n_kf;
     int need_new, was_keyframe;
     int n_iters;
-    int cur_slot; // slot holding this stream's current frame: vo_base + n_kf (see k_vo_begin)
+    int cur_slot; // slot holding this stream's current frame: vo_base + min(n_kf, max_kf)
     int pad;
     unsigned long long gn_iters;  // Gauss-Newton iterations since dvo_vo_reset
-    unsigned long long gn_pixels; // pixels swept by those iterations (sum of level sizes)
+    unsigned long long gn_pixels; // pixels swept by those iterations
     unsigned long long n_propagate, n_update; // frames mapped by propagate / update
 };
 
@@ -89,5 +105,9 @@ struct PoseTab { // per (stream, age): exp(-r_xi) and -r_xi[0:3] (src/map/mapper
     float t[3];
     float pad;
 };
+
+// slot holding stream s's current VO frame (entry k of the pool = keyframe k of every stream;
+// the frame being processed lives in the entry after the stream's newest keyframe)
+__host__ __device__ __forceinline__ int vo_cur_slot(const Consts& c, int n_kf) { return c.vo_base + (n_kf < c.max_kf ? n_kf : c.max_kf); }
 
 } // namespace dvo

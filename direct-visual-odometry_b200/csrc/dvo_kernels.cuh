@@ -6,53 +6,51 @@
 namespace dvo {
 
 // =============================================================================================
-// Frame construction: Convert::cullImage (convert.cpp:7-20), Convert::gradiate (convert.cpp:41-75),
-// Frame::createScenePyramid (frame.cpp:30-37).  grid = (ceil(n_top/256), S, L)
+// Level views: a coarser level is read through the finest image (dvo_internal.cuh).
 // =============================================================================================
-// Slot of stream s for the frame-construction kernels: a fixed slot (granular API) or, in the VO
-// loop, the stream's own current slot (streams take keyframes at different times, so the current
-// frame of each stream lives in the pool entry after its newest keyframe).
-__device__ __forceinline__ const SlotDev& slot_of(const SlotDev* __restrict__ slots, int fixed, const VoState* __restrict__ vo, int s)
+__device__ __forceinline__ LevelView level_view(const Consts& c, int l)
 {
-    return slots[vo ? vo[s].cur_slot : fixed];
+    LevelView v;
+    v.w = c.lv[l].w; v.h = c.lv[l].h; v.t = c.L - 1 - l; v.W = c.lv[c.L - 1].w;
+    return v;
 }
+__device__ __forceinline__ size_t top_index(const LevelView& v, int x, int y) { return (size_t)(y << v.t) * v.W + (x << v.t); }
+// gray / depth / sigma of level pixel (x, y): the stored value at the finest level, Convert::getPixel
+// (values <= -2 become exactly -2) on every coarser one.
+__device__ __forceinline__ float level_value(const LevelView& v, float raw) { return v.t ? get_pixel_value(raw) : raw; }
 
-__global__ void __launch_bounds__(256) k_cull_gray(const __grid_constant__ Consts c, const float* __restrict__ in,
-                                                   const SlotDev* __restrict__ slots, int fixed, const VoState* __restrict__ vo)
-{
-    const int l = blockIdx.z, s = blockIdx.y;
-    const SlotDev& slot = slot_of(slots, fixed, vo, s);
-    const LevelGeom g = c.lv[l];
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= g.n) return;
-    const int sh = c.culls + (c.L - 1 - l);
-    const int y = i / g.w, x = i - y * g.w;
-    const float v = __ldg(in + (size_t)s * c.in_w * c.in_h + (size_t)(y << sh) * c.in_w + (x << sh));
-    // cull of a cull == direct sample: getPixel maps every value <= -2 to exactly -2 (idempotent)
-    slot.gray[l][(size_t)s * g.n + i] = (sh == 0) ? v : get_pixel_value(v);
-}
-
-__global__ void __launch_bounds__(256) k_build_tex(const __grid_constant__ Consts c, const SlotDev* __restrict__ slots, int fixed,
+// =============================================================================================
+// Frame construction: Frame ctor = Convert::cullImage(gray, culls) (frame.hpp:108-117,
+// convert.cpp:7-20).  One thread per 4 finest-level pixels; the input row is read with a stride of
+// 2^culls elements.  row_shift = culls when `in` holds every input row, 0 when the host staged only
+// the rows that are sampled.   grid = (ceil(n_top / 1024), S)
+// =============================================================================================
+__global__ void __launch_bounds__(256) k_cull_gray(const __grid_constant__ Consts c, const float* __restrict__ in, int in_rows,
+                                                   int row_shift, const SlotDev* __restrict__ slots, int fixed,
                                                    const VoState* __restrict__ vo)
 {
-    const int l = blockIdx.z, s = blockIdx.y;
-    const SlotDev& slot = slot_of(slots, fixed, vo, s);
-    const LevelGeom g = c.lv[l];
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= g.n) return;
-    const int y = i / g.w, x = i - y * g.w;
-    const float* gr = slot.gray[l] + (size_t)s * g.n;
-    const float v = gr[i];
-    float gx = DVO_INV, gy = DVO_INV;
-    if (!(x - 1 <= -1 || x + 1 >= g.w)) {
-        float a = get_pixel_value(gr[i - 1]), b = get_pixel_value(gr[i + 1]);
-        if (!(is_invalid(a) || is_invalid(b))) gx = b - a;
+    const int s = blockIdx.y;
+    const SlotDev& slot = slots[vo ? vo_cur_slot(c, vo[s].n_kf) : fixed];
+    const LevelGeom g = c.lv[c.L - 1];
+    const float* __restrict__ src = in + (size_t)s * c.in_w * in_rows;
+    float* __restrict__ dst = slot.gray + (size_t)s * g.n;
+    const int sh = c.culls;
+    const int base = blockIdx.x * 1024 + threadIdx.x;
+    float v[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int i = base + k * 256;
+        v[k] = 0.f;
+        if (i < g.n) {
+            const int y = i / g.w, x = i - y * g.w;
+            v[k] = __ldcs(src + (size_t)(y << row_shift) * c.in_w + (x << sh)); // streamed once: evict-first
+        }
     }
-    if (!(y - 1 <= -1 || y + 1 >= g.h)) {
-        float a = get_pixel_value(gr[i - g.w]), b = get_pixel_value(gr[i + g.w]);
-        if (!(is_invalid(a) || is_invalid(b))) gy = b - a;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int i = base + k * 256;
+        if (i < g.n) dst[i] = (sh == 0) ? v[k] : get_pixel_value(v[k]);
     }
-    slot.tex[l][(size_t)s * g.n + i] = make_float4(v, gx, gy, 0.f);
 }
 
 // depth / sigma / age upload (Frame 6-arg ctor frame.hpp:91-106, updateDepthSigmaAge frame.cpp:47-54).
@@ -63,13 +61,13 @@ __global__ void __launch_bounds__(256) k_set_top(const __grid_constant__ Consts 
                                                  int shift)
 {
     const int s = blockIdx.y;
-    const SlotDev& slot = slot_of(slots, fixed, vo, s);
+    const SlotDev& slot = slots[vo ? vo_cur_slot(c, vo[s].n_kf) : fixed];
     const LevelGeom g = c.lv[c.L - 1];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= g.n) return;
     const int y = i / g.w, x = i - y * g.w;
     const size_t src = (size_t)s * sw * sh_ + (size_t)(y << shift) * sw + (x << shift);
-    float2* ds = slot.ds[c.L - 1] + (size_t)s * g.n;
+    float2* ds = slot.ds + (size_t)s * g.n;
     float2 v = ds[i];
     if (depth) { float d = depth[src]; v.x = shift ? get_pixel_value(d) : d; }
     if (sigma) { float d = sigma[src]; v.y = shift ? get_pixel_value(d) : d; }
@@ -77,69 +75,109 @@ __global__ void __launch_bounds__(256) k_set_top(const __grid_constant__ Consts 
     if (age) { float d = age[src]; slot.age[(size_t)s * g.n + i] = shift ? get_pixel_value(d) : d; }
 }
 
-// Re-cull the coarser depth/sigma levels from the finest (frame.cpp:39-61).
-// grid = (ceil(n_{L-2}/256), S, L-1)
-__global__ void __launch_bounds__(256) k_cull_ds(const __grid_constant__ Consts c, const SlotDev* __restrict__ slots, int fixed,
-                                                 const VoState* __restrict__ vo)
+// Convert::gradiate (convert.cpp:41-75) of level pixel (x, y), recomputed from the gray image.
+__device__ __forceinline__ float grad_x_at(const float* __restrict__ gray, const LevelView& v, int x, int y)
 {
-    const int l = blockIdx.z, s = blockIdx.y;
-    const SlotDev& slot = slot_of(slots, fixed, vo, s);
-    const LevelGeom g = c.lv[l];
-    const LevelGeom gt = c.lv[c.L - 1];
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= g.n) return;
-    const int t = c.L - 1 - l;
-    const int y = i / g.w, x = i - y * g.w;
-    const float2 v = slot.ds[c.L - 1][(size_t)s * gt.n + (size_t)(y << t) * gt.w + (x << t)];
-    slot.ds[l][(size_t)s * g.n + i] = make_float2(get_pixel_value(v.x), get_pixel_value(v.y));
+    if (x - 1 <= -1 || x + 1 >= v.w) return DVO_INV;
+    const float a = __ldg(gray + top_index(v, x - 1, y)), b = __ldg(gray + top_index(v, x + 1, y));
+    if (is_invalid(a) || is_invalid(b)) return DVO_INV;
+    return b - a;
+}
+__device__ __forceinline__ float grad_y_at(const float* __restrict__ gray, const LevelView& v, int x, int y)
+{
+    if (y - 1 <= -1 || y + 1 >= v.h) return DVO_INV;
+    const float a = __ldg(gray + top_index(v, x, y - 1)), b = __ldg(gray + top_index(v, x, y + 1));
+    if (is_invalid(a) || is_invalid(b)) return DVO_INV;
+    return b - a;
 }
 
-// unpack one image component for download.  grid = (ceil(n_l/256), S)
+// one image component of one level for download.  grid = (ceil(n_l/256), S)
 __global__ void __launch_bounds__(256) k_extract(const __grid_constant__ Consts c, SlotDev slot, int l, int kind, float* __restrict__ out)
 {
     const int s = blockIdx.y;
     const LevelGeom g = c.lv[l];
+    const LevelView v = level_view(c, l);
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= g.n) return;
-    const size_t o = (size_t)s * g.n + i;
-    float v;
+    const int y = i / g.w, x = i - y * g.w;
+    const size_t nt = (size_t)c.lv[c.L - 1].n;
+    const size_t ti = (size_t)s * nt + top_index(v, x, y);
+    float r;
     switch (kind) {
-    case DVO_IMG_GRAY: v = slot.gray[l][o]; break;
-    case DVO_IMG_DEPTH: v = slot.ds[l][o].x; break;
-    case DVO_IMG_SIGMA: v = slot.ds[l][o].y; break;
-    case DVO_IMG_GRADX: v = slot.tex[l][o].y; break;
-    case DVO_IMG_GRADY: v = slot.tex[l][o].z; break;
-    default: v = slot.age[o]; break;
+    case DVO_IMG_GRAY: r = level_value(v, slot.gray[ti]); break;
+    case DVO_IMG_DEPTH: r = level_value(v, slot.ds[ti].x); break;
+    case DVO_IMG_SIGMA: r = level_value(v, slot.ds[ti].y); break;
+    case DVO_IMG_GRADX: r = grad_x_at(slot.gray + (size_t)s * nt, v, x, y); break;
+    case DVO_IMG_GRADY: r = grad_y_at(slot.gray + (size_t)s * nt, v, x, y); break;
+    default: r = slot.age[ti]; break;
     }
-    out[o] = v;
+    out[(size_t)s * g.n + i] = r;
 }
 
 // =============================================================================================
-// Sampling of the {gray, gx, gy} texel array at one warped point: Convert::getSubpixel for the
-// gray channel (with the repair automaton) and Convert::getSubpixelFromDense for the gradients
-// share x0,y0,h,v and the four taps (src/core/convert.cpp:77-105,128-177).
+// Sampling of {gray, gradX, gradY} of one level at a warped point.  Convert::getSubpixel for the
+// gray channel (with the invalid-tap repair automaton) and Convert::getSubpixelFromDense for the two
+// gradients share x0, y0, h, v and the 2x2 footprint (src/core/convert.cpp:77-105,128-177); the
+// gradients of the four footprint pixels are central differences of the 12 gray values around it.
+//            x0-1  x0   x1   x0+2
+//   y0-1            a0   a1
+//   y0        bm    b0   b1   b2
+//   y1        cm    c0   c1   c2
+//   y0+2            d0   d1
 // =============================================================================================
 struct Sample3 {
     float I, gx, gy;
-    bool in; // (x0,y0) in range
+    bool in; // (x0, y0) in range
 };
-__device__ __forceinline__ Sample3 sample_tex(const float4* __restrict__ tex, int w, int h, float px, float py)
+template <bool WANT_GRAD>
+__device__ __forceinline__ Sample3 sample_level(const float* __restrict__ gray, const LevelView& lv, float px, float py)
 {
     Sample3 r;
     r.I = r.gx = r.gy = DVO_INV;
     const int x0 = trunc_x86(px), y0 = trunc_x86(py);
+    const int w = lv.w, h = lv.h;
     r.in = in_range(x0, y0, w, h);
     if (!r.in) return r;
     const float hh = px - (float)x0, v = py - (float)y0;
     const bool xin = (x0 + 1) < w, yin = (y0 + 1) < h;
-    const float4* p = tex + (size_t)y0 * w + x0;
-    const float4 t0 = __ldg(p);
-    const float4 t1 = xin ? __ldg(p + 1) : t0;
-    const float4 t2 = yin ? __ldg(p + w) : t0;
-    const float4 t3 = (xin && yin) ? __ldg(p + w + 1) : t0;
-    r.gx = bilerp(t0.y, t1.y, t2.y, t3.y, hh, v);
-    r.gy = bilerp(t0.z, t1.z, t2.z, t3.z, hh, v);
-    float g[4] = {t0.x, t1.x, t2.x, t3.x};
+    const float* p = gray + top_index(lv, x0, y0);
+    const int dx = 1 << lv.t;
+    const ptrdiff_t dy = (ptrdiff_t)lv.W << lv.t;
+    const float b0 = level_value(lv, __ldg(p));
+    const float b1 = xin ? level_value(lv, __ldg(p + dx)) : b0;
+    const float c0 = yin ? level_value(lv, __ldg(p + dy)) : b0;
+    const float c1 = (xin && yin) ? level_value(lv, __ldg(p + dy + dx)) : b0;
+    if (WANT_GRAD) {
+        // gradient of a footprint pixel: INVALID on the image border or next to an invalid tap
+        const bool xl = x0 - 1 >= 0, xr = x0 + 2 < w, yu = y0 - 1 >= 0, yd = y0 + 2 < h;
+        const float bm = xl ? __ldg(p - dx) : DVO_INV;
+        const float b2 = xr ? __ldg(p + 2 * dx) : DVO_INV;
+        const float a0 = yu ? __ldg(p - dy) : DVO_INV;
+        const float d0 = yd ? __ldg(p + 2 * dy) : DVO_INV;
+        float gx00 = DVO_INV, gy00 = DVO_INV; // texel (x0, y0)
+        if (xl && xin && !(is_invalid(bm) || is_invalid(b1))) gx00 = b1 - bm;
+        if (yu && yin && !(is_invalid(a0) || is_invalid(c0))) gy00 = c0 - a0;
+        float gx10 = gx00, gy10 = gy00, gx01 = gx00, gy01 = gy00, gx11 = gx00, gy11 = gy00;
+        if (xin) { // texel (x1, y0)
+            const float a1 = yu ? __ldg(p - dy + dx) : DVO_INV;
+            gx10 = (xr && !(is_invalid(b0) || is_invalid(b2))) ? b2 - b0 : DVO_INV;
+            gy10 = (yu && yin && !(is_invalid(a1) || is_invalid(c1))) ? c1 - a1 : DVO_INV;
+        }
+        if (yin) { // texel (x0, y1)
+            const float cm = xl ? __ldg(p + dy - dx) : DVO_INV;
+            gx01 = (xl && xin && !(is_invalid(cm) || is_invalid(c1))) ? c1 - cm : DVO_INV;
+            gy01 = (yd && !(is_invalid(b0) || is_invalid(d0))) ? d0 - b0 : DVO_INV;
+        }
+        if (xin && yin) { // texel (x1, y1)
+            const float c2 = xr ? __ldg(p + dy + 2 * dx) : DVO_INV;
+            const float d1 = yd ? __ldg(p + 2 * dy + dx) : DVO_INV;
+            gx11 = (xr && !(is_invalid(c0) || is_invalid(c2))) ? c2 - c0 : DVO_INV;
+            gy11 = (yd && !(is_invalid(b1) || is_invalid(d1))) ? d1 - b1 : DVO_INV;
+        }
+        r.gx = bilerp(gx00, gx10, gx01, gx11, hh, v);
+        r.gy = bilerp(gy00, gy10, gy01, gy11, hh, v);
+    }
+    float g[4] = {b0, b1, c0, c1};
     if (!(is_valid(g[0]) && is_valid(g[1]) && is_valid(g[2]) && is_valid(g[3]))) {
         if (!repair_taps(g)) return r; // I stays INVALID
     }
@@ -153,18 +191,20 @@ __global__ void __launch_bounds__(256) k_warp_image(const __grid_constant__ Cons
 {
     const int s = blockIdx.y;
     const LevelGeom g = c.lv[l];
+    const LevelView lv = level_view(c, l);
     __shared__ float T[12];
     if (threadIdx.x == 0) se3_exp_neg12(xi + 6 * s, T);
     __syncthreads();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= g.n) return;
     const int y = i / g.w, x = i - y * g.w;
-    const float d = ref.ds[l][(size_t)s * g.n + i].x;
+    const size_t nt = (size_t)c.lv[c.L - 1].n;
+    const float d = level_value(lv, ref.ds[(size_t)s * nt + top_index(lv, x, y)].x);
     float p = DVO_INV;
     if (!(fabsf(d) < DVO_EPS)) {
         float wx, wy;
         warp_point(T, g, (float)x, (float)y, d, wx, wy);
-        p = sample_tex(ref.tex[l] + (size_t)s * g.n, g.w, g.h, wx, wy).I;
+        p = sample_level<false>(ref.gray + (size_t)s * nt, lv, wx, wy).I;
     }
     out[(size_t)s * g.n + i] = p;
 }
@@ -260,149 +300,51 @@ __device__ inline void solve6(const double* H, const double* b, double* x)
 }
 
 // =============================================================================================
-// The fused Gauss-Newton iteration: Transform::warpImage + Track::optimize + the iteration tail
-// of Tracker::track (src/core/transform.cpp:35-51, src/track/optimize.cpp:10-99,
-// src/track/tracker.cpp:42-73) for every stream, one launch per iteration.
-//   grid = (blocks_x, S), 256 threads, PPT pixels per thread (contiguous 256*PPT chunk per block).
-// Per pixel: gates -> warp -> 4 texel taps -> residual, weight, 1x6 Jacobian -> 29 fp64 sums.
-// Block partials are written to global memory; the last block of each stream (ticket) reduces
-// them in a fixed order (deterministic), solves the 6x6 system, composes the pose, applies the
-// stop rules and advances the per-stream state machine — no host round trip between iterations.
+// Tracking: Tracker::track (src/track/tracker.cpp:22-85) as ONE persistent launch per frame.
+//   grid = (B, S): stream s owns CTAs (0..B-1, s); B = 1 when there are enough streams to fill the
+//   GPU, otherwise the stream's pixels are split over B co-resident CTAs (cooperative launch) that
+//   meet at a global-memory barrier once per Gauss-Newton iteration.
+// Per iteration (Transform::warpImage + Track::optimize fused, transform.cpp:35-51,
+// optimize.cpp:10-99): every thread walks its share of the level's (ROI) pixels — gates -> warp ->
+// 12 gray taps -> residual, weight, 1x6 Jacobian -> 29 fp64 sums — then the sums are reduced in a
+// fixed order (warp shuffle, shared memory, block partials) and the stream's leader thread solves the
+// 6x6 system, composes the pose, applies the stop rules and publishes the next iteration's level and
+// exp(-xi).  No host round trip, no empty launches.  In VO mode the leader finishes with
+// Frame::updateXi + Mapper::needNewFrame + FrameHistory::setRefFrame and the pose table of
+// Mapper::update (system.hpp:57-58, mapper.cpp:16-60,107).
 // =============================================================================================
-struct GnArgs {
+struct TrackArgs {
     TrackState* st;       // [S]
-    double* partials;     // [S][max_blocks][32]
-    int max_blocks;
+    double* partials;     // [S][B][32]
+    int B;
     dvo_iter_log* log;    // [S][log_cap]
     int log_cap;
-    uint8_t* mask;        // optional [S][n_level] (single-step mode)
-    int ppt;
+    uint8_t* mask;        // optional [S][n_level] (single-step mode; pre-zeroed)
+    // granular mode (vo == nullptr)
+    int obj_slot, ref_slot, mode, level0;
+    const float* xi0;     // [S][6] or nullptr
+    double stop_update;
+    float stop_residual;
+    // VO mode
+    const SlotDev* slots;
+    VoState* vo;
+    MapState* ms;
+    int* hist;
+    PoseTab* tab;
+    int frame_id;
+    const float* forced_rel;
 };
 
-template <int PPT>
-__global__ void __launch_bounds__(GN_THREADS) k_gn_step(const __grid_constant__ Consts c, const GnArgs a)
+struct TrackCtl { // per-CTA copy of the stream's iteration state
+    int level, iter, done;
+    float T[12];
+};
+
+// One Gauss-Newton tail: solve, compose, log, stop rules (optimize.cpp:92-98, tracker.cpp:46-73).
+__device__ __noinline__ void gn_tail(const Consts& c, const TrackArgs& a, TrackState* st, int s, const double* stot, TrackCtl* ctl)
 {
-    const int s = blockIdx.y;
-    TrackState* __restrict__ st = a.st + s;
-    if (st->done) return;
-    const int level = st->level;
-    const LevelGeom g = c.lv[level];
-    const int nb = (g.n + GN_THREADS * PPT - 1) / (GN_THREADS * PPT);
-    if ((int)blockIdx.x >= nb) return;
-
-    __shared__ float sT[12];
-    __shared__ double sred[GN_THREADS / 32][NACC + 1];
-    __shared__ double stot[NACC + 3];
-    __shared__ int s_last;
-    if (threadIdx.x < 12) sT[threadIdx.x] = st->Tn[threadIdx.x];
-    const float* __restrict__ obj_gray = st->obj_gray[level];
-    const float4* __restrict__ tex = st->ref_tex[level];
-    const float2* __restrict__ ds = st->ref_ds[level];
-    const bool roi = (level == c.roi_level);
-    float step = c.step_default; // optimize.cpp:22-26
-    if (level == 1) step = c.step_level1;
-    if (level == 2) step = c.step_level2;
-    __syncthreads();
-
-    double acc[NACC];
-#pragma unroll
-    for (int k = 0; k < NACC; k++) acc[k] = 0.0;
-
-#pragma unroll
-    for (int k = 0; k < PPT; k++) {
-        const int i = (blockIdx.x * PPT + k) * GN_THREADS + threadIdx.x;
-        if (i >= g.n) break;
-        const int y = i / g.w, x = i - y * g.w;
-        bool ok = true;
-        if (roi) ok = !(x < c.roi_x0 || x > c.roi_x1 || y < c.roi_y0 || y > c.roi_y1); // optimize.cpp:33-36
-        float2 dsv = make_float2(0.f, 0.f);
-        float I1 = DVO_INV;
-        if (ok) {
-            dsv = __ldg(ds + i);
-            I1 = __ldg(obj_gray + i);
-            ok = !(dsv.x < c.min_depth_f) && !is_invalid(I1); // optimize.cpp:39,46
-        }
-        if (ok) {
-            const float depth = dsv.x;
-            float X, Y, Z;
-            back_project(g, (float)x, (float)y, depth, X, Y, Z);
-            const float tx = (sT[0] * X + sT[1] * Y + sT[2] * Z) + sT[3];
-            const float ty = (sT[4] * X + sT[5] * Y + sT[6] * Z) + sT[7];
-            const float tz = (sT[8] * X + sT[9] * Y + sT[10] * Z) + sT[11];
-            const float wx = tx * g.fx / tz + g.cx;
-            const float wy = ty * g.fy / tz + g.cy;
-            const Sample3 sm = sample_tex(tex, g.w, g.h, wx, wy);
-            // I_2 valid (optimize.cpp:46); warped point inside the image (:52-56); gradients valid (:61)
-            ok = sm.in && !is_invalid(sm.I) && !(wx < 0 || wy < 0 || (float)g.w <= wx || (float)g.h <= wy)
-                 && !(is_invalid(sm.gx) || is_invalid(sm.gy));
-            if (ok) {
-                const float fgx = g.fx * sm.gx, fgy = g.fy * sm.gy; // optimize.cpp:67-77
-                const float xz = X / Z, yz = Y / Z;
-                float J[6];
-                J[0] = fgx / Z;
-                J[1] = fgy / Z;
-                J[2] = -(fgx * X + fgy * Y) / Z / Z;
-                J[3] = -fgx * xz * yz - fgy * (1.0f + yz * yz);
-                J[4] = fgx * (1.0f + xz * xz) + fgy * xz * yz;
-                J[5] = (-fgx * yz + fgy * xz);
-                const float r = sm.I - I1;
-                const float sg = (dsv.y < c.sigma_lo) ? c.sigma_lo : (c.sigma_hi < dsv.y) ? c.sigma_hi : dsv.y; // std::clamp :83
-                const float bw = r * (step / sg);
-                double Jd[6];
-#pragma unroll
-                for (int q = 0; q < 6; q++) Jd[q] = (double)J[q];
-                int idx = 0;
-#pragma unroll
-                for (int p = 0; p < 6; p++)
-#pragma unroll
-                    for (int q = p; q < 6; q++) { acc[idx] = fma(Jd[p], Jd[q], acc[idx]); idx++; }
-                const double bd = (double)bw;
-#pragma unroll
-                for (int q = 0; q < 6; q++) acc[21 + q] = fma(Jd[q], bd, acc[21 + q]);
-                acc[27] += (double)(r * r);
-                acc[28] += 1.0;
-            }
-        }
-        if (a.mask) a.mask[(size_t)s * g.n + i] = ok ? 1 : 0;
-    }
-
-    // ---- block reduction (fixed order => deterministic) ----
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-#pragma unroll
-    for (int k = 0; k < NACC; k++) {
-        double v = acc[k];
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
-        if (lane == 0) sred[warp][k] = v;
-    }
-    __syncthreads();
-    double* mypart = a.partials + ((size_t)s * a.max_blocks + blockIdx.x) * 32;
-    if (threadIdx.x < NACC) {
-        double v = 0;
-#pragma unroll
-        for (int wv = 0; wv < GN_THREADS / 32; wv++) v += sred[wv][threadIdx.x];
-        mypart[threadIdx.x] = v;
-    }
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        unsigned int t = atomicAdd(&st->ticket, 1u);
-        s_last = (t == (unsigned)(nb - 1));
-    }
-    __syncthreads();
-    if (!s_last) return;
-
-    // ---- tail: last block of this stream ----
-    __threadfence();
-    if (threadIdx.x < NACC) {
-        const double* base = a.partials + (size_t)s * a.max_blocks * 32 + threadIdx.x;
-        double v = 0;
-        for (int b = 0; b < nb; b++) v += __ldcg(base + (size_t)b * 32);
-        stot[threadIdx.x] = v;
-    }
-    __syncthreads();
-    if (threadIdx.x != 0) return;
-
+    const int level = ctl->level;
+    const LevelGeom& g = c.lv[level];
     const int valid = (int)stot[28];
     float upd[6] = {0, 0, 0, 0, 0, 0};
     float residual = -1.0f; // optimize.cpp:92-93
@@ -419,7 +361,7 @@ __global__ void __launch_bounds__(GN_THREADS) k_gn_step(const __grid_constant__ 
     float xi[6], xin[6];
     for (int q = 0; q < 6; q++) xi[q] = st->xi[q];
     const int n_total = st->n_total;
-    bool advance_pose = (st->mode == 0);
+    const bool advance_pose = (st->mode == 0);
     if (advance_pose) {
         se3_concatenate(xi, upd, xin); // tracker.cpp:46
         bool nan = false;
@@ -429,60 +371,314 @@ __global__ void __launch_bounds__(GN_THREADS) k_gn_step(const __grid_constant__ 
     }
     if (a.log && n_total < a.log_cap) {
         dvo_iter_log* L = a.log + (size_t)s * a.log_cap + n_total;
-        L->level = level; L->iteration = st->iter; L->valid_pixels = valid; L->residual = residual;
+        L->level = level; L->iteration = ctl->iter; L->valid_pixels = valid; L->residual = residual;
         for (int q = 0; q < 6; q++) { L->update[q] = upd[q]; L->xi_after[q] = xi[q]; }
     }
     st->n_total = n_total + 1;
     st->px_total += g.n;
-    st->ticket = 0;
     if (!advance_pose) {
-        st->done = 1;
-        return;
+        ctl->done = 1;
+    } else {
+        for (int q = 0; q < 6; q++) st->xi[q] = xi[q];
+        se3_exp_neg12(xi, ctl->T); // stuff.update(xi): the next iteration warps with exp(-xi)
+        // stop rules, tracker.cpp:68-70 (time budget never reached)
+        const bool stop = (norm_n(upd, 6) < st->stop_update) || (residual < st->stop_residual);
+        int iter = ctl->iter + 1;
+        if (stop || iter >= c.max_iter) {
+            iter = 0;
+            ctl->level = level + 1;
+            if (ctl->level >= c.L) ctl->done = 1;
+        }
+        ctl->iter = iter;
     }
-    for (int q = 0; q < 6; q++) st->xi[q] = xi[q];
-    float Tn[12];
-    se3_exp_neg12(xi, Tn); // stuff.update(xi): the next iteration warps with exp(-xi)
-    for (int q = 0; q < 12; q++) st->Tn[q] = Tn[q];
-    // stop rules, tracker.cpp:68-70 (time budget never reached)
-    const bool stop = (norm_n(upd, 6) < st->stop_update) || (residual < st->stop_residual);
-    int iter = st->iter + 1;
-    if (stop || iter >= c.max_iter) {
-        iter = 0;
-        const int nl = level + 1;
-        st->level = nl;
-        if (nl >= c.L) st->done = 1;
-    }
-    st->iter = iter;
+    // publish for the other CTAs of the stream and for the host
+    st->level = ctl->level; st->iter = ctl->iter; st->done = ctl->done;
+    for (int q = 0; q < 12; q++) st->Tn[q] = ctl->T[q];
 }
 
-// per-stream tracker reset (xi = 0, level 0) — Tracker::track prologue, tracker.cpp:28-40.
-// obj_slot / ref_slot: if ref_per_stream != nullptr the keyframe slot is taken from VoState.
-__global__ void k_track_init(const __grid_constant__ Consts c, TrackState* st, const SlotDev* __restrict__ slots, int obj_slot,
-                             int ref_slot, const VoState* __restrict__ vo, int mode, int level, const float* __restrict__ xi0,
-                             double stop_update, float stop_residual)
+// pose table of Mapper::update (mapper.cpp:107): r_xi = concatenate(obj.m_xi, -born.m_xi) depends on the
+// age only, so it is hoisted out of the pixel loop.  One entry per call.
+__device__ inline void pose_table_entry(const Consts& c, const SlotDev* __restrict__ slots, const MapState* m, const int* __restrict__ hist,
+                                        PoseTab* __restrict__ tab, int s, int age)
 {
-    const int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= c.S) return;
-    TrackState* t = st + s;
-    const int rs = vo ? vo[s].kf_slot : ref_slot;
-    if (vo) obj_slot = vo[s].cur_slot;
-    const SlotDev o = slots[obj_slot];
-    const SlotDev r = slots[rs < 0 ? obj_slot : rs];
-    for (int l = 0; l < c.L; l++) {
-        const size_t off = (size_t)s * c.lv[l].n;
-        t->obj_gray[l] = o.gray[l] + off;
-        t->ref_tex[l] = r.tex[l] + off;
-        t->ref_ds[l] = r.ds[l] + off;
+    const int born_slot = hist[(size_t)s * c.max_kf + (m->n_hist - 1 - age)]; // FrameHistory::operator[] frame.hpp:176
+    const float* oxi = slots[m->obj_slot].xi + 6 * s;
+    const float* bxi = slots[born_slot].xi + 6 * s;
+    float a6[6], nb[6], r[6];
+    for (int q = 0; q < 6; q++) { a6[q] = oxi[q]; nb[q] = -bxi[q]; }
+    se3_concatenate(a6, nb, r);
+    PoseTab* t = tab + (size_t)s * c.max_kf + age;
+    se3_exp_neg12(r, t->T);
+    t->t[0] = -r[0]; t->t[1] = -r[1]; t->t[2] = -r[2];
+}
+
+// After tracking (one thread per stream): Frame::updateXi (frame.cpp:7-14), Mapper::needNewFrame
+// (mapper.cpp:45-60) and FrameHistory::setRefFrame (frame.hpp:151-157).  The keyframe list is appended
+// here already; propagate / update work from the snapshot (ref_slot, n_hist) taken before.
+__device__ __noinline__ void vo_decide(const Consts& c, const TrackArgs& a, const TrackState* st, int s)
+{
+    VoState* v = a.vo + s;
+    MapState* m = a.ms + s;
+    const int cur_slot = vo_cur_slot(c, v->n_kf);
+    v->cur_slot = cur_slot;
+    const SlotDev cur = a.slots[cur_slot];
+    m->valid_update = 0; m->n_reject = 0; m->ticket = 0;
+    if (v->kf_slot < 0) { // first frame: m_history.setRefFrame(frame); return identity (system.hpp:49-54)
+        for (int q = 0; q < 6; q++) { cur.xi[6 * s + q] = 0.f; cur.rel_xi[6 * s + q] = 0.f; }
+        m->do_propagate = 0; m->do_update = 0; m->do_regularize = 0;
+        v->need_new = 1; v->was_keyframe = 1; v->n_iters = 0;
+        a.hist[(size_t)s * c.max_kf] = cur_slot;
+        v->n_kf = 1; v->kf_slot = cur_slot; v->kf_frame_id = a.frame_id;
+        m->reg_slot = cur_slot;
+        return;
     }
-    float xi[6];
-    for (int q = 0; q < 6; q++) xi[q] = xi0 ? xi0[6 * s + q] : 0.f;
-    for (int q = 0; q < 6; q++) t->xi[q] = xi[q];
-    float Tn[12];
-    se3_exp_neg12(xi, Tn);
-    for (int q = 0; q < 12; q++) t->Tn[q] = Tn[q];
-    t->level = level; t->iter = 0; t->n_total = 0; t->px_total = 0; t->mode = mode; t->ticket = 0;
-    t->done = (vo && rs < 0) ? 1 : 0;
-    t->stop_update = stop_update; t->stop_residual = stop_residual;
+    float rel[6], kxi[6], xi[6];
+    const SlotDev kf = a.slots[v->kf_slot];
+    // forced_rel: the caller supplies the relative pose (teacher-forced parity runs, external pose
+    // priors); the tracker's own result stays available in the iteration log.
+    for (int q = 0; q < 6; q++) { rel[q] = a.forced_rel ? a.forced_rel[6 * s + q] : st->xi[q]; kxi[q] = kf.xi[6 * s + q]; }
+    se3_concatenate(kxi, rel, xi);
+    for (int q = 0; q < 6; q++) { cur.xi[6 * s + q] = xi[q]; cur.rel_xi[6 * s + q] = rel[q]; }
+    v->n_iters = st->n_total;
+    v->gn_iters += (unsigned long long)st->n_total;
+    v->gn_pixels += (unsigned long long)st->px_total;
+    bool need = false;
+    if (norm_n(rel, 3) > (double)c.min_movement) need = true;          // mapper.cpp:48-52
+    else if (a.frame_id - v->kf_frame_id >= c.max_forward) need = true; // mapper.cpp:53-56
+    v->need_new = need ? 1 : 0;
+    if (need) v->n_propagate++; else v->n_update++;
+    v->was_keyframe = need ? 1 : 0;
+    m->ref_slot = v->kf_slot; m->obj_slot = cur_slot; m->new_slot = cur_slot;
+    m->n_hist = v->n_kf;
+    m->do_propagate = need ? 1 : 0;
+    m->do_update = need ? 0 : 1;
+    m->do_regularize = 1;
+    float T[16];
+    se3_exp(rel, T);
+    for (int q = 0; q < 12; q++) m->Trel[q] = T[q];
+    m->rel_z = rel[2];
+    if (need) {
+        if (v->n_kf >= c.max_kf) {
+            atomicCAS(&m->err, 0, (int)DVO_ERR_HISTORY);
+        } else {
+            a.hist[(size_t)s * c.max_kf + v->n_kf] = cur_slot;
+            v->n_kf += 1;
+            v->kf_slot = cur_slot;
+            v->kf_frame_id = a.frame_id;
+        }
+    }
+    m->reg_slot = v->kf_slot;
+}
+
+__device__ __forceinline__ unsigned int ld_volatile_u32(const unsigned int* p) { return *(const volatile unsigned int*)p; }
+
+__global__ void __launch_bounds__(TRK_THREADS, 2) k_track(const __grid_constant__ Consts c, const TrackArgs a)
+{
+    const int s = blockIdx.y, b = blockIdx.x, B = a.B;
+    const int tid = threadIdx.x;
+    const bool leader = (b == 0);
+    TrackState* __restrict__ st = a.st + s;
+
+    __shared__ TrackCtl ctl;
+    __shared__ double sred[TRK_THREADS / 32][NACC + 1];
+    __shared__ double stot[32];
+    __shared__ const float* s_obj;
+    __shared__ const float* s_ref;
+    __shared__ const float2* s_ds;
+    __shared__ unsigned int s_gen0;
+
+    // ---- prologue: Tracker::track's xi = 0, level 0 (tracker.cpp:28-40); every CTA of the stream
+    // derives the same initial state, the leader also publishes it for the host.
+    if (tid == 0) {
+        int obj_slot = a.obj_slot, ref_slot = a.ref_slot;
+        int done = 0;
+        if (a.vo) {
+            // All streams of a context are in lock-step, so "first frame" is a launch-wide fact passed by
+            // the host (frame_id == 0) — it must not be read from VoState, which the stream's leader CTA
+            // rewrites in its epilogue while a late sibling CTA may still be in this prologue.
+            if (a.frame_id == 0) { obj_slot = ref_slot = c.vo_base; done = 1; } // nothing to track against
+            else { obj_slot = vo_cur_slot(c, a.vo[s].n_kf); ref_slot = a.vo[s].kf_slot; }
+        }
+        const size_t off = (size_t)s * c.lv[c.L - 1].n;
+        s_obj = a.slots[obj_slot].gray + off;
+        s_ref = a.slots[ref_slot].gray + off;
+        s_ds = a.slots[ref_slot].ds + off;
+        float xi[6];
+        for (int q = 0; q < 6; q++) xi[q] = a.xi0 ? a.xi0[6 * s + q] : 0.f;
+        se3_exp_neg12(xi, ctl.T);
+        ctl.level = a.level0; ctl.iter = 0; ctl.done = done;
+        s_gen0 = (B > 1) ? ld_volatile_u32(&st->gen) : 0u;
+        if (leader) {
+            for (int q = 0; q < 6; q++) st->xi[q] = xi[q];
+            for (int q = 0; q < 12; q++) st->Tn[q] = ctl.T[q];
+            st->level = ctl.level; st->iter = 0; st->done = done; st->n_total = 0; st->px_total = 0; st->mode = a.mode;
+            st->stop_update = a.stop_update; st->stop_residual = a.stop_residual;
+            st->obj_gray = s_obj; st->ref_gray = s_ref; st->ref_ds = s_ds;
+        }
+    }
+    __syncthreads();
+    const float* __restrict__ obj_gray = s_obj;
+    const float* __restrict__ ref_gray = s_ref;
+    const float2* __restrict__ ref_ds = s_ds;
+    const unsigned int gen0 = s_gen0;
+    unsigned int epoch = 0;
+
+    while (!ctl.done) {
+        const int level = ctl.level;
+        const LevelGeom g = c.lv[level];
+        const LevelView lv = level_view(c, level);
+        float T[12];
+#pragma unroll
+        for (int q = 0; q < 12; q++) T[q] = ctl.T[q];
+        float step = c.step_default; // optimize.cpp:22-26
+        if (level == 1) step = c.step_level1;
+        if (level == 2) step = c.step_level2;
+        // pixels of this iteration: the whole level, or the ROI of optimize.cpp:33-36
+        int rx0 = 0, rx1 = g.w - 1, ry0 = 0, ry1 = g.h - 1;
+        if (level == c.roi_level) {
+            rx0 = max(rx0, c.roi_x0); rx1 = min(rx1, c.roi_x1); ry0 = max(ry0, c.roi_y0); ry1 = min(ry1, c.roi_y1);
+        }
+        const int rw = rx1 - rx0 + 1, rh = ry1 - ry0 + 1;
+        const int count = (rw > 0 && rh > 0) ? rw * rh : 0;
+        const int per = (count + B - 1) / B;
+        const int j0 = b * per, j1 = min(count, j0 + per);
+
+        double acc[NACC];
+#pragma unroll
+        for (int k = 0; k < NACC; k++) acc[k] = 0.0;
+
+        if (j0 + tid < j1) {
+            int j = j0 + tid;
+            int y = ry0 + j / rw, x = rx0 + (j - (j / rw) * rw);
+            const int sx = TRK_THREADS % rw, sy = TRK_THREADS / rw;
+            for (; j < j1; j += TRK_THREADS) {
+                const size_t ti = top_index(lv, x, y);
+                const float2 dsr = __ldg(ref_ds + ti);
+                const float depth = level_value(lv, dsr.x);
+                const float I1 = level_value(lv, __ldg(obj_gray + ti));
+                bool ok = !(depth < c.min_depth_f) && !is_invalid(I1); // optimize.cpp:39,46
+                if (ok) {
+                    float X, Y, Z;
+                    back_project(g, (float)x, (float)y, depth, X, Y, Z);
+                    const float tx = (T[0] * X + T[1] * Y + T[2] * Z) + T[3];
+                    const float ty = (T[4] * X + T[5] * Y + T[6] * Z) + T[7];
+                    const float tz = (T[8] * X + T[9] * Y + T[10] * Z) + T[11];
+                    const float wx = tx * g.fx / tz + g.cx;
+                    const float wy = ty * g.fy / tz + g.cy;
+                    const Sample3 sm = sample_level<true>(ref_gray, lv, wx, wy);
+                    // I_2 valid (optimize.cpp:46); warped point inside the image (:52-56); gradients valid (:61)
+                    ok = sm.in && !is_invalid(sm.I) && !(wx < 0 || wy < 0 || (float)g.w <= wx || (float)g.h <= wy)
+                         && !(is_invalid(sm.gx) || is_invalid(sm.gy));
+                    if (ok) {
+                        const float fgx = g.fx * sm.gx, fgy = g.fy * sm.gy; // optimize.cpp:67-77
+                        const float xz = X / Z, yz = Y / Z;
+                        float J[6];
+                        J[0] = fgx / Z;
+                        J[1] = fgy / Z;
+                        J[2] = -(fgx * X + fgy * Y) / Z / Z;
+                        J[3] = -fgx * xz * yz - fgy * (1.0f + yz * yz);
+                        J[4] = fgx * (1.0f + xz * xz) + fgy * xz * yz;
+                        J[5] = (-fgx * yz + fgy * xz);
+                        const float r = sm.I - I1;
+                        const float sg0 = level_value(lv, dsr.y);
+                        const float sg = (sg0 < c.sigma_lo) ? c.sigma_lo : (c.sigma_hi < sg0) ? c.sigma_hi : sg0; // std::clamp :83
+                        const float bw = r * (step / sg);
+                        double Jd[6];
+#pragma unroll
+                        for (int q = 0; q < 6; q++) Jd[q] = (double)J[q];
+                        int idx = 0;
+#pragma unroll
+                        for (int p = 0; p < 6; p++)
+#pragma unroll
+                            for (int q = p; q < 6; q++) { acc[idx] = fma(Jd[p], Jd[q], acc[idx]); idx++; }
+                        const double bd = (double)bw;
+#pragma unroll
+                        for (int q = 0; q < 6; q++) acc[21 + q] = fma(Jd[q], bd, acc[21 + q]);
+                        acc[27] += (double)(r * r);
+                        acc[28] += 1.0;
+                    }
+                }
+                if (a.mask && ok) a.mask[(size_t)s * g.n + (size_t)y * g.w + x] = 1;
+                x += sx; y += sy;
+                if (x > rx1) { x -= rw; y++; }
+            }
+        }
+
+        // ---- reduction in a fixed order (deterministic for a given B) ----
+        const int lane = tid & 31, warp = tid >> 5;
+#pragma unroll
+        for (int k = 0; k < NACC; k++) {
+            double v = acc[k];
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
+            if (lane == 0) sred[warp][k] = v;
+        }
+        __syncthreads();
+        if (tid < NACC) {
+            double v = 0;
+#pragma unroll
+            for (int wv = 0; wv < TRK_THREADS / 32; wv++) v += sred[wv][tid];
+            if (B == 1) stot[tid] = v;
+            else a.partials[((size_t)s * B + b) * 32 + tid] = v;
+        }
+        epoch++;
+        if (B > 1) {
+            __threadfence();
+            __syncthreads();
+            if (tid == 0) {
+                atomicAdd(&st->arrive, 1u);
+                if (leader) { // wait until every CTA of the stream has delivered this iteration's partials
+                    const unsigned int target = (gen0 + epoch) * (unsigned int)B;
+                    while ((int)(ld_volatile_u32(&st->arrive) - target) < 0) __nanosleep(32);
+                    __threadfence();
+                }
+            }
+            __syncthreads();
+            if (leader && tid < NACC) {
+                const double* base = a.partials + (size_t)s * B * 32 + tid;
+                double v = 0;
+                for (int bb = 0; bb < B; bb++) v += __ldcg(base + (size_t)bb * 32);
+                stot[tid] = v;
+            }
+        }
+        __syncthreads();
+        if (leader) {
+            if (tid == 0) {
+                gn_tail(c, a, st, s, stot, &ctl);
+                if (B > 1) {
+                    __threadfence();
+                    atomicExch(&st->gen, gen0 + epoch);
+                }
+            }
+        } else if (tid == 0) {
+            const unsigned int target = gen0 + epoch;
+            while ((int)(ld_volatile_u32(&st->gen) - target) < 0) __nanosleep(32);
+            __threadfence();
+            ctl.level = __ldcg(&st->level); ctl.iter = __ldcg(&st->iter); ctl.done = __ldcg(&st->done);
+            for (int q = 0; q < 12; q++) ctl.T[q] = __ldcg(&st->Tn[q]);
+        }
+        __syncthreads();
+    }
+
+    // ---- VO epilogue (leader CTA of each stream) ----
+    if (a.vo && leader) {
+        if (tid == 0) vo_decide(c, a, st, s);
+        __syncthreads();
+        const MapState* m = a.ms + s;
+        if (m->do_update)
+            for (int age = tid; age < m->n_hist; age += TRK_THREADS) pose_table_entry(c, a.slots, m, a.hist, a.tab, s, age);
+    }
+}
+
+// pose tables for the granular Mapper::update entry point.  grid = (ceil(max_kf/64), S)
+__global__ void k_pose_tables(const __grid_constant__ Consts c, const SlotDev* __restrict__ slots, MapState* __restrict__ mst,
+                              const int* __restrict__ hist, PoseTab* __restrict__ tab)
+{
+    const int s = blockIdx.y;
+    const int a = blockIdx.x * blockDim.x + threadIdx.x;
+    MapState* m = mst + s;
+    if (!m->do_update || a >= m->n_hist) return;
+    pose_table_entry(c, slots, m, hist, tab, s, a);
 }
 
 // =============================================================================================
@@ -496,9 +692,9 @@ __device__ __forceinline__ double point_norm(float x, float y)
     return sqrt(__dadd_rn(__dmul_rn((double)x, (double)x), __dmul_rn((double)y, (double)y)));
 }
 
-__device__ inline void implement_update(const float* __restrict__ born_gray, const float4* __restrict__ born_tex, const LevelGeom& g,
-                                        const float* __restrict__ T, const float* __restrict__ tneg, const float* __restrict__ Kc,
-                                        int px, int py, float og, float depth, float sigma, float& new_depth, float& new_sigma)
+__device__ inline void implement_update(const float* __restrict__ born_gray, const LevelGeom& g, const float* __restrict__ T,
+                                        const float* __restrict__ tneg, int px, int py, float og, float depth, float sigma,
+                                        float& new_depth, float& new_sigma)
 {
     const int w = g.w, h = g.h;
     const float dmin = (depth - sigma) < 0.10f ? 0.10f : (depth - sigma); // :30
@@ -508,29 +704,46 @@ __device__ inline void implement_update(const float* __restrict__ born_gray, con
     warp_point(T, g, (float)px, (float)py, dmin, ex, ey); // end   :32
     const float length = (float)point_norm(sx - ex, sy - ey); // :33
 
-    // doMatching :106-152
+    // doMatching :106-152.  The three taps of a step are pt - dir, pt, pt + dir; the last one is the
+    // next step's centre tap (same coordinates bit for bit), so it is carried over instead of re-sampled.
     const float dirx = (ex - sx) / length, diry = (ey - sy) / length;
     float ptx = sx, pty = sy, bestx = sx, besty = sy;
     float min_ssd = 2.0f * 3;
     int count = 0;
     const double len_d = (double)length;
+    bool have_c = false;
+    float carry = 0.f;
     while (point_norm(ptx - sx, pty - sy) < len_d) {
         float ssd = 0;
         ptx += dirx;
         pty += diry;
-#pragma unroll
-        for (int i = 0; i < 3; i++) {
-            const float k = (float)(i - 1);
-            const float tx = ptx + dirx * k, ty = pty + diry * k;
-            const float sub = subpixel_dense(born_gray, w, h, tx, ty);
-            if (is_invalid(sub)) {
+        bool next_have = false;
+        float next = 0.f;
+        {
+            const float s0 = subpixel_dense(born_gray, w, h, ptx + dirx * -1.0f, pty + diry * -1.0f);
+            if (is_invalid(s0)) {
                 ssd = 2.0f * 3;
-                break;
+            } else {
+                const float d0 = s0 - og;
+                ssd = (float)__dadd_rn((double)ssd, __dmul_rn(1.0 * 1 / 3, (double)(d0 * d0))); // :134
+                const float s1 = have_c ? carry : subpixel_dense(born_gray, w, h, ptx + dirx * 0.0f, pty + diry * 0.0f);
+                if (is_invalid(s1)) {
+                    ssd = 2.0f * 3;
+                } else {
+                    const float d1 = s1 - og;
+                    ssd = (float)__dadd_rn((double)ssd, __dmul_rn(1.0 * 2 / 3, (double)(d1 * d1)));
+                    const float s2 = subpixel_dense(born_gray, w, h, ptx + dirx * 1.0f, pty + diry * 1.0f);
+                    next = s2; next_have = true;
+                    if (is_invalid(s2)) {
+                        ssd = 2.0f * 3;
+                    } else {
+                        const float d2 = s2 - og;
+                        ssd = (float)__dadd_rn((double)ssd, __dmul_rn(1.0 * 3 / 3, (double)(d2 * d2)));
+                    }
+                }
             }
-            const float diff = sub - og;
-            const double wk = (i == 0) ? (1.0 * 1 / 3) : (i == 1) ? (1.0 * 2 / 3) : (1.0 * 3 / 3); // :134
-            ssd = (float)__dadd_rn((double)ssd, __dmul_rn(wk, (double)(diff * diff)));
         }
+        have_c = next_have; carry = next;
         if (ssd < min_ssd) {
             bestx = ptx; besty = pty;
             min_ssd = ssd;
@@ -545,6 +758,7 @@ __device__ inline void implement_update(const float* __restrict__ born_gray, con
     }
     // depthEstimate :49-71
     {
+        const float Kc[9] = {g.fx, 0.f, g.cx, 0.f, g.fy, g.cy, 0.f, 0.f, 1.f};
         const float xq0 = 1.0f * ((float)px - g.cx) / g.fx, xq1 = 1.0f * ((float)py - g.cy) / g.fy, xq2 = 1.0f;
         const float R[9] = {T[0], T[1], T[2], T[4], T[5], T[6], T[8], T[9], T[10]};
         const float xi3[3] = {mx, my, 1.0f};
@@ -580,8 +794,10 @@ __device__ inline void implement_update(const float* __restrict__ born_gray, con
             new_sigma = -1;
             return;
         }
-        const float4 t = __ldg(born_tex + idx);
-        const float gx = t.y, gy = t.z;
+        // ref_grad_x(ref_x_i): the gradient image's element at that linear index
+        LevelView tv; tv.w = w; tv.h = h; tv.t = 0; tv.W = w;
+        const int yy = (int)(idx / w), xx = (int)(idx - (long long)yy * w);
+        const float gx = grad_x_at(born_gray, tv, xx, yy), gy = grad_y_at(born_gray, tv, xx, yy);
         if (is_invalid(gx) || is_invalid(gy)) {
             new_sigma = -1;
             return;
@@ -595,27 +811,7 @@ __device__ inline void implement_update(const float* __restrict__ born_gray, con
     }
 }
 
-// pose tables for Mapper::update (mapper.cpp:107): r_xi = concatenate(obj.m_xi, -born.m_xi) depends
-// on the age only, so it is hoisted out of the pixel loop.  grid = (ceil(max_kf/64), S)
-__global__ void k_pose_tables(const __grid_constant__ Consts c, const SlotDev* __restrict__ slots, MapState* __restrict__ mst,
-                              const int* __restrict__ hist, PoseTab* __restrict__ tab)
-{
-    const int s = blockIdx.y;
-    const int a = blockIdx.x * blockDim.x + threadIdx.x;
-    MapState* m = mst + s;
-    if (!m->do_update || a >= m->n_hist) return;
-    const int born_slot = hist[(size_t)s * c.max_kf + (m->n_hist - 1 - a)]; // FrameHistory::operator[] frame.hpp:176
-    const float* oxi = slots[m->obj_slot].xi + 6 * s;
-    const float* bxi = slots[born_slot].xi + 6 * s;
-    float a6[6], nb[6], r[6];
-    for (int q = 0; q < 6; q++) { a6[q] = oxi[q]; nb[q] = -bxi[q]; }
-    se3_concatenate(a6, nb, r);
-    PoseTab* t = tab + (size_t)s * c.max_kf + a;
-    se3_exp_neg12(r, t->T);
-    t->t[0] = -r[0]; t->t[1] = -r[1]; t->t[2] = -r[2];
-}
-
-// exp(rel_xi) for Mapper::update's projection (mapper.cpp:94) and Implement::propagate (:239)
+// exp(rel_xi) for Mapper::update's projection (mapper.cpp:94) and Implement::propagate (:239) — granular API
 __global__ void k_map_prepare(const __grid_constant__ Consts c, MapState* __restrict__ mst, const float* __restrict__ rel_xi)
 {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
@@ -629,61 +825,63 @@ __global__ void k_map_prepare(const __grid_constant__ Consts c, MapState* __rest
     mst[s].ticket = 0;
 }
 
+// The ROI of Mapper::update (mapper.cpp:90) clipped to the image; threads are laid out over it in
+// row-major order, which is also the reference's visiting order restricted to the ROI.
+struct MapRoi {
+    int x0, y0, w, h, n; // origin, size, pixel count
+    int nblk;            // blocks of 256 covering it
+};
+
 // Mapper::update phase A (mapper.cpp:76-137): per ref pixel, epipolar observation + gate + fusion.
 // Rejected pixels (Gaussian::update reset, gaussian.cpp:21-25) are only flagged here: their value
 // depends on the row-major rank among all rejects (mt19937 order) -> phase B.
-// grid = (ceil(n_top/256), S)
-__global__ void __launch_bounds__(256) k_map_update(const __grid_constant__ Consts c, const SlotDev* __restrict__ slots,
-                                                    MapState* __restrict__ mst, const int* __restrict__ hist,
-                                                    const PoseTab* __restrict__ tab, uint8_t* __restrict__ flags,
-                                                    unsigned int* __restrict__ blockcnt, int nblk)
+// grid = (roi.nblk, S)
+__global__ void __launch_bounds__(256, 3) k_map_update(const __grid_constant__ Consts c, const MapRoi roi, const SlotDev* __restrict__ slots,
+                                                       MapState* __restrict__ mst, const int* __restrict__ hist,
+                                                       const PoseTab* __restrict__ tab, uint8_t* __restrict__ flags,
+                                                       unsigned int* __restrict__ blockcnt)
 {
     const int s = blockIdx.y;
     MapState* m = mst + s;
     if (!m->do_update) return;
-    const int top = c.L - 1;
-    const LevelGeom g = c.lv[top];
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const LevelGeom g = c.lv[c.L - 1];
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
     uint8_t fl = 0;
     bool reject = false;
-    if (i < g.n) {
-        const int y = i / g.w, x = i - y * g.w;
-        if (!(x < c.map_x0 || x > c.map_x1 || y < c.map_y0 || y > c.map_y1)) { // mapper.cpp:90
-            const SlotDev ref = slots[m->ref_slot];
-            const SlotDev obj = slots[m->obj_slot];
-            float2* ds = ref.ds[top] + (size_t)s * g.n;
-            const float2 dsv = ds[i];
-            const float d = dsv.x;
-            float wx, wy;
-            warp_point(m->Trel, g, (float)x, (float)y, d, wx, wy);
-            const int px = round_x86(wx), py = round_x86(wy); // Point2f -> Point2i :94
-            if (in_range(px, py, g.w, g.h)) {
-                const int age = trunc_x86(ref.age[(size_t)s * g.n + i]); // :99
-                if (age < 0 || age >= m->n_hist) {
-                    atomicCAS(&m->err, 0, (int)DVO_ERR_HISTORY); // m_history.at() would throw
-                } else {
-                    const int born_slot = hist[(size_t)s * c.max_kf + (m->n_hist - 1 - age)];
-                    const SlotDev born = slots[born_slot];
-                    const PoseTab* pt = tab + (size_t)s * c.max_kf + age;
-                    const float prior_d = d - m->rel_z; // :104
-                    const float prior_s = dsv.y;
-                    const float Kc[9] = {g.fx, 0.f, g.cx, 0.f, g.fy, g.cy, 0.f, 0.f, 1.f};
-                    const float og = obj.gray[top][(size_t)s * g.n + (size_t)py * g.w + px];
-                    float nd, ns;
-                    implement_update(born.gray[top] + (size_t)s * g.n, born.tex[top] + (size_t)s * g.n, g, pt->T, pt->t, Kc, px, py,
-                                     og, prior_d, prior_s, nd, ns);
-                    fl |= 1;
-                    if (nd > c.acc_d_lo && nd < c.acc_d_hi && ns > 0.0f && ns < c.acc_s_hi) { // :122
-                        fl |= 2;
-                        // Gaussian::update (gaussian.cpp:12-31)
-                        float gd = prior_d, gs = prior_s;
-                        if (gaussian_fuse(gd, gs, nd, ns)) {
-                            fl |= 4;
-                            ds[i] = make_float2(gd, gs);
-                        } else {
-                            fl |= 8;
-                            reject = true;
-                        }
+    if (j < roi.n) {
+        const int ry = j / roi.w;
+        const int x = roi.x0 + (j - ry * roi.w), y = roi.y0 + ry;
+        const int i = y * g.w + x;
+        const SlotDev ref = slots[m->ref_slot];
+        float2* ds = ref.ds + (size_t)s * g.n;
+        const float2 dsv = ds[i];
+        const float d = dsv.x;
+        float wx, wy;
+        warp_point(m->Trel, g, (float)x, (float)y, d, wx, wy);
+        const int px = round_x86(wx), py = round_x86(wy); // Point2f -> Point2i :94
+        if (in_range(px, py, g.w, g.h)) {
+            const int age = trunc_x86(ref.age[(size_t)s * g.n + i]); // :99
+            if (age < 0 || age >= m->n_hist) {
+                atomicCAS(&m->err, 0, (int)DVO_ERR_HISTORY); // m_history.at() would throw
+            } else {
+                const int born_slot = hist[(size_t)s * c.max_kf + (m->n_hist - 1 - age)];
+                const PoseTab* pt = tab + (size_t)s * c.max_kf + age;
+                const float prior_d = d - m->rel_z; // :104
+                const float prior_s = dsv.y;
+                const float og = __ldg(slots[m->obj_slot].gray + (size_t)s * g.n + (size_t)py * g.w + px);
+                float nd, ns;
+                implement_update(slots[born_slot].gray + (size_t)s * g.n, g, pt->T, pt->t, px, py, og, prior_d, prior_s, nd, ns);
+                fl |= 1;
+                if (nd > c.acc_d_lo && nd < c.acc_d_hi && ns > 0.0f && ns < c.acc_s_hi) { // :122
+                    fl |= 2;
+                    // Gaussian::update (gaussian.cpp:12-31)
+                    float gd = prior_d, gs = prior_s;
+                    if (gaussian_fuse(gd, gs, nd, ns)) {
+                        fl |= 4;
+                        ds[i] = make_float2(gd, gs);
+                    } else {
+                        fl |= 8;
+                        reject = true;
                     }
                 }
             }
@@ -693,34 +891,37 @@ __global__ void __launch_bounds__(256) k_map_update(const __grid_constant__ Cons
     const int nrej = __syncthreads_count(reject);
     const int nval = __syncthreads_count((fl & 4) != 0);
     if (threadIdx.x == 0) {
-        blockcnt[(size_t)s * nblk + blockIdx.x] = (unsigned)nrej;
+        blockcnt[(size_t)s * roi.nblk + blockIdx.x] = (unsigned)nrej;
         if (nval) atomicAdd(&m->valid_update, nval);
     }
 }
 
 // Mapper::update phase B: replay of the mt19937 stream for the rejected pixels in row-major order.
-// rank = (rejects in preceding blocks) + (rejects before this thread in the block).
-__global__ void __launch_bounds__(256) k_map_update_apply(const __grid_constant__ Consts c, const SlotDev* __restrict__ slots,
+// rank = (rejects in preceding blocks) + (rejects before this thread in the block).  grid = (roi.nblk, S)
+__global__ void __launch_bounds__(256) k_map_update_apply(const __grid_constant__ Consts c, const MapRoi roi, const SlotDev* __restrict__ slots,
                                                           MapState* __restrict__ mst, const uint8_t* __restrict__ flags,
-                                                          const unsigned int* __restrict__ blockcnt, int nblk,
-                                                          const uint32_t* __restrict__ rng_raw)
+                                                          const unsigned int* __restrict__ blockcnt, const uint32_t* __restrict__ rng_raw)
 {
     const int s = blockIdx.y;
     MapState* m = mst + s;
     if (!m->do_update) return;
-    const int top = c.L - 1;
-    const LevelGeom g = c.lv[top];
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const LevelGeom g = c.lv[c.L - 1];
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    int i = -1;
+    if (j < roi.n) {
+        const int ry = j / roi.w;
+        i = (roi.y0 + ry) * g.w + roi.x0 + (j - ry * roi.w);
+    }
     __shared__ unsigned int s_warp[8];
     __shared__ unsigned int s_base;
     __shared__ unsigned int s_part[8];
     // offset of this block = sum of preceding block counts
     unsigned int part = 0;
-    for (int b = threadIdx.x; b < (int)blockIdx.x; b += blockDim.x) part += blockcnt[(size_t)s * nblk + b];
+    for (int b = threadIdx.x; b < (int)blockIdx.x; b += blockDim.x) part += blockcnt[(size_t)s * roi.nblk + b];
     for (int off = 16; off > 0; off >>= 1) part += __shfl_down_sync(0xffffffffu, part, off);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (lane == 0) s_part[warp] = part;
-    const bool rej = (i < g.n) && (flags[(size_t)s * g.n + i] & 8);
+    const bool rej = (i >= 0) && (flags[(size_t)s * g.n + i] & 8);
     const unsigned int bal = __ballot_sync(0xffffffffu, rej);
     if (lane == 0) s_warp[warp] = __popc(bal);
     __syncthreads();
@@ -739,8 +940,8 @@ __global__ void __launch_bounds__(256) k_map_update_apply(const __grid_constant_
         } else {
             const float u = dist_from_u32(__ldg(rng_raw + pos));
             const SlotDev ref = slots[m->ref_slot];
-            ref.ds[top][(size_t)s * g.n + i] = make_float2(4.0f < u ? 4.0f : u, 0.5f); // gaussian.cpp:22-23
-            ref.age[(size_t)s * g.n + i] = 0.f;                                        // mapper.cpp:126
+            ref.ds[(size_t)s * g.n + i] = make_float2(4.0f < u ? 4.0f : u, 0.5f); // gaussian.cpp:22-23
+            ref.age[(size_t)s * g.n + i] = 0.f;                                   // mapper.cpp:126
         }
     }
     // the last block of the stream advances the replay position
@@ -748,9 +949,9 @@ __global__ void __launch_bounds__(256) k_map_update_apply(const __grid_constant_
     if (threadIdx.x == 0) {
         __threadfence();
         unsigned int t = atomicAdd(&m->ticket, 1u);
-        if (t == (unsigned)(nblk - 1)) {
+        if (t == (unsigned)(roi.nblk - 1)) {
             unsigned int total = 0;
-            for (int b = 0; b < nblk; b++) total += blockcnt[(size_t)s * nblk + b];
+            for (int b = 0; b < roi.nblk; b++) total += blockcnt[(size_t)s * roi.nblk + b];
             m->n_reject = total;
             m->rng_pos += total;
             m->ticket = 0;
@@ -760,19 +961,18 @@ __global__ void __launch_bounds__(256) k_map_update_apply(const __grid_constant_
 
 // Implement::propagate (implement.cpp:217-256).  Pass 1: the serial reference lets the LAST source
 // pixel in row-major order win a destination; atomicMax of the source index reproduces that
-// without a race.  winner must be pre-filled with -1.
+// without a race.  `winner` is all -1 between calls (pass 2 restores it).
 __global__ void __launch_bounds__(256) k_propagate_scatter(const __grid_constant__ Consts c, const SlotDev* __restrict__ slots,
                                                            const MapState* __restrict__ mst, int* __restrict__ winner)
 {
     const int s = blockIdx.y;
     const MapState* m = mst + s;
     if (!m->do_propagate) return;
-    const int top = c.L - 1;
-    const LevelGeom g = c.lv[top];
+    const LevelGeom g = c.lv[c.L - 1];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= g.n) return;
     const int y = i / g.w, x = i - y * g.w;
-    const float rd = slots[m->ref_slot].ds[top][(size_t)s * g.n + i].x;
+    const float rd = slots[m->ref_slot].ds[(size_t)s * g.n + i].x;
     if (fabsf(rd) < DVO_EPS) return; // :236
     float wx, wy;
     warp_point(m->Trel, g, (float)x, (float)y, rd, wx, wy); // :239
@@ -781,15 +981,15 @@ __global__ void __launch_bounds__(256) k_propagate_scatter(const __grid_constant
     atomicMax(winner + (size_t)s * g.n + (size_t)py * g.w + px, i);
 }
 
-// Pass 2: gather from the winning source (or the 1/1/0 defaults, :229-231) into new_slot.
+// Pass 2: gather from the winning source (or the 1/1/0 defaults, :229-231) into new_slot
+// (= Frame::updateDepthSigmaAge, frame.cpp:47-54: the coarser levels are views of this one).
 __global__ void __launch_bounds__(256) k_propagate_gather(const __grid_constant__ Consts c, const SlotDev* __restrict__ slots,
-                                                          const MapState* __restrict__ mst, const int* __restrict__ winner)
+                                                          const MapState* __restrict__ mst, int* __restrict__ winner)
 {
     const int s = blockIdx.y;
     const MapState* m = mst + s;
     if (!m->do_propagate) return;
-    const int top = c.L - 1;
-    const LevelGeom g = c.lv[top];
+    const LevelGeom g = c.lv[c.L - 1];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= g.n) return;
     const SlotDev ref = slots[m->ref_slot];
@@ -798,7 +998,8 @@ __global__ void __launch_bounds__(256) k_propagate_gather(const __grid_constant_
     float2 out = make_float2(1.0f, 1.0f);
     float age = 0.f;
     if (src >= 0) {
-        const float2 v = ref.ds[top][(size_t)s * g.n + src];
+        winner[(size_t)s * g.n + i] = -1;
+        const float2 v = ref.ds[(size_t)s * g.n + src];
         const float d0 = v.x < 0.01f ? 0.01f : v.x; // :244
         const float d1 = d0 + m->rel_z;
         const float q = d1 / d0;
@@ -807,7 +1008,7 @@ __global__ void __launch_bounds__(256) k_propagate_gather(const __grid_constant_
         out = make_float2(d1 < 0.0f ? 0.0f : d1, sg);
         age = ref.age[(size_t)s * g.n + src] + 1; // :252
     }
-    dst.ds[top][(size_t)s * g.n + i] = out;
+    dst.ds[(size_t)s * g.n + i] = out;
     dst.age[(size_t)s * g.n + i] = age;
 }
 
@@ -819,12 +1020,11 @@ __global__ void __launch_bounds__(256) k_regularize(const __grid_constant__ Cons
     const int s = blockIdx.y;
     const MapState* m = mst + s;
     if (!m->do_regularize) return;
-    const int top = c.L - 1;
-    const LevelGeom g = c.lv[top];
+    const LevelGeom g = c.lv[c.L - 1];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= g.n) return;
     const int y = i / g.w, x = i - y * g.w;
-    const float2* ds = slots[m->reg_slot].ds[top] + (size_t)s * g.n;
+    const float2* ds = slots[m->reg_slot].ds + (size_t)s * g.n;
     float2 v = ds[i];
     float gd = v.x, gs = v.y;
     if (x - 1 >= 0) { const float2 n = __ldg(ds + i - 1); gaussian_fuse(gd, gs, n.x, n.y); }      // {0,-1}
@@ -834,100 +1034,29 @@ __global__ void __launch_bounds__(256) k_regularize(const __grid_constant__ Cons
     tmp[(size_t)s * g.n + i] = gd < 6.0f ? gd : 6.0f; // cv::min(new_depth, 6.0) :178
 }
 
-// Frame::updateDepth (frame.cpp:56-61) after regularize: finest depth <- tmp, coarser depth AND
-// sigma re-culled (this also covers Frame::updateDepthSigma of Mapper::update, mapper.cpp:135).
-// grid = (ceil(n_top/256), S, L)
-__global__ void __launch_bounds__(256) k_ds_rebuild(const __grid_constant__ Consts c, const SlotDev* __restrict__ slots,
-                                                    const MapState* __restrict__ mst, const float* __restrict__ tmp)
+// Frame::updateDepth (frame.cpp:56-61): depth <- tmp; sigma stays.  Two pixels per thread so that
+// whole float4 {d, s, d, s} are rewritten.  grid = (ceil(n_top/512), S)
+__global__ void __launch_bounds__(256) k_regularize_commit(const __grid_constant__ Consts c, const SlotDev* __restrict__ slots,
+                                                           const MapState* __restrict__ mst, const float* __restrict__ tmp)
 {
-    const int l = blockIdx.z, s = blockIdx.y;
+    const int s = blockIdx.y;
     const MapState* m = mst + s;
     if (!m->do_regularize) return;
-    const int top = c.L - 1;
-    const LevelGeom g = c.lv[l];
-    const LevelGeom gt = c.lv[top];
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const LevelGeom g = c.lv[c.L - 1];
+    const int i = (blockIdx.x * blockDim.x + threadIdx.x) * 2;
     if (i >= g.n) return;
-    const SlotDev sl = slots[m->reg_slot];
-    if (l == top) {
-        reinterpret_cast<float*>(sl.ds[top] + (size_t)s * g.n + i)[0] = tmp[(size_t)s * g.n + i];
-        return;
+    float2* ds = slots[m->reg_slot].ds + (size_t)s * g.n;
+    const float* t = tmp + (size_t)s * g.n;
+    const bool vec = (i + 1 < g.n) && ((((size_t)s * g.n + i) & 1) == 0);
+    if (vec) {
+        float4 v = *reinterpret_cast<float4*>(ds + i);
+        const float2 d = *reinterpret_cast<const float2*>(t + i);
+        v.x = d.x; v.z = d.y;
+        *reinterpret_cast<float4*>(ds + i) = v;
+    } else {
+        ds[i].x = t[i];
+        if (i + 1 < g.n) ds[i + 1].x = t[i + 1];
     }
-    const int t = top - l;
-    const int y = i / g.w, x = i - y * g.w;
-    const size_t src = (size_t)(y << t) * gt.w + (x << t);
-    const float d = tmp[(size_t)s * gt.n + src];
-    const float sg = reinterpret_cast<const float*>(sl.ds[top] + (size_t)s * gt.n + src)[1];
-    sl.ds[l][(size_t)s * g.n + i] = make_float2(get_pixel_value(d), get_pixel_value(sg));
-}
-
-// =============================================================================================
-// VisualOdometry control (include/system/system.hpp:44-74, src/map/mapper.cpp:16-60) on device
-// =============================================================================================
-// After tracking: Frame::updateXi (frame.cpp:7-14), Mapper::needNewFrame (mapper.cpp:45-60).
-__global__ void k_vo_decide(const __grid_constant__ Consts c, const SlotDev* __restrict__ slots, const TrackState* __restrict__ ts,
-                            VoState* __restrict__ vo, MapState* __restrict__ mst, int frame_id, const float* __restrict__ forced_rel)
-{
-    const int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= c.S) return;
-    VoState* v = vo + s;
-    MapState* m = mst + s;
-    const int cur_slot = v->cur_slot;
-    const SlotDev cur = slots[cur_slot];
-    m->valid_update = 0; m->n_reject = 0; m->ticket = 0;
-    if (v->kf_slot < 0) { // first frame: m_history.setRefFrame(frame); return identity (system.hpp:49-54)
-        for (int q = 0; q < 6; q++) { cur.xi[6 * s + q] = 0.f; cur.rel_xi[6 * s + q] = 0.f; }
-        m->do_propagate = 0; m->do_update = 0; m->do_regularize = 0;
-        v->need_new = 1; v->was_keyframe = 1; v->n_iters = 0;
-        return;
-    }
-    float rel[6], kxi[6], xi[6];
-    const SlotDev kf = slots[v->kf_slot];
-    // forced_rel: the caller supplies the relative pose (teacher-forced parity runs, external pose
-    // priors); the tracker's own result stays available in the iteration log.
-    for (int q = 0; q < 6; q++) { rel[q] = forced_rel ? forced_rel[6 * s + q] : ts[s].xi[q]; kxi[q] = kf.xi[6 * s + q]; }
-    se3_concatenate(kxi, rel, xi);
-    for (int q = 0; q < 6; q++) { cur.xi[6 * s + q] = xi[q]; cur.rel_xi[6 * s + q] = rel[q]; }
-    v->n_iters = ts[s].n_total;
-    v->gn_iters += (unsigned long long)ts[s].n_total;
-    v->gn_pixels += (unsigned long long)ts[s].px_total;
-    bool need = false;
-    if (norm_n(rel, 3) > (double)c.min_movement) need = true;       // mapper.cpp:48-52
-    else if (frame_id - v->kf_frame_id >= c.max_forward) need = true; // mapper.cpp:53-56
-    v->need_new = need ? 1 : 0;
-    if (need) v->n_propagate++; else v->n_update++;
-    v->was_keyframe = need ? 1 : 0;
-    m->ref_slot = v->kf_slot; m->obj_slot = cur_slot; m->new_slot = cur_slot;
-    m->n_hist = v->n_kf;
-    m->do_propagate = need ? 1 : 0;
-    m->do_update = need ? 0 : 1;
-    m->do_regularize = 1;
-    float T[16];
-    se3_exp(rel, T);
-    for (int q = 0; q < 12; q++) m->Trel[q] = T[q];
-    m->rel_z = rel[2];
-}
-
-// FrameHistory::setRefFrame (frame.hpp:151-157) after propagate; regularize target = newest keyframe.
-__global__ void k_vo_commit(const __grid_constant__ Consts c, VoState* __restrict__ vo, MapState* __restrict__ mst, int* __restrict__ hist,
-                            int frame_id)
-{
-    const int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= c.S) return;
-    VoState* v = vo + s;
-    MapState* m = mst + s;
-    const int cur_slot = v->cur_slot;
-    if (v->need_new) {
-        if (v->n_kf >= c.max_kf) {
-            atomicCAS(&m->err, 0, (int)DVO_ERR_HISTORY);
-        } else {
-            hist[(size_t)s * c.max_kf + v->n_kf] = cur_slot;
-            v->n_kf += 1;
-            v->kf_slot = cur_slot;
-            v->kf_frame_id = frame_id;
-        }
-    }
-    m->reg_slot = v->kf_slot;
 }
 
 // se3::exp(frame->m_xi) for odometrize's return value (system.hpp:73)
@@ -939,17 +1068,6 @@ __global__ void k_pose_out(const __grid_constant__ Consts c, const SlotDev* __re
     float T[16];
     se3_exp(slots[vo[s].cur_slot].xi + 6 * s, T);
     for (int q = 0; q < 16; q++) T_out[16 * s + q] = T[q];
-}
-
-// Start of a VO frame: the stream's current frame goes into the pool entry after its newest
-// keyframe (entry k of the pool holds keyframe k of every stream: FrameHistory::m_history[k]).
-__global__ void k_vo_begin(const __grid_constant__ Consts c, VoState* __restrict__ vo, MapState* __restrict__ mst)
-{
-    const int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= c.S) return;
-    int k = vo[s].n_kf;
-    if (k > c.max_kf) k = c.max_kf;
-    vo[s].cur_slot = c.vo_base + k;
 }
 
 // xi / rel_xi of every stream's current frame, gathered for dvo_vo_state.  out: [S][12]

@@ -49,6 +49,10 @@ EXPORTS = [
 ]
 
 
+class DvoKernelTime(C.Structure):
+    _fields_ = [("name", C.c_char * 32), ("total_ms", C.c_float), ("launches", C.c_int)]
+
+
 def load_library(path=None):
     path = path or LIB_PATH
     if not os.path.exists(path):
@@ -105,6 +109,7 @@ def load_library(path=None):
     lib.dvo_launch_count.restype = C.c_uint64
     lib.dvo_launch_count.argtypes = [C.c_void_p]
     lib.dvo_gn_timing.argtypes = [C.c_void_p, C.c_int, F32P, I32P]
+    lib.dvo_kernel_timing.argtypes = [C.c_void_p, C.c_int, C.POINTER(DvoKernelTime), C.c_int, I32P]
     return lib
 
 
@@ -382,6 +387,13 @@ class Dvo:
 
     def launch_count(self):
         return int(self.lib.dvo_launch_count(self.ctx))
+
+    def kernel_timing(self, enable):
+        """enable=True starts timing every hot-path launch with CUDA events; enable=False stops and
+        returns {kernel: (total_ms, launches)}."""
+        out = (DvoKernelTime * 16)(); n = C.c_int(0)
+        self._ck(self.lib.dvo_kernel_timing(self.ctx, 1 if enable else 0, out, 16, C.byref(n)))
+        return {out[k].name.decode(): (out[k].total_ms, out[k].launches) for k in range(n.value)}
 
     def gn_timing(self, enable):
         ms = C.c_float(0); n = C.c_int(0)

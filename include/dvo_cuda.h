@@ -117,8 +117,8 @@ int dvo_warp_image(dvo_ctx* ctx, int ref_slot, int level, const float* xi, float
  * pixel count, and (optional) the contributing-pixel mask [n_streams][h][w]. */
 int dvo_gn_step(dvo_ctx* ctx, int obj_slot, int ref_slot, int level, const float* xi, float* upd,
                 float* residual, int* valid, uint8_t* mask);
-/* Tracker::track(obj, ref) (src/track/tracker.cpp:22-85), device resident: one kernel per
- * Gauss-Newton iteration, solve + se3 composition + stop rules in the kernel tail, no host round
+/* Tracker::track(obj, ref) (src/track/tracker.cpp:22-85), device resident: ONE persistent kernel
+ * launch runs every level and iteration (solve + se3 composition + stop rules on device), no host round
  * trip.  stop_update/stop_residual < 0 select the reference constants.  log: [n_streams][log_cap]. */
 int dvo_track(dvo_ctx* ctx, int obj_slot, int ref_slot, float* xi_out, dvo_iter_log* log, int log_cap,
               int* n_iters, double stop_update, float stop_residual);
@@ -195,8 +195,16 @@ int dvo_timer_start(dvo_ctx* ctx);
 int dvo_timer_stop(dvo_ctx* ctx, float* ms); /* synchronises */
 /* number of kernels this context has launched since creation */
 uint64_t dvo_launch_count(const dvo_ctx* ctx);
-/* cumulative device time (ms) of GN-iteration kernels between gn_timing(1) and gn_timing(0),
- * measured with CUDA events around each launch; *launches = number of launches timed. */
+/* Device time per kernel between kernel_timing(1, ...) and kernel_timing(0, out, cap, &n): CUDA events
+ * are recorded around every launch of the hot-path kernels on the context's stream while enabled
+ * (this serialises nothing but adds two event records per launch, so use it in a separate pass). */
+typedef struct dvo_kernel_time {
+    char name[32];
+    float total_ms;
+    int launches;
+} dvo_kernel_time;
+int dvo_kernel_timing(dvo_ctx* ctx, int enable, dvo_kernel_time* out, int cap, int* n_out);
+/* the tracking kernel's share of the above (k_track: one launch = Tracker::track of every stream) */
 int dvo_gn_timing(dvo_ctx* ctx, int enable, float* total_ms, int* launches);
 
 #ifdef __cplusplus
