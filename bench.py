@@ -13,8 +13,11 @@ run N x 256 streams with no data-path collective ("scaling": "weak").
   value      frames/s with the frames already resident in HBM (dvo_vo_push_dev), CUDA events
   e2e        the same through dvo_vo_push with pinned HOST frames: the H2D copy of the step's input and
              the D2H read of the step's poses are inside the timed region
-  roofline   the Gauss-Newton iteration kernel (k_gn_step): algorithmic bytes 16 B x pixels swept
-              / its device time (CUDA events around every launch, separate pass)
+  roofline   the dominant kernel of the step (largest share of device time in a separate pass with CUDA
+             events around every launch): algorithmic bytes (SURVEY §8-d, DESIGN.md §4) / its device time;
+             `kernels` lists the same for every hot-path kernel
+  cpu_baseline  the reference's own sources (oracle/_ref) on the host cores, one sequence per core,
+             with the C restatement (oracle/dvo_oracle.c) beside it
   cpu_baseline  the CPU oracle (oracle/, a C restatement of the reference; or oracle/_ref = the
              reference's own sources when built) on the host cores, one sequence per core
 
@@ -356,13 +359,28 @@ def run_gpu_arm(args, rank, world, local_rank, dist):
         raise SystemExit("bench.py: device-side VO error")
     gn_iters = int((c1["gn_iters"] - c0["gn_iters"]).sum())
     n_prop = int((c1["n_propagate"] - c0["n_propagate"]).sum()); n_upd = int((c1["n_update"] - c0["n_update"]).sum())
-    # --- roofline pass: events around every Gauss-Newton launch (perturbs the step, so it is separate)
-    dv.gn_timing(True)
+    # --- roofline pass: CUDA events around every hot-path launch (adds event records to the stream, so it
+    # is a separate pass); the dominant kernel = the largest share of the step's device time
+    dv.kernel_timing(True)
     for _ in range(R):
         dv.vo_push_dev(fptr(f)); f += 1
-    gn_ms, gn_launches = dv.gn_timing(False)
+    ktimes = dv.kernel_timing(False)
     c2 = dv.vo_counters()
     gn_px = int((c2["gn_pixels"] - c1["gn_pixels"]).sum())
+    rp = int((c2["n_propagate"] - c1["n_propagate"]).sum()); ru = int((c2["n_update"] - c1["n_update"]).sum())
+    n_top = (W_IN >> CULLS) * (H_IN >> CULLS)
+    P = dv.params
+    roi_n = (max(0, min(P.map_roi_x1, (W_IN >> CULLS) - 1) - max(P.map_roi_x0, 0) + 1) *
+             max(0, min(P.map_roi_y1, (H_IN >> CULLS) - 1) - max(P.map_roi_y0, 0) + 1))
+    # algorithmic bytes moved over the R timed steps (SURVEY §8-d / DESIGN.md §4), per kernel
+    alg = {"k_cull_gray": (8 * n_top * S * R, "frame ingest: sampled gray in + finest level out, 8 B/px"),
+           "k_track": (GN_BYTES_PER_PX * gn_px, "16 B x pixels swept by the Gauss-Newton iterations"),
+           "k_propagate_scatter": (8 * n_top * rp, "depth+sigma in, 8 B/px of a propagating stream"),
+           "k_propagate_gather": (16 * n_top * rp, "winner in + depth, sigma, age out, 16 B/px (propagate = 24 B/px in all)"),
+           "k_map_update": (40 * roi_n * ru, "40 B x ROI pixels of an updating stream"),
+           "k_map_update_apply": (1 * roi_n * ru, "flag byte per ROI pixel"),
+           "k_regularize": (12 * n_top * (rp + ru), "depth, sigma in + depth out, 12 B/px"),
+           "k_regularize_commit": (8 * n_top * (rp + ru), "depth copy-back, 8 B/px")}
     # --- end-to-end: host frames through dvo_vo_push, H2D of the input and D2H of the poses inside
     T = np.empty((S, 4, 4), np.float32)
     Tp = T.ctypes.data_as(C.POINTER(C.c_float))
@@ -380,15 +398,23 @@ def run_gpu_arm(args, rank, world, local_rank, dist):
     dv.dev_free(dev)
     dv.close()
     peak, peak_src = peak_hbm()
-    gn_gbs = (GN_BYTES_PER_PX * gn_px / (gn_ms * 1e-3) / 1e9) if gn_ms > 0 else 0.0
+    tot_ms = sum(v[0] for v in ktimes.values()) or 1e-9
+    table = []
+    for name, (kms, kn) in sorted(ktimes.items(), key=lambda kv: -kv[1][0]):
+        b, what = alg.get(name, (0, ""))
+        gbs = b / (kms * 1e-3) / 1e9 if kms > 0 else 0.0
+        table.append(dict(kernel=name, launches=kn, avg_launch_us=1e3 * kms / kn if kn else None, share=kms / tot_ms,
+                          algorithmic_bytes_per_launch=b / kn if kn else None, achieved_gbs=gbs, frac=gbs / peak, bytes_model=what))
+    top = table[0]
     res = dict(
         value=world * S * K_ / (ms * 1e-3), ms_per_step=ms / K_,
         e2e=dict(value=world * S * E / e2e_s, unit="frames/s", h2d_bytes_per_step=frame_bytes, d2h_bytes_per_step=S * 64, steps=E),
         gpu_launches=int(l1 - l0), clocks=clocks,
-        roofline=dict(kernel="k_gn_step (fused warp + residual + Jacobian + 6x6 reduction, one launch per GN iteration)",
-                      bound="hbm", achieved=gn_gbs, peak=peak, unit="GB/s", frac=gn_gbs / peak, traffic=None, peak_source=peak_src,
-                      launches=gn_launches, avg_launch_us=(1e3 * gn_ms / gn_launches) if gn_launches else None,
-                      algorithmic_bytes_per_launch=(GN_BYTES_PER_PX * gn_px / gn_launches) if gn_launches else None),
+        roofline=dict(kernel=top["kernel"], bound="hbm", achieved=top["achieved_gbs"], peak=peak, unit="GB/s", frac=top["frac"],
+                      traffic=None, peak_source=peak_src, launches=top["launches"], avg_launch_us=top["avg_launch_us"],
+                      algorithmic_bytes_per_launch=top["algorithmic_bytes_per_launch"], share_of_step=top["share"],
+                      bytes_model=top["bytes_model"]),
+        kernels=table,
         gn_iters_per_s=world * gn_iters / (ms * 1e-3), gn_iters_per_frame=gn_iters / float(S * K_),
         frames_propagate=n_prop, frames_update=n_upd)
     return res

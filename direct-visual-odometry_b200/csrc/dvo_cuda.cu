@@ -241,7 +241,7 @@ extern "C" int dvo_create(dvo_ctx** out, const dvo_params* p)
         const int x1 = c.map_x1 < gt.w - 1 ? c.map_x1 : gt.w - 1, y1 = c.map_y1 < gt.h - 1 ? c.map_y1 : gt.h - 1;
         r.w = x1 - r.x0 + 1 > 0 ? x1 - r.x0 + 1 : 0; r.h = y1 - r.y0 + 1 > 0 ? y1 - r.y0 + 1 : 0;
         r.n = r.w * r.h;
-        r.nblk = cdiv(r.n > 0 ? r.n : 1, 256);
+        r.nblk = cdiv(r.n > 0 ? r.n : 1, MAPU_THREADS);
         if (r.w == 0) r.w = 1;
     }
     ctx->nblk_top = ctx->roi.nblk;
@@ -685,12 +685,12 @@ static int enqueue_update(dvo_ctx* ctx, bool tables)
     dim3 grid(ctx->roi.nblk, c.S);
     {
         KTimer t(ctx, K_MAP_UPDATE);
-        k_map_update<<<grid, 256, 0, ctx->stream>>>(c, ctx->roi, ctx->d_slots, ctx->d_ms, ctx->d_hist, ctx->d_tab, ctx->d_flags, ctx->d_blockcnt);
+        k_map_update<<<grid, MAPU_THREADS, 0, ctx->stream>>>(c, ctx->roi, ctx->d_slots, ctx->d_ms, ctx->d_hist, ctx->d_tab, ctx->d_flags, ctx->d_blockcnt);
         KCHECK();
     }
     {
         KTimer t(ctx, K_MAP_APPLY);
-        k_map_update_apply<<<grid, 256, 0, ctx->stream>>>(c, ctx->roi, ctx->d_slots, ctx->d_ms, ctx->d_flags, ctx->d_blockcnt, ctx->d_rng);
+        k_map_update_apply<<<grid, MAPU_THREADS, 0, ctx->stream>>>(c, ctx->roi, ctx->d_slots, ctx->d_ms, ctx->d_flags, ctx->d_blockcnt, ctx->d_rng);
         KCHECK();
     }
     return DVO_OK;

@@ -691,6 +691,25 @@ __device__ __forceinline__ double point_norm(float x, float y)
 {
     return sqrt(__dadd_rn(__dmul_rn((double)x, (double)x), __dmul_rn((double)y, (double)y)));
 }
+// `cv::norm(Point2f(x, y)) < L` (implement.cpp:120) for a float-valued L, without the fp64 square root
+// on the common path.  L*L is exact in double (24-bit L); sqrt is monotonic and correctly rounded, so
+// d2 >= L*L gives sqrt(d2) >= L, and d2 <= L*L*(1 - 2^-49) gives sqrt(d2) < L - ulp(L); only the sliver
+// in between (and NaNs) needs the real square root.  Bit-identical to the plain comparison.
+struct NormLess {
+    double L, hi, lo;
+    __device__ __forceinline__ explicit NormLess(float length) : L((double)length)
+    {
+        hi = __dmul_rn(L, L);
+        lo = __dmul_rn(hi, 1.0 - 1.7763568394002505e-15);
+    }
+    __device__ __forceinline__ bool operator()(float x, float y) const
+    {
+        const double d2 = __dadd_rn(__dmul_rn((double)x, (double)x), __dmul_rn((double)y, (double)y));
+        if (d2 >= hi) return false;
+        if (d2 <= lo) return true;
+        return sqrt(d2) < L;
+    }
+};
 
 __device__ inline void implement_update(const float* __restrict__ born_gray, const LevelGeom& g, const float* __restrict__ T,
                                         const float* __restrict__ tneg, int px, int py, float og, float depth, float sigma,
@@ -710,10 +729,10 @@ __device__ inline void implement_update(const float* __restrict__ born_gray, con
     float ptx = sx, pty = sy, bestx = sx, besty = sy;
     float min_ssd = 2.0f * 3;
     int count = 0;
-    const double len_d = (double)length;
+    const NormLess shorter_than(length);
     bool have_c = false;
     float carry = 0.f;
-    while (point_norm(ptx - sx, pty - sy) < len_d) {
+    while (shorter_than(ptx - sx, pty - sy)) {
         float ssd = 0;
         ptx += dirx;
         pty += diry;
@@ -827,16 +846,17 @@ __global__ void k_map_prepare(const __grid_constant__ Consts c, MapState* __rest
 
 // The ROI of Mapper::update (mapper.cpp:90) clipped to the image; threads are laid out over it in
 // row-major order, which is also the reference's visiting order restricted to the ROI.
+constexpr int MAPU_THREADS = 64; // small blocks: a block waits for its slowest epipolar search
 struct MapRoi {
     int x0, y0, w, h, n; // origin, size, pixel count
-    int nblk;            // blocks of 256 covering it
+    int nblk;            // blocks of MAPU_THREADS covering it
 };
 
 // Mapper::update phase A (mapper.cpp:76-137): per ref pixel, epipolar observation + gate + fusion.
 // Rejected pixels (Gaussian::update reset, gaussian.cpp:21-25) are only flagged here: their value
 // depends on the row-major rank among all rejects (mt19937 order) -> phase B.
 // grid = (roi.nblk, S)
-__global__ void __launch_bounds__(256, 3) k_map_update(const __grid_constant__ Consts c, const MapRoi roi, const SlotDev* __restrict__ slots,
+__global__ void __launch_bounds__(MAPU_THREADS, 16) k_map_update(const __grid_constant__ Consts c, const MapRoi roi, const SlotDev* __restrict__ slots,
                                                        MapState* __restrict__ mst, const int* __restrict__ hist,
                                                        const PoseTab* __restrict__ tab, uint8_t* __restrict__ flags,
                                                        unsigned int* __restrict__ blockcnt)
@@ -898,7 +918,7 @@ __global__ void __launch_bounds__(256, 3) k_map_update(const __grid_constant__ C
 
 // Mapper::update phase B: replay of the mt19937 stream for the rejected pixels in row-major order.
 // rank = (rejects in preceding blocks) + (rejects before this thread in the block).  grid = (roi.nblk, S)
-__global__ void __launch_bounds__(256) k_map_update_apply(const __grid_constant__ Consts c, const MapRoi roi, const SlotDev* __restrict__ slots,
+__global__ void __launch_bounds__(MAPU_THREADS) k_map_update_apply(const __grid_constant__ Consts c, const MapRoi roi, const SlotDev* __restrict__ slots,
                                                           MapState* __restrict__ mst, const uint8_t* __restrict__ flags,
                                                           const unsigned int* __restrict__ blockcnt, const uint32_t* __restrict__ rng_raw)
 {
@@ -912,9 +932,9 @@ __global__ void __launch_bounds__(256) k_map_update_apply(const __grid_constant_
         const int ry = j / roi.w;
         i = (roi.y0 + ry) * g.w + roi.x0 + (j - ry * roi.w);
     }
-    __shared__ unsigned int s_warp[8];
+    __shared__ unsigned int s_warp[MAPU_THREADS / 32];
     __shared__ unsigned int s_base;
-    __shared__ unsigned int s_part[8];
+    __shared__ unsigned int s_part[MAPU_THREADS / 32];
     // offset of this block = sum of preceding block counts
     unsigned int part = 0;
     for (int b = threadIdx.x; b < (int)blockIdx.x; b += blockDim.x) part += blockcnt[(size_t)s * roi.nblk + b];
@@ -927,7 +947,7 @@ __global__ void __launch_bounds__(256) k_map_update_apply(const __grid_constant_
     __syncthreads();
     if (threadIdx.x == 0) {
         unsigned int t = 0;
-        for (int k = 0; k < 8; k++) t += s_part[k];
+        for (int k = 0; k < MAPU_THREADS / 32; k++) t += s_part[k];
         s_base = t;
     }
     __syncthreads();

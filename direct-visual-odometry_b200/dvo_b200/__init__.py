@@ -45,7 +45,7 @@ EXPORTS = [
     "dvo_gn_step", "dvo_track", "dvo_map_propagate", "dvo_map_update", "dvo_map_regularize", "dvo_rng_position",
     "dvo_mask_compact", "dvo_vo_reset", "dvo_vo_reserve", "dvo_vo_force_pose", "dvo_vo_push", "dvo_vo_push_dev", "dvo_vo_state", "dvo_vo_ref_slot",
     "dvo_vo_last_slot", "dvo_vo_last_log", "dvo_vo_counters", "dvo_vo_error", "dvo_synth_render_dev", "dvo_dev_alloc", "dvo_dev_free",
-    "dvo_copy_to_host", "dvo_copy_to_dev", "dvo_timer_start", "dvo_timer_stop", "dvo_launch_count", "dvo_gn_timing",
+    "dvo_copy_to_host", "dvo_copy_to_dev", "dvo_timer_start", "dvo_timer_stop", "dvo_launch_count", "dvo_gn_timing", "dvo_kernel_timing",
 ]
 
 
