@@ -62,6 +62,12 @@ struct dvo_ctx {
     std::vector<int> k_ev_id;
     size_t k_ev_used = 0;
     bool rows_only_staged = false; // d_stage_in holds only the sampled input rows (host path)
+    // pipelined submission (dvo_vo_submit / dvo_vo_collect)
+    cudaStream_t copy_stream = nullptr;
+    float* d_stage_pp[2] = {nullptr, nullptr};
+    cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_consumed[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
+    uint64_t pp_head = 0;
+    int pp_in_flight = 0;
     // VO host mirror
     int vo_frame_id = -1;
     std::mt19937 engine; // default seed 5489, src/math/gaussian.cpp:8
@@ -279,6 +285,12 @@ extern "C" void dvo_destroy(dvo_ctx* ctx)
     for (int k = 0; k < 3; k++) cudaFree(ctx->d_stage[k]);
     cudaFree(ctx->d_small); cudaFree(ctx->d_ismall); cudaFree(ctx->d_forced);
     if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
+    if (ctx->copy_stream) {
+        cudaStreamSynchronize(ctx->copy_stream);
+        cudaFree(ctx->d_stage_pp[1]);
+        for (int k = 0; k < 2; k++) { cudaEventDestroy(ctx->ev_copied[k]); cudaEventDestroy(ctx->ev_consumed[k]); cudaEventDestroy(ctx->ev_done[k]); }
+        cudaStreamDestroy(ctx->copy_stream);
+    }
     for (auto e : ctx->k_ev) cudaEventDestroy(e);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -376,21 +388,22 @@ static int build_frame(dvo_ctx* ctx, int slot, const float* gray_dev, bool rows_
 
 // Host frame -> device staging.  Convert::cullImage only samples rows that are multiples of 2^culls,
 // so when the geometry allows one uniform pitch only those rows cross PCIe (1/2^culls of the bytes).
-static int stage_gray(dvo_ctx* ctx, const float* gray, bool* rows_only)
+static int stage_gray_to(dvo_ctx* ctx, float* dst, cudaStream_t st, const float* gray, bool* rows_only)
 {
     const Consts& c = ctx->c;
     const int step = 1 << c.culls;
     const LevelGeom& gt = c.lv[c.L - 1];
     if (c.culls > 0 && c.in_h % step == 0 && gt.h == c.in_h / step) {
-        CK(cudaMemcpy2DAsync(ctx->d_stage_in, sizeof(float) * (size_t)c.in_w, gray, sizeof(float) * (size_t)c.in_w * step,
-                             sizeof(float) * (size_t)c.in_w, (size_t)c.S * gt.h, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpy2DAsync(dst, sizeof(float) * (size_t)c.in_w, gray, sizeof(float) * (size_t)c.in_w * step,
+                             sizeof(float) * (size_t)c.in_w, (size_t)c.S * gt.h, cudaMemcpyHostToDevice, st));
         *rows_only = true;
     } else {
-        CK(cudaMemcpyAsync(ctx->d_stage_in, gray, sizeof(float) * (size_t)c.S * c.in_w * c.in_h, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(dst, gray, sizeof(float) * (size_t)c.S * c.in_w * c.in_h, cudaMemcpyHostToDevice, st));
         *rows_only = false;
     }
     return DVO_OK;
 }
+static int stage_gray(dvo_ctx* ctx, const float* gray, bool* rows_only) { return stage_gray_to(ctx, ctx->d_stage_in, ctx->stream, gray, rows_only); }
 
 extern "C" int dvo_frame_create_dev(dvo_ctx* ctx, int* slot, const float* gray_dev)
 {
@@ -806,6 +819,60 @@ extern "C" int dvo_rng_position(dvo_ctx* ctx, uint64_t* pos)
     return DVO_OK;
 }
 
+// Scratch device buffer of the granular entry points below (freed on every exit path).
+struct DevScratch {
+    void* p = nullptr;
+    ~DevScratch() { if (p) cudaFree(p); }
+};
+
+extern "C" int dvo_map_update_points(dvo_ctx* ctx, int obj_slot, int born_slot, const float* relative_xi, int n, const int* px,
+                                     const int* py, const float* depth, const float* sigma, float* out_depth, float* out_sigma)
+{
+    int rc = check_slot(ctx, obj_slot);
+    if (rc) return rc;
+    rc = check_slot(ctx, born_slot);
+    if (rc) return rc;
+    const Consts& c = ctx->c;
+    ARG(relative_xi && n > 0 && px && py && depth && sigma && out_depth && out_sigma, "bad argument");
+    const size_t N = (size_t)c.S * n;
+    DevScratch sc;
+    CK(cudaMalloc(&sc.p, N * 24 + sizeof(float) * 6 * (size_t)c.S));
+    int* d_px = (int*)sc.p; int* d_py = d_px + N;
+    float* d_d = (float*)(d_py + N); float* d_s = d_d + N; float* d_od = d_s + N; float* d_os = d_od + N; float* d_xi = d_os + N;
+    CK(cudaMemcpyAsync(d_px, px, N * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d_py, py, N * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d_d, depth, N * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d_s, sigma, N * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d_xi, relative_xi, sizeof(float) * 6 * (size_t)c.S, cudaMemcpyHostToDevice, ctx->stream));
+    k_update_points<<<dim3(cdiv(n, 64), c.S), 64, 0, ctx->stream>>>(c, ctx->slots[obj_slot].dev, ctx->slots[born_slot].dev, d_xi, n, d_px, d_py,
+                                                                   d_d, d_s, d_od, d_os);
+    KCHECK();
+    CK(cudaMemcpyAsync(out_depth, d_od, N * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(out_sigma, d_os, N * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return DVO_OK;
+}
+
+// ---- se3 algebra ----------------------------------------------------------------------------
+static int se3_op(dvo_ctx* ctx, int op, const float* a, int na, const float* b, float* out, int nout, int n)
+{
+    ARG(a && out && n > 0 && (op != 2 || b), "bad argument");
+    DevScratch sc;
+    const size_t ba = sizeof(float) * (size_t)na * n, bo = sizeof(float) * (size_t)nout * n;
+    CK(cudaMalloc(&sc.p, 2 * ba + bo));
+    float* d_a = (float*)sc.p; float* d_b = d_a + (size_t)na * n; float* d_o = d_b + (size_t)na * n;
+    CK(cudaMemcpyAsync(d_a, a, ba, cudaMemcpyHostToDevice, ctx->stream));
+    if (b) CK(cudaMemcpyAsync(d_b, b, ba, cudaMemcpyHostToDevice, ctx->stream));
+    k_se3_ops<<<cdiv(n, 64), 64, 0, ctx->stream>>>(op, d_a, d_b, d_o, n);
+    KCHECK();
+    CK(cudaMemcpyAsync(out, d_o, bo, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return DVO_OK;
+}
+extern "C" int dvo_se3_exp(dvo_ctx* ctx, const float* xi, float* T, int n) { return se3_op(ctx, 0, xi, 6, nullptr, T, 16, n); }
+extern "C" int dvo_se3_log(dvo_ctx* ctx, const float* T, float* xi, int n) { return se3_op(ctx, 1, T, 16, nullptr, xi, 6, n); }
+extern "C" int dvo_se3_concatenate(dvo_ctx* ctx, const float* a, const float* b, float* out, int n) { return se3_op(ctx, 2, a, 6, b, out, 6, n); }
+
 // ---- mask compaction ------------------------------------------------------------------------
 extern "C" int dvo_mask_compact(dvo_ctx* ctx, const uint8_t* mask, int n, int32_t* idx, int* count)
 {
@@ -879,7 +946,10 @@ extern "C" int dvo_vo_force_pose(dvo_ctx* ctx, const float* rel_xi)
     return DVO_OK;
 }
 
-extern "C" int dvo_vo_push_dev(dvo_ctx* ctx, const float* gray_dev, const float* init_depth, const float* init_sigma, float* T_out)
+// One odometrize for every stream, enqueued on the context's stream.  after_cull (nullable) is recorded
+// once the staging buffer has been consumed; sync_out = false leaves the pose read-back asynchronous.
+static int vo_push_impl(dvo_ctx* ctx, const float* gray_dev, const float* init_depth, const float* init_sigma, float* T_out,
+                        cudaEvent_t after_cull, bool sync_out)
 {
     const Consts& c = ctx->c;
     ARG(gray_dev, "null gray");
@@ -901,6 +971,7 @@ extern "C" int dvo_vo_push_dev(dvo_ctx* ctx, const float* gray_dev, const float*
     int rc = build_frame(ctx, -1, gray_dev, ctx->rows_only_staged); // make_shared<Frame>(gray, K, 3, 2), system.hpp:47
     ctx->rows_only_staged = false;
     if (rc) return rc;
+    if (after_cull) CK(cudaEventRecord(after_cull, ctx->stream));
     if (init_depth || init_sigma) {
         rc = set_depth_impl(ctx, -1, init_depth, init_sigma, nullptr, 0);
         if (rc) return rc;
@@ -923,20 +994,81 @@ extern "C" int dvo_vo_push_dev(dvo_ctx* ctx, const float* gray_dev, const float*
         k_pose_out<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_vo, ctx->d_small);
         KCHECK();
         CK(cudaMemcpyAsync(T_out, ctx->d_small, sizeof(float) * 16 * (size_t)c.S, cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaStreamSynchronize(ctx->stream));
+        if (sync_out) CK(cudaStreamSynchronize(ctx->stream));
     }
     return DVO_OK;
+}
+
+extern "C" int dvo_vo_push_dev(dvo_ctx* ctx, const float* gray_dev, const float* init_depth, const float* init_sigma, float* T_out)
+{
+    return vo_push_impl(ctx, gray_dev, init_depth, init_sigma, T_out, nullptr, true);
 }
 
 extern "C" int dvo_vo_push(dvo_ctx* ctx, const float* gray, const float* init_depth, const float* init_sigma, float* T_out)
 {
     ARG(gray, "null gray");
-    const Consts& c = ctx->c;
     bool rows_only = false;
     int rc = stage_gray(ctx, gray, &rows_only);
     if (rc) return rc;
     ctx->rows_only_staged = rows_only;
-    return dvo_vo_push_dev(ctx, ctx->d_stage_in, init_depth, init_sigma, T_out);
+    // d_stage_in doubles as pipeline buffer 0: tell a later dvo_vo_submit when this frame has consumed it
+    return vo_push_impl(ctx, ctx->d_stage_in, init_depth, init_sigma, T_out, ctx->copy_stream ? ctx->ev_consumed[0] : nullptr, true);
+}
+
+// Pipelined submission: two staging buffers filled on a copy stream, so frame n+1 crosses PCIe while
+// frame n's kernels run.
+static int pipe_init(dvo_ctx* ctx)
+{
+    if (ctx->copy_stream) return DVO_OK;
+    const Consts& c = ctx->c;
+    CK(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    ctx->d_stage_pp[0] = ctx->d_stage_in;
+    CK(cudaMalloc(&ctx->d_stage_pp[1], sizeof(float) * (size_t)c.S * c.in_w * c.in_h));
+    for (int k = 0; k < 2; k++) {
+        CK(cudaEventCreateWithFlags(&ctx->ev_copied[k], cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&ctx->ev_consumed[k], cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&ctx->ev_done[k], cudaEventDisableTiming));
+    }
+    return DVO_OK;
+}
+
+extern "C" int dvo_vo_submit(dvo_ctx* ctx, const float* gray, float* T_out)
+{
+    ARG(gray, "null gray");
+    if (ctx->pp_in_flight >= 2) {
+        ctx->err = "dvo_vo_submit: two frames already in flight (call dvo_vo_collect)";
+        return DVO_ERR_STATE;
+    }
+    int rc = pipe_init(ctx);
+    if (rc) return rc;
+    const int k = (int)(ctx->pp_head & 1);
+    // the buffer's previous contents must have been consumed, and d_stage_in (buffer 0) may also have been
+    // filled by a plain dvo_vo_push on the compute stream before
+    CK(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_consumed[k], 0));
+    bool rows_only = false;
+    rc = stage_gray_to(ctx, ctx->d_stage_pp[k], ctx->copy_stream, gray, &rows_only);
+    if (rc) return rc;
+    CK(cudaEventRecord(ctx->ev_copied[k], ctx->copy_stream));
+    CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_copied[k], 0));
+    ctx->rows_only_staged = rows_only;
+    rc = vo_push_impl(ctx, ctx->d_stage_pp[k], nullptr, nullptr, T_out, ctx->ev_consumed[k], false);
+    if (rc) return rc;
+    CK(cudaEventRecord(ctx->ev_done[k], ctx->stream));
+    ctx->pp_head++;
+    ctx->pp_in_flight++;
+    return DVO_OK;
+}
+
+extern "C" int dvo_vo_collect(dvo_ctx* ctx)
+{
+    if (ctx->pp_in_flight <= 0) {
+        ctx->err = "dvo_vo_collect: nothing in flight";
+        return DVO_ERR_STATE;
+    }
+    const int k = (int)((ctx->pp_head - ctx->pp_in_flight) & 1);
+    CK(cudaEventSynchronize(ctx->ev_done[k]));
+    ctx->pp_in_flight--;
+    return DVO_OK;
 }
 
 extern "C" int dvo_vo_state(dvo_ctx* ctx, float* xi, float* rel_xi, int* was_keyframe, int* n_keyframes, int* valid_updates, int* n_iters)

@@ -1100,6 +1100,57 @@ __global__ void k_vo_gather_xi(const __grid_constant__ Consts c, const SlotDev* 
     for (int q = 0; q < 6; q++) { out[12 * s + q] = sd.xi[6 * s + q]; out[12 * s + 6 + q] = sd.rel_xi[6 * s + q]; }
 }
 
+// math::se3::{exp, log, concatenate} (src/math/se3.cpp:76-131) for n operands.  op 0: exp(a) -> out[16];
+// 1: log(a[16]) -> out[6]; 2: concatenate(a, b) -> out[6].
+__global__ void k_se3_ops(int op, const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ out, int n)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    if (op == 0) {
+        float xi[6], T[16];
+        for (int q = 0; q < 6; q++) xi[q] = a[6 * i + q];
+        se3_exp(xi, T);
+        for (int q = 0; q < 16; q++) out[16 * i + q] = T[q];
+    } else if (op == 1) {
+        float T[16], xi[6];
+        for (int q = 0; q < 16; q++) T[q] = a[16 * i + q];
+        se3_log(T, xi);
+        for (int q = 0; q < 6; q++) out[6 * i + q] = xi[q];
+    } else {
+        float x[6], y[6], r[6];
+        for (int q = 0; q < 6; q++) { x[q] = a[6 * i + q]; y[q] = b[6 * i + q]; }
+        se3_concatenate(x, y, r);
+        for (int q = 0; q < 6; q++) out[6 * i + q] = r[q];
+    }
+}
+
+// Map::Implement::update (implement.cpp:182-214) for a list of points.  grid = (ceil(n/64), S)
+__global__ void __launch_bounds__(64) k_update_points(const __grid_constant__ Consts c, SlotDev obj, SlotDev born, const float* __restrict__ rxi,
+                                                      int n, const int* __restrict__ px, const int* __restrict__ py,
+                                                      const float* __restrict__ depth, const float* __restrict__ sigma,
+                                                      float* __restrict__ out_d, float* __restrict__ out_s)
+{
+    const int s = blockIdx.y;
+    const LevelGeom g = c.lv[c.L - 1];
+    __shared__ float T[12];
+    __shared__ float tneg[3];
+    if (threadIdx.x == 0) {
+        se3_exp_neg12(rxi + 6 * s, T); // exp(-xi): implement.cpp:56,193
+        for (int q = 0; q < 3; q++) tneg[q] = -rxi[6 * s + q];
+    }
+    __syncthreads();
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const size_t k = (size_t)s * n + i;
+    const int x = px[k], y = py[k];
+    float nd = -1.f, ns = -1.f;
+    if (in_range(x, y, g.w, g.h)) {
+        const float og = __ldg(obj.gray + (size_t)s * g.n + (size_t)y * g.w + x);
+        implement_update(born.gray + (size_t)s * g.n, g, T, tneg, x, y, og, depth[k], sigma[k], nd, ns);
+    }
+    out_d[k] = nd; out_s[k] = ns;
+}
+
 // =============================================================================================
 // Row-major mask compaction (decoupled 2-pass: block counts, then offsets + scatter).
 // =============================================================================================

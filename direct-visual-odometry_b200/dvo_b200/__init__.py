@@ -46,6 +46,7 @@ EXPORTS = [
     "dvo_mask_compact", "dvo_vo_reset", "dvo_vo_reserve", "dvo_vo_force_pose", "dvo_vo_push", "dvo_vo_push_dev", "dvo_vo_state", "dvo_vo_ref_slot",
     "dvo_vo_last_slot", "dvo_vo_last_log", "dvo_vo_counters", "dvo_vo_error", "dvo_synth_render_dev", "dvo_dev_alloc", "dvo_dev_free",
     "dvo_copy_to_host", "dvo_copy_to_dev", "dvo_timer_start", "dvo_timer_stop", "dvo_launch_count", "dvo_gn_timing", "dvo_kernel_timing",
+    "dvo_map_update_points", "dvo_se3_exp", "dvo_se3_log", "dvo_se3_concatenate", "dvo_vo_submit", "dvo_vo_collect",
 ]
 
 
@@ -110,6 +111,12 @@ def load_library(path=None):
     lib.dvo_launch_count.argtypes = [C.c_void_p]
     lib.dvo_gn_timing.argtypes = [C.c_void_p, C.c_int, F32P, I32P]
     lib.dvo_kernel_timing.argtypes = [C.c_void_p, C.c_int, C.POINTER(DvoKernelTime), C.c_int, I32P]
+    lib.dvo_map_update_points.argtypes = [C.c_void_p, C.c_int, C.c_int, F32P, C.c_int, I32P, I32P, F32P, F32P, F32P, F32P]
+    lib.dvo_se3_exp.argtypes = [C.c_void_p, F32P, F32P, C.c_int]
+    lib.dvo_se3_log.argtypes = [C.c_void_p, F32P, F32P, C.c_int]
+    lib.dvo_se3_concatenate.argtypes = [C.c_void_p, F32P, F32P, F32P, C.c_int]
+    lib.dvo_vo_submit.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.dvo_vo_collect.argtypes = [C.c_void_p]
     return lib
 
 
@@ -273,6 +280,34 @@ class Dvo:
 
     def map_regularize(self, slot):
         self._ck(self.lib.dvo_map_regularize(self.ctx, slot))
+
+    def map_update_points(self, obj_slot, born_slot, relative_xi, px, py, depth, sigma):
+        """Map::Implement::update for [S][n] points -> (depth, sigma), (-1, -1) on failure."""
+        S = self.S
+        px = np.ascontiguousarray(np.asarray(px, np.int32).reshape(S, -1)); py = np.ascontiguousarray(np.asarray(py, np.int32).reshape(S, -1))
+        d = np.ascontiguousarray(np.asarray(depth, np.float32).reshape(S, -1)); sg = np.ascontiguousarray(np.asarray(sigma, np.float32).reshape(S, -1))
+        n = px.shape[1]
+        od = np.empty((S, n), np.float32); os_ = np.empty((S, n), np.float32)
+        xi = self._xi(relative_xi)
+        self._ck(self.lib.dvo_map_update_points(self.ctx, obj_slot, born_slot, _p(xi), n, px.ctypes.data_as(I32P), py.ctypes.data_as(I32P),
+                                                _p(d), _p(sg), _p(od), _p(os_)))
+        return od, os_
+
+    def se3_exp(self, xi):
+        xi = np.ascontiguousarray(np.asarray(xi, np.float32).reshape(-1, 6)); T = np.empty((len(xi), 4, 4), np.float32)
+        self._ck(self.lib.dvo_se3_exp(self.ctx, _p(xi), _p(T), len(xi)))
+        return T
+
+    def se3_log(self, T):
+        T = np.ascontiguousarray(np.asarray(T, np.float32).reshape(-1, 16)); xi = np.empty((len(T), 6), np.float32)
+        self._ck(self.lib.dvo_se3_log(self.ctx, _p(T), _p(xi), len(T)))
+        return xi
+
+    def se3_concatenate(self, a, b):
+        a = np.ascontiguousarray(np.asarray(a, np.float32).reshape(-1, 6)); b = np.ascontiguousarray(np.asarray(b, np.float32).reshape(-1, 6))
+        out = np.empty_like(a)
+        self._ck(self.lib.dvo_se3_concatenate(self.ctx, _p(a), _p(b), _p(out), len(a)))
+        return out
 
     def rng_position(self):
         pos = (C.c_uint64 * self.S)()

@@ -136,8 +136,23 @@ int dvo_map_update(dvo_ctx* ctx, int obj_slot, int ref_slot, const int* history_
 /* Mapper::regularize (src/map/mapper.cpp:139-144) = Implement::regularize (implement.cpp:156-180)
  * + Frame::updateDepth. */
 int dvo_map_regularize(dvo_ctx* ctx, int slot);
+/* Map::Implement::update (include/map/implement.hpp:10-19, src/map/implement.cpp:182-214) for a batch
+ * of n points per stream: epipolar search of obj_slot's pixel (px, py) in born_slot's finest-level
+ * gray along the segment of prior (depth, sigma) under relative_xi, then depthEstimate + sigmaEstimate.
+ * relative_xi: [n_streams][6]; px, py: [n_streams][n]; depth, sigma: [n_streams][n];
+ * out_depth, out_sigma: [n_streams][n], (-1, -1) where the reference returns failure. */
+int dvo_map_update_points(dvo_ctx* ctx, int obj_slot, int born_slot, const float* relative_xi, int n, const int* px,
+                          const int* py, const float* depth, const float* sigma, float* out_depth, float* out_sigma);
 /* mt19937 replay position (draws consumed so far by Gaussian::update resets), per stream. */
 int dvo_rng_position(dvo_ctx* ctx, uint64_t* pos /*[n_streams]*/);
+
+/* ---- se3 algebra: math::se3 (include/math/se3.hpp, src/math/se3.cpp:76-131) ---------------------
+ * Evaluated by the device code the tracker itself uses (cv::Rodrigues restated, lazy MatExpr order),
+ * so host-side pose bookkeeping (Frame::updateXi, frame.cpp:7-14) agrees with the kernels bit for bit.
+ * n twists / matrices per call; xi: [n][6] (v, omega), T: [n][16] row-major 4x4. */
+int dvo_se3_exp(dvo_ctx* ctx, const float* xi, float* T, int n);                        /* se3::exp   se3.cpp:76-99 */
+int dvo_se3_log(dvo_ctx* ctx, const float* T, float* xi, int n);                        /* se3::log   se3.cpp:102-124 */
+int dvo_se3_concatenate(dvo_ctx* ctx, const float* a, const float* b, float* out, int n); /* log(exp(a)*exp(b)) se3.cpp:127-131 */
 
 /* ---- mask compaction ----------------------------------------------------------- */
 /* Row-major compaction of a byte mask on device: idx receives the linear indices of non-zero
@@ -156,6 +171,14 @@ int dvo_vo_reserve(dvo_ctx* ctx, int n_keyframes);
  * T_out ([n_streams][16], nullable) = se3::exp(frame->m_xi); passing NULL keeps the call async. */
 int dvo_vo_push(dvo_ctx* ctx, const float* gray, const float* init_depth, const float* init_sigma, float* T_out);
 int dvo_vo_push_dev(dvo_ctx* ctx, const float* gray_dev, const float* init_depth, const float* init_sigma, float* T_out);
+/* Pipelined form of dvo_vo_push for throughput: dvo_vo_submit stages `gray` (pinned host memory from
+ * dvo_host_alloc, kept untouched until the matching collect) on a copy stream into one of two device
+ * staging buffers and enqueues the frame behind it; it returns without waiting, so the next frame's
+ * host->device copy overlaps this frame's kernels.  T_out ([n_streams][16], pinned, nullable) is filled
+ * by the time the matching dvo_vo_collect returns.  At most 2 frames may be in flight; collect returns
+ * them in submission order.  Results are identical to dvo_vo_push. */
+int dvo_vo_submit(dvo_ctx* ctx, const float* gray, float* T_out);
+int dvo_vo_collect(dvo_ctx* ctx);
 /* Supply the relative pose (frame-from-keyframe twist, [n_streams][6]) the NEXT dvo_vo_push uses for
  * Frame::updateXi (frame.cpp:7-14) and mapping instead of its own tracking result; the tracker still
  * runs and its iterations stay readable through dvo_vo_last_log.  Used for teacher-forced parity
