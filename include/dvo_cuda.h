@@ -19,6 +19,7 @@
  */
 #ifndef DVO_CUDA_H
 #define DVO_CUDA_H
+#include <stddef.h>
 #include <stdint.h>
 #ifdef __cplusplus
 extern "C" {
