@@ -20,7 +20,7 @@ inline Mat1f warpImage(const Mat1f& xi, const Mat1f& gray_image, const Mat1f& de
     float tw[6];
     for (int i = 0; i < 6; i++) tw[i] = xi(i);
     Mat1f out(gray_image.rows, gray_image.cols);
-    ctx->check(dvo_warp_image(ctx->h, slot.id, 0, tw, out.ptr<float>(0)));
+    ctx->check(dvo_warp_image(ctx->h, slot.id, 0, tw, dvo::data(out)));
     return out;
 }
 }  // namespace Transform

@@ -49,7 +49,7 @@ public:
     Mat1f levelK(int level) const
     {
         Mat1f K(3, 3);
-        check(dvo_level_K(h, level, K.ptr<float>(0)));
+        check(dvo_level_K(h, level, dvo::data(K)));
         return K;
     }
 
@@ -140,7 +140,7 @@ public:
     Mat1f download(int level, int kind) const
     {
         Mat1f out(ctx->levelRows(level), ctx->levelCols(level));
-        ctx->check(dvo_frame_download(ctx->h, id, level, kind, out.ptr<float>(0)));
+        ctx->check(dvo_frame_download(ctx->h, id, level, kind, dvo::data(out)));
         return out;
     }
 

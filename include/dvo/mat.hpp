@@ -18,6 +18,8 @@
 namespace dvo {
 using Mat1f = cv::Mat1f;
 using Point2i = cv::Point2i;
+inline float* data(Mat1f& m) { return reinterpret_cast<float*>(m.data); }
+inline const float* data(const Mat1f& m) { return reinterpret_cast<const float*>(m.data); }
 }  // namespace dvo
 #else
 namespace dvo {
@@ -69,6 +71,9 @@ private:
     std::shared_ptr<float> m_data;
 };
 
+inline float* data(Mat1f& m) { return m.ptr<float>(0); }
+inline const float* data(const Mat1f& m) { return m.ptr<float>(0); }
+
 }  // namespace dvo
 #endif
 
@@ -89,9 +94,9 @@ inline void require(bool ok, const char* what)
 // continuous float pointer of an image (clones a non-continuous cv::Mat view)
 inline const float* pixels(const Mat1f& m, Mat1f& keep)
 {
-    if (m.isContinuous()) return m.template ptr<float>(0);
+    if (m.isContinuous()) return data(m);
     keep = m.clone();
-    return keep.template ptr<float>(0);
+    return data(keep);
 }
 
 }  // namespace dvo

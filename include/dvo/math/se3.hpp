@@ -39,7 +39,7 @@ inline Mat1f exp(const Mat1f& twist)
     float in[6];
     for (int i = 0; i < 6; i++) in[i] = twist(i);
     Mat1f out(4, 4);
-    ctx->check(dvo_se3_exp(ctx->h, in, out.ptr<float>(0), 1));
+    ctx->check(dvo_se3_exp(ctx->h, in, dvo::data(out), 1));
     return out;
 }
 // se3::log (src/math/se3.cpp:102-124): 4x4 -> 6x1
@@ -51,7 +51,7 @@ inline Mat1f log(const Mat1f& pose)
     for (int r = 0; r < 4; r++)
         for (int c = 0; c < 4; c++) in[r * 4 + c] = pose(r, c);
     Mat1f out(6, 1);
-    ctx->check(dvo_se3_log(ctx->h, in, out.ptr<float>(0), 1));
+    ctx->check(dvo_se3_log(ctx->h, in, dvo::data(out), 1));
     return out;
 }
 // se3::concatenate (src/math/se3.cpp:127-131): log(exp(a) * exp(b))
@@ -62,7 +62,7 @@ inline Mat1f concatenate(const Mat1f& a, const Mat1f& b)
     float x[6], y[6];
     for (int i = 0; i < 6; i++) { x[i] = a(i); y[i] = b(i); }
     Mat1f out(6, 1);
-    ctx->check(dvo_se3_concatenate(ctx->h, x, y, out.ptr<float>(0), 1));
+    ctx->check(dvo_se3_concatenate(ctx->h, x, y, dvo::data(out), 1));
     return out;
 }
 }  // namespace se3

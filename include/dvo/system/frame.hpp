@@ -92,7 +92,7 @@ public:
             const float d = dist(priorEngine());
             depth(i) = d < 0.5f ? 0.5f : d;
         }
-        ctx().check(dvo_frame_set_depth(ctx().h, m_slot->id, depth.ptr<float>(0), sigma.ptr<float>(0), nullptr, 0));
+        ctx().check(dvo_frame_set_depth(ctx().h, m_slot->id, dvo::data(depth), dvo::data(sigma), nullptr, 0));
     }
 
     static std::mt19937& priorEngine()

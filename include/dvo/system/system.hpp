@@ -63,10 +63,10 @@ public:
             }
             dvo::require(m_init_depth.rows == h && m_init_depth.cols == w && m_init_sigma.rows == h && m_init_sigma.cols == w,
                          "initial depth/sigma must have the finest level's size");
-            d = m_init_depth.ptr<float>(0);
-            s = m_init_sigma.ptr<float>(0);
+            d = dvo::data(m_init_depth);
+            s = dvo::data(m_init_sigma);
         }
-        c.check(dvo_vo_push(c.h, dvo::pixels(gray_image, keep), d, s, T.ptr<float>(0)));
+        c.check(dvo_vo_push(c.h, dvo::pixels(gray_image, keep), d, s, dvo::data(T)));
         c.check(dvo_vo_error(c.h));
         return T;
     }
@@ -97,7 +97,7 @@ public:
         State st;
         st.xi = Mat1f(6, 1); st.relative_xi = Mat1f(6, 1);
         int kf = 0;
-        m_vo->check(dvo_vo_state(m_vo->h, st.xi.ptr<float>(0), st.relative_xi.ptr<float>(0), &kf, &st.n_keyframes, &st.valid_updates, &st.iterations));
+        m_vo->check(dvo_vo_state(m_vo->h, dvo::data(st.xi), dvo::data(st.relative_xi), &kf, &st.n_keyframes, &st.valid_updates, &st.iterations));
         st.was_keyframe = kf != 0;
         return st;
     }
@@ -108,7 +108,7 @@ public:
         int slot = -1;
         m_vo->check(dvo_vo_ref_slot(m_vo->h, 0, &slot));
         Mat1f out(m_vo->levelRows(level), m_vo->levelCols(level));
-        m_vo->check(dvo_frame_download(m_vo->h, slot, level, kind, out.ptr<float>(0)));
+        m_vo->check(dvo_frame_download(m_vo->h, slot, level, kind, dvo::data(out)));
         return out;
     }
 

@@ -33,7 +33,7 @@ struct Stuff {
         for (int i = 0; i < 6; i++) tw[i] = xi(i);
         Mat1f out(rows, cols);
         dvo::Context& c = *ref->slot()->ctx;
-        c.check(dvo_warp_image(c.h, ref->slot()->id, ref->level(), tw, out.ptr<float>(0)));
+        c.check(dvo_warp_image(c.h, ref->slot()->id, ref->level(), tw, dvo::data(out)));
         return out;
     }
 

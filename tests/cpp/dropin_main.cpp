@@ -24,13 +24,13 @@ static void put(const float* p, int n)
     fwrite(&n, sizeof(int), 1, g_out);
     fwrite(p, sizeof(float), (size_t)n, g_out);
 }
-static void put(const Mat1f& m) { put(m.ptr<float>(0), (int)m.total()); }
+static void put(const Mat1f& m) { put(dvo::data(m), (int)m.total()); }
 static void put(float v) { put(&v, 1); }
 
 static Mat1f read_mat(FILE* f, int h, int w)
 {
     Mat1f m(h, w);
-    if (fread(m.ptr<float>(0), sizeof(float), (size_t)h * w, f) != (size_t)h * w) {
+    if (fread(dvo::data(m), sizeof(float), (size_t)h * w, f) != (size_t)h * w) {
         fprintf(stderr, "short read\n");
         exit(2);
     }

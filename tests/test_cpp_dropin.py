@@ -48,6 +48,13 @@ def test_each_header_is_self_contained():
                                    "/dev/null"])
 
 
+def test_compiles_against_cv_mat1f():
+    """DVO_WITH_OPENCV: dvo::Mat1f is cv::Mat1f.  OpenCV C++ is not installed in this image, so the cv::Mat1f used
+    here is the oracle's OpenCV-API shim (test infrastructure) — syntax check only, nothing is linked."""
+    shim = os.path.join(ROOT, "oracle", "shim")
+    subprocess.check_call(["g++", "-std=c++17", "-fsyntax-only", "-DDVO_WITH_OPENCV", "-I" + shim, "-I" + os.path.join(ROOT, "include"), SRC])
+
+
 def test_no_cpu_fallback(tmp_path):
     if has_gpu():
         pytest.skip("GPU present")
