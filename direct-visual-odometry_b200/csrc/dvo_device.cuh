@@ -105,6 +105,37 @@ __device__ __forceinline__ float subpixel_dense(const float* __restrict__ img, i
     return bilerp(g0, g1, g2, g3, hh, v);
 }
 
+// The same, split into position, loads and arithmetic, so that a caller can put several samples' loads in
+// flight before consuming any of them, or take the four texels from elsewhere when (x0, y0) coincide.
+struct TapPos {
+    int x0, y0;
+    float hh, v;
+    bool in; // (x0, y0) inside the image
+};
+struct Texels {
+    float g0, g1, g2, g3;
+};
+__device__ __forceinline__ TapPos tap_pos(int w, int h, float px, float py)
+{
+    TapPos t;
+    t.x0 = trunc_x86(px); t.y0 = trunc_x86(py);
+    t.in = in_range(t.x0, t.y0, w, h);
+    t.hh = px - (float)t.x0; t.v = py - (float)t.y0;
+    return t;
+}
+__device__ __forceinline__ Texels tap_fetch(const float* __restrict__ img, int w, int h, const TapPos& t)
+{
+    Texels g;
+    const float* p = img + (size_t)t.y0 * w + t.x0;
+    const bool xin = t.x0 + 1 < w, yin = t.y0 + 1 < h;
+    g.g0 = __ldg(p);
+    g.g1 = xin ? __ldg(p + 1) : g.g0;
+    g.g2 = yin ? __ldg(p + w) : g.g0;
+    g.g3 = (xin && yin) ? __ldg(p + w + 1) : g.g0;
+    return g;
+}
+__device__ __forceinline__ float tap_value(const TapPos& t, const Texels& g) { return t.in ? bilerp(g.g0, g.g1, g.g2, g.g3, t.hh, t.v) : DVO_INV; }
+
 // ---------------------------------------------------------------------------------------------
 // se3 / so3 — src/math/se3.cpp.  Transcendentals: the reference calls glibc (double for
 // Rodrigues/acos, float overloads elsewhere); here every one is evaluated in double and rounded,

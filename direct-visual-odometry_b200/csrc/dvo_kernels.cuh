@@ -711,64 +711,193 @@ struct NormLess {
     }
 };
 
-__device__ inline void implement_update(const float* __restrict__ born_gray, const LevelGeom& g, const float* __restrict__ T,
-                                        const float* __restrict__ tneg, int px, int py, float og, float depth, float sigma,
-                                        float& new_depth, float& new_sigma)
-{
-    const int w = g.w, h = g.h;
-    const float dmin = (depth - sigma) < 0.10f ? 0.10f : (depth - sigma); // :30
-    const float dmax = depth + sigma;
-    float sx, sy, ex, ey;
-    warp_point(T, g, (float)px, (float)py, dmax, sx, sy); // start :31
-    warp_point(T, g, (float)px, (float)py, dmin, ex, ey); // end   :32
-    const float length = (float)point_norm(sx - ex, sy - ey); // :33
+// ---------------------------------------------------------------------------------------------
+// doMatching (implement.cpp:106-152) as a WARP-COOPERATIVE search.  The reference walks each pixel's
+// epipolar segment serially; segment lengths differ wildly between neighbouring pixels (1 .. 102 steps,
+// measured lane efficiency of a one-pixel-per-lane loop: 0.26-0.37), so the (pixel, step) pairs of the 32
+// pixels of a warp are flattened and dealt out 32 at a time:
+//   1. every lane walks its own segment WITHOUT sampling (pt += dir, the reference's float accumulation,
+//      and the `norm(pt - start) < length` / 102-step stop rules) to learn its step count, leaving a
+//      checkpoint of pt every 8 steps in shared memory;
+//   2. the work unit is a CHUNK of 8 consecutive steps of one pixel, starting exactly on a checkpoint; an
+//      inclusive warp scan of the chunk counts orders all chunks of the warp;
+//   3. lane i of round r takes chunk (32 r + i): a head-lane table gives (pixel p, chunk c); the lane runs the
+//      reference's loop body for steps 8c+1 .. 8c+8 from the checkpoint (same additions in the same order as
+//      the serial walk; the tap pt + dir is bit-for-bit the next step's centre tap and is carried over);
+//   4. the weighted SSD (float accumulator, double terms, implement.cpp:134) is packed with the step index
+//      into one 64-bit key (ssd >= 0: its bit pattern is monotonic); the lane keeps the smallest key of its
+//      chunk, a segmented warp min (redux.sync) keeps, per pixel, the smallest ssd and among equal ones the
+//      earliest step — the reference's strict `<` rule.
+// Results are bit-identical to the serial walk.
+// ---------------------------------------------------------------------------------------------
+#ifdef DVO_MAP_STATS
+__device__ unsigned long long g_map_stats[8]; // [0] steps, [1] lane slots spent on them
+__device__ unsigned int g_map_hist[128];
+#endif
 
-    // doMatching :106-152.  The three taps of a step are pt - dir, pt, pt + dir; the last one is the
-    // next step's centre tap (same coordinates bit for bit), so it is carried over instead of re-sampled.
-    const float dirx = (ex - sx) / length, diry = (ey - sy) / length;
-    float ptx = sx, pty = sy, bestx = sx, besty = sy;
-    float min_ssd = 2.0f * 3;
-    int count = 0;
-    const NormLess shorter_than(length);
-    bool have_c = false;
-    float carry = 0.f;
-    while (shorter_than(ptx - sx, pty - sy)) {
-        float ssd = 0;
-        ptx += dirx;
-        pty += diry;
-        bool next_have = false;
-        float next = 0.f;
-        {
-            const float s0 = subpixel_dense(born_gray, w, h, ptx + dirx * -1.0f, pty + diry * -1.0f);
-            if (is_invalid(s0)) {
-                ssd = 2.0f * 3;
-            } else {
-                const float d0 = s0 - og;
-                ssd = (float)__dadd_rn((double)ssd, __dmul_rn(1.0 * 1 / 3, (double)(d0 * d0))); // :134
-                const float s1 = have_c ? carry : subpixel_dense(born_gray, w, h, ptx + dirx * 0.0f, pty + diry * 0.0f);
-                if (is_invalid(s1)) {
-                    ssd = 2.0f * 3;
-                } else {
-                    const float d1 = s1 - og;
-                    ssd = (float)__dadd_rn((double)ssd, __dmul_rn(1.0 * 2 / 3, (double)(d1 * d1)));
-                    const float s2 = subpixel_dense(born_gray, w, h, ptx + dirx * 1.0f, pty + diry * 1.0f);
-                    next = s2; next_have = true;
-                    if (is_invalid(s2)) {
-                        ssd = 2.0f * 3;
-                    } else {
-                        const float d2 = s2 - og;
-                        ssd = (float)__dadd_rn((double)ssd, __dmul_rn(1.0 * 3 / 3, (double)(d2 * d2)));
-                    }
-                }
+#ifndef DVO_CP_SHIFT
+#define DVO_CP_SHIFT 3
+#endif
+constexpr int SEARCH_CP_SHIFT = DVO_CP_SHIFT;     // checkpoint every 2^shift steps
+constexpr int SEARCH_NCP = (102 >> SEARCH_CP_SHIFT) + 1; // steps 0, 8, ..., 96
+#ifndef DVO_SEARCH_UNROLL
+#define DVO_SEARCH_UNROLL 1
+#endif
+constexpr int SEARCH_UNROLL = DVO_SEARCH_UNROLL; // steps of a chunk whose loads are in flight together
+struct SearchSmem { // per warp
+    float2 cp[SEARCH_NCP][32];
+    float dirx[32], diry[32], og[32];
+    const float* born[32];
+    int nsteps[32];
+    int2 owner[32]; // per round: run head lane -> {pixel, first chunk index of the pixel}
+    unsigned long long best[32];
+};
+
+__device__ __forceinline__ float search_ssd(float s0, float s1, float s2, float og)
+{
+    // implement.cpp:122-139: a tap that is invalid ends the accumulation with ssd = 2.0 * 3
+    if (is_invalid(s0) || is_invalid(s1) || is_invalid(s2)) return 2.0f * 3;
+    const float d0 = s0 - og, d1 = s1 - og, d2 = s2 - og;
+    float ssd = (float)__dadd_rn(0.0, __dmul_rn(1.0 * 1 / 3, (double)(d0 * d0))); // :134
+    ssd = (float)__dadd_rn((double)ssd, __dmul_rn(1.0 * 2 / 3, (double)(d1 * d1)));
+    ssd = (float)__dadd_rn((double)ssd, __dmul_rn(1.0 * 3 / 3, (double)(d2 * d2)));
+    return ssd;
+}
+
+// All 32 lanes of the warp must call this (active = false for lanes without a segment).  w, h are warp-uniform.
+__device__ __forceinline__ void warp_search(SearchSmem& sm, bool active, const float* __restrict__ born_gray, int w, int h, float sx,
+                                            float sy, float dirx, float diry, float length, float og, float& bestx, float& besty,
+                                            float& min_ssd)
+{
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    // 1. dry walk: step count + checkpoints.  The stop rule `norm(pt - start) < length` (fp64) cannot fire
+    // during the first (int)length - 2 steps: |dir| <= 1 + 3 * 2^-24 and, for |start| < 2^14, the float
+    // accumulation drifts by < 0.1 px per 102 steps — so those steps only accumulate pt (bit-identical walk).
+    int n = 0;
+    sm.cp[0][lane] = make_float2(sx, sy);
+    if (active) {
+        float ptx = sx, pty = sy;
+        int nskip = 0;
+        if (fabsf(sx) < 16384.f && fabsf(sy) < 16384.f && length < 16384.f) nskip = min((int)length - 2, 100);
+        for (; n < nskip;) {
+            ptx += dirx;
+            pty += diry;
+            n++;
+            if ((n & ((1 << SEARCH_CP_SHIFT) - 1)) == 0) sm.cp[n >> SEARCH_CP_SHIFT][lane] = make_float2(ptx, pty);
+        }
+        const NormLess shorter_than(length);
+        while (shorter_than(ptx - sx, pty - sy)) { // :120
+            ptx += dirx;
+            pty += diry;
+            n++;
+            if ((n & ((1 << SEARCH_CP_SHIFT) - 1)) == 0) sm.cp[n >> SEARCH_CP_SHIFT][lane] = make_float2(ptx, pty);
+            if (n > 101) break; // `if (count++ > 100) break` :141 -> at most 102 steps
+        }
+    }
+    // 2. work unit = one CHUNK of 2^SEARCH_CP_SHIFT consecutive steps of one pixel (it starts exactly on a
+    // checkpoint); inclusive scan of the chunk counts
+    const int nch = (n + (1 << SEARCH_CP_SHIFT) - 1) >> SEARCH_CP_SHIFT;
+    int incl = nch;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const int v = __shfl_up_sync(full, incl, off);
+        if (lane >= off) incl += v;
+    }
+    const int excl = incl - nch;
+    const int total = __shfl_sync(full, incl, 31);
+    sm.dirx[lane] = dirx; sm.diry[lane] = diry; sm.og[lane] = og; sm.born[lane] = born_gray; sm.nsteps[lane] = n;
+    const unsigned long long key0 = (unsigned long long)__float_as_uint(2.0f * 3) << 32; // min_ssd = 6, best = start (step 0)
+    sm.best[lane] = key0;
+    __syncwarp();
+#ifdef DVO_MAP_STATS
+    if (lane == 0) { atomicAdd(&g_map_stats[0], (unsigned long long)__reduce_add_sync(full, n)); atomicAdd(&g_map_stats[1], (unsigned long long)((total + 31) / 32) * 32 << SEARCH_CP_SHIFT); }
+#endif
+    // 3./4. flattened chunks, 32 per round
+    for (int base = 0; base < total; base += 32) {
+        const int wi = base + lane;
+        const bool on = wi < total;
+        // which pixel owns chunk wi: pixel q's run starts at lane (excl_q - base); runs are contiguous and ordered
+        const int p0 = __popc(__ballot_sync(full, incl <= base)); // the pixel that owns chunk `base`
+        const int st = excl - base;
+        const unsigned hb = (nch > 0 && st >= 0 && st < 32) ? (1u << st) : 0u;
+        const unsigned heads = __reduce_or_sync(full, hb) | 1u;
+        if (hb) sm.owner[st] = make_int2(lane, excl);
+        else if (lane == p0) sm.owner[0] = make_int2(lane, excl);
+        __syncwarp();
+        const int hp = 31 - __clz(heads & (0xffffffffu >> (31 - lane))); // head lane of this lane's run
+        if (on) {
+            const int2 o = sm.owner[hp];
+            const int p = o.x;
+            const int ch = wi - o.y;                       // chunk of pixel p: steps ch*2^k + 1 ... (ch+1)*2^k
+            const int b0 = ch << SEARCH_CP_SHIFT;
+            const int cnt = min(1 << SEARCH_CP_SHIFT, sm.nsteps[p] - b0);
+            const float2 cpt = sm.cp[ch][p];
+            float ptx = cpt.x, pty = cpt.y;
+            const float dx = sm.dirx[p], dy = sm.diry[p], ogp = sm.og[p];
+            const float* __restrict__ img = sm.born[p];
+            // the reference's loop body (implement.cpp:121-140) for steps b0+1 .. b0+cnt: the tap pt + dir is, bit for
+            // bit, the next step's centre tap and is carried over instead of re-sampled
+            float carry = 0.f;
+            unsigned long long kbest = ~0ull;
+#pragma unroll(SEARCH_UNROLL)
+            for (int k = 1; k <= cnt; k++) {
+                ptx += dx;
+                pty += dy;
+                const float s0 = subpixel_dense(img, w, h, ptx + dx * -1.0f, pty + dy * -1.0f);
+                const float s1 = (k > 1) ? carry : subpixel_dense(img, w, h, ptx + dx * 0.0f, pty + dy * 0.0f);
+                const float s2 = subpixel_dense(img, w, h, ptx + dx * 1.0f, pty + dy * 1.0f);
+                carry = s2;
+                const unsigned long long key = ((unsigned long long)__float_as_uint(search_ssd(s0, s1, s2, ogp)) << 32) | (unsigned)(b0 + k);
+                if (key < kbest) kbest = key;
+            }
+            // lanes [hp, rend) form this lane's run: smallest ssd of the run, at its earliest step
+            const unsigned above = (hp == 31) ? 0u : (heads >> (hp + 1)) << (hp + 1);
+            const int end = above ? __ffs(above) - 1 : 32;
+            const int rend = min(end, min(total - base, 32));
+            const unsigned seg = ((rend == 32) ? 0xffffffffu : ((1u << rend) - 1u)) & ~((1u << hp) - 1u);
+            const unsigned hi = (unsigned)(kbest >> 32), lo = (unsigned)kbest;
+            const unsigned m = __reduce_min_sync(seg, hi);
+            const unsigned bm = __reduce_min_sync(seg, hi == m ? lo : 0xffffffffu);
+            if (lane == hp) {
+                const unsigned long long key = ((unsigned long long)m << 32) | bm;
+                if (key < sm.best[p]) sm.best[p] = key;
             }
         }
-        have_c = next_have; carry = next;
-        if (ssd < min_ssd) {
-            bestx = ptx; besty = pty;
-            min_ssd = ssd;
-        }
-        if (count++ > 100) break;
+        __syncwarp();
     }
+    // 5. this lane's result
+    const unsigned long long kb = sm.best[lane];
+    min_ssd = __uint_as_float((unsigned)(kb >> 32));
+    const int bb = (int)(unsigned)kb;
+    const float2 c = sm.cp[bb >> SEARCH_CP_SHIFT][lane];
+    bestx = c.x; besty = c.y;
+    for (int r = bb & ((1 << SEARCH_CP_SHIFT) - 1); r > 0; r--) { bestx += dirx; besty += diry; }
+    __syncwarp(); // the shared arrays are reused by the warp's next call
+}
+
+// Epipolar segment of Implement::update (EpipolarSegment, implement.cpp:23-47).
+struct Segment {
+    float dmin, dmax, sx, sy, ex, ey, length;
+};
+__device__ __forceinline__ Segment make_segment(const LevelGeom& g, const float* __restrict__ T, int px, int py, float depth, float sigma)
+{
+    Segment e;
+    e.dmin = (depth - sigma) < 0.10f ? 0.10f : (depth - sigma); // :30
+    e.dmax = depth + sigma;
+    warp_point(T, g, (float)px, (float)py, e.dmax, e.sx, e.sy); // start :31
+    warp_point(T, g, (float)px, (float)py, e.dmin, e.ex, e.ey); // end   :32
+    e.length = (float)point_norm(e.sx - e.ex, e.sy - e.ey);     // :33
+    return e;
+}
+
+// Implement::update after doMatching: bounds check (:196-200), depthEstimate (:49-71), sigmaEstimate (:73-104).
+__device__ inline void implement_finish(const float* __restrict__ born_gray, const LevelGeom& g, const float* __restrict__ T,
+                                        const float* __restrict__ tneg, int px, int py, const Segment& e, float bestx, float besty,
+                                        float min_ssd, float& new_depth, float& new_sigma)
+{
+    const int w = g.w, h = g.h;
+    const float dmin = e.dmin, dmax = e.dmax, sx = e.sx, sy = e.sy, ex = e.ex, ey = e.ey, length = e.length;
     float mx = bestx, my = besty;
     if ((double)min_ssd > 3 * 0.1) { mx = -1; my = -1; } // :145
     if (mx < 0 || my < 0 || mx > (float)w || my > (float)h) { // :196-200
@@ -856,7 +985,10 @@ struct MapRoi {
 // Rejected pixels (Gaussian::update reset, gaussian.cpp:21-25) are only flagged here: their value
 // depends on the row-major rank among all rejects (mt19937 order) -> phase B.
 // grid = (roi.nblk, S)
-__global__ void __launch_bounds__(MAPU_THREADS, 16) k_map_update(const __grid_constant__ Consts c, const MapRoi roi, const SlotDev* __restrict__ slots,
+#ifndef DVO_MAPU_MINB
+#define DVO_MAPU_MINB 16
+#endif
+__global__ void __launch_bounds__(MAPU_THREADS, DVO_MAPU_MINB) k_map_update(const __grid_constant__ Consts c, const MapRoi roi, const SlotDev* __restrict__ slots,
                                                        MapState* __restrict__ mst, const int* __restrict__ hist,
                                                        const PoseTab* __restrict__ tab, uint8_t* __restrict__ flags,
                                                        unsigned int* __restrict__ blockcnt)
@@ -866,48 +998,67 @@ __global__ void __launch_bounds__(MAPU_THREADS, 16) k_map_update(const __grid_co
     if (!m->do_update) return;
     const LevelGeom g = c.lv[c.L - 1];
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    __shared__ SearchSmem s_search[MAPU_THREADS / 32];
     uint8_t fl = 0;
     bool reject = false;
+    // --- per pixel: candidate gate, keyframe lookup, epipolar segment (mapper.cpp:90-107, implement.cpp:23-47)
+    bool cand = false;
+    int i = 0, px = 0, py = 0;
+    float prior_d = 0.f, prior_s = 0.f, og = 0.f;
+    const float* born_gray = nullptr;
+    const PoseTab* pt = nullptr;
+    Segment seg{};
+    float2* ds = nullptr;
     if (j < roi.n) {
         const int ry = j / roi.w;
         const int x = roi.x0 + (j - ry * roi.w), y = roi.y0 + ry;
-        const int i = y * g.w + x;
+        i = y * g.w + x;
         const SlotDev ref = slots[m->ref_slot];
-        float2* ds = ref.ds + (size_t)s * g.n;
+        ds = ref.ds + (size_t)s * g.n;
         const float2 dsv = ds[i];
         const float d = dsv.x;
         float wx, wy;
         warp_point(m->Trel, g, (float)x, (float)y, d, wx, wy);
-        const int px = round_x86(wx), py = round_x86(wy); // Point2f -> Point2i :94
+        px = round_x86(wx); py = round_x86(wy); // Point2f -> Point2i :94
         if (in_range(px, py, g.w, g.h)) {
             const int age = trunc_x86(ref.age[(size_t)s * g.n + i]); // :99
             if (age < 0 || age >= m->n_hist) {
                 atomicCAS(&m->err, 0, (int)DVO_ERR_HISTORY); // m_history.at() would throw
             } else {
                 const int born_slot = hist[(size_t)s * c.max_kf + (m->n_hist - 1 - age)];
-                const PoseTab* pt = tab + (size_t)s * c.max_kf + age;
-                const float prior_d = d - m->rel_z; // :104
-                const float prior_s = dsv.y;
-                const float og = __ldg(slots[m->obj_slot].gray + (size_t)s * g.n + (size_t)py * g.w + px);
-                float nd, ns;
-                implement_update(slots[born_slot].gray + (size_t)s * g.n, g, pt->T, pt->t, px, py, og, prior_d, prior_s, nd, ns);
-                fl |= 1;
-                if (nd > c.acc_d_lo && nd < c.acc_d_hi && ns > 0.0f && ns < c.acc_s_hi) { // :122
-                    fl |= 2;
-                    // Gaussian::update (gaussian.cpp:12-31)
-                    float gd = prior_d, gs = prior_s;
-                    if (gaussian_fuse(gd, gs, nd, ns)) {
-                        fl |= 4;
-                        ds[i] = make_float2(gd, gs);
-                    } else {
-                        fl |= 8;
-                        reject = true;
-                    }
-                }
+                pt = tab + (size_t)s * c.max_kf + age;
+                prior_d = d - m->rel_z; // :104
+                prior_s = dsv.y;
+                og = __ldg(slots[m->obj_slot].gray + (size_t)s * g.n + (size_t)py * g.w + px);
+                born_gray = slots[born_slot].gray + (size_t)s * g.n;
+                seg = make_segment(g, pt->T, px, py, prior_d, prior_s);
+                cand = true;
             }
         }
-        flags[(size_t)s * g.n + i] = fl;
     }
+    // --- epipolar search, shared by the warp (implement.cpp:106-152)
+    float bestx, besty, min_ssd;
+    warp_search(s_search[threadIdx.x >> 5], cand, born_gray, g.w, g.h, seg.sx, seg.sy, (seg.ex - seg.sx) / seg.length,
+                (seg.ey - seg.sy) / seg.length, seg.length, og, bestx, besty, min_ssd);
+    // --- per pixel: depth / sigma estimate, gate, fusion (implement.cpp:196-212, mapper.cpp:122-131)
+    if (cand) {
+        float nd, ns;
+        implement_finish(born_gray, g, pt->T, pt->t, px, py, seg, bestx, besty, min_ssd, nd, ns);
+        fl |= 1;
+        if (nd > c.acc_d_lo && nd < c.acc_d_hi && ns > 0.0f && ns < c.acc_s_hi) { // :122
+            fl |= 2;
+            // Gaussian::update (gaussian.cpp:12-31)
+            float gd = prior_d, gs = prior_s;
+            if (gaussian_fuse(gd, gs, nd, ns)) {
+                fl |= 4;
+                ds[i] = make_float2(gd, gs);
+            } else {
+                fl |= 8;
+                reject = true;
+            }
+        }
+    }
+    if (j < roi.n) flags[(size_t)s * g.n + i] = fl;
     const int nrej = __syncthreads_count(reject);
     const int nval = __syncthreads_count((fl & 4) != 0);
     if (threadIdx.x == 0) {
@@ -1139,15 +1290,24 @@ __global__ void __launch_bounds__(64) k_update_points(const __grid_constant__ Co
         for (int q = 0; q < 3; q++) tneg[q] = -rxi[6 * s + q];
     }
     __syncthreads();
+    __shared__ SearchSmem s_search[2];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const size_t k = (size_t)s * n + i;
+    const size_t k = (size_t)s * n + (i < n ? i : 0);
     const int x = px[k], y = py[k];
-    float nd = -1.f, ns = -1.f;
-    if (in_range(x, y, g.w, g.h)) {
-        const float og = __ldg(obj.gray + (size_t)s * g.n + (size_t)y * g.w + x);
-        implement_update(born.gray + (size_t)s * g.n, g, T, tneg, x, y, og, depth[k], sigma[k], nd, ns);
+    const bool cand = i < n && in_range(x, y, g.w, g.h);
+    const float* born_gray = born.gray + (size_t)s * g.n;
+    float og = 0.f;
+    Segment seg{};
+    if (cand) {
+        og = __ldg(obj.gray + (size_t)s * g.n + (size_t)y * g.w + x);
+        seg = make_segment(g, T, x, y, depth[k], sigma[k]);
     }
+    float bestx, besty, min_ssd;
+    warp_search(s_search[threadIdx.x >> 5], cand, born_gray, g.w, g.h, seg.sx, seg.sy, (seg.ex - seg.sx) / seg.length,
+                (seg.ey - seg.sy) / seg.length, seg.length, og, bestx, besty, min_ssd);
+    float nd = -1.f, ns = -1.f;
+    if (cand) implement_finish(born_gray, g, T, tneg, x, y, seg, bestx, besty, min_ssd, nd, ns);
+    if (i >= n) return;
     out_d[k] = nd; out_s[k] = ns;
 }
 

@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 PKG_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-LIB_PATH = os.path.join(PKG_ROOT, "libdvo_cuda.so")
+LIB_PATH = os.environ.get("DVO_LIB") or os.path.join(PKG_ROOT, "libdvo_cuda.so")  # DVO_LIB: experiment builds
 F32P = C.POINTER(C.c_float)
 I32P = C.POINTER(C.c_int)
 U8P = C.POINTER(C.c_uint8)
