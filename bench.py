@@ -290,6 +290,9 @@ def run_gpu_arm(args, rank, world, local_rank, dist):
     dv.vo_reserve(n_total + W_ + E + 2)
     frame_bytes = S * H_IN * W_IN * 4
     h2d_bytes = S * (H_IN >> CULLS) * W_IN * 4 if (CULLS > 0 and H_IN % (1 << CULLS) == 0) else frame_bytes  # stage_gray_to()
+    # global sequence ids are sharded id mod world (dvo_b200/shard.py); a rank's S local streams are ids
+    # rank, rank + world, ... and the renderer seeds stream k of this context with seed0 + k: the bench uses the
+    # contiguous relabelling 1000 + rank * S + k (any bijection of independent sequences gives the same workload)
     seed0 = 1000 + rank * S
     # --- inputs: rendered on device, resident in HBM before the timed region starts
     dev = dv.dev_alloc(frame_bytes * n_dev_frames)
@@ -321,13 +324,10 @@ def run_gpu_arm(args, rank, world, local_rank, dist):
         if dist is not None:
             dist.barrier()
 
-    def maxrank(x):
-        if dist is None:
-            return x
-        import torch
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+    from dvo_b200 import shard
+
+    def maxrank(x):  # slowest rank's time (device-timed), dvo_b200/shard.py
+        return shard.max_over_ranks(x, dist, device="cuda")
 
     # --- first keyframe + warm-up
     def fptr(i):  # ping-pong over the resident frames
