@@ -1,0 +1,161 @@
+"""BASELINE.json configs[0] and configs[1] on the reference's BUNDLED data.
+
+tests/golden/bundled_golden.npz holds (a) the pixels `Frame(.)` samples from data/KINECT_50MM entries 9, 10
+(test/track.cpp:12-25, through KinectLoader::getMappedImages) and from the first frames of data/logicool0
+(main.cpp:22-49, through Loader::getNormalizedUndistortedImages), and (b) what THE REFERENCE'S OWN CODE
+(oracle/_ref) computed from them; tests/golden/make_bundled.py made it.  Nothing here reads /root/reference.
+
+  * CPU: the plain-C oracle reproduces the reference bit for bit;
+  * `gpu`: the CUDA path through the C ABI — schedules, valid-pixel counts, keyframe decisions, ages bit-exact;
+    per-iteration pose updates within 1e-5 (se3 norm), poses within 1e-4, depth / sigma maps within 1e-4 relative.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from helpers import se3_norm
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+UPD_TOL, POSE_TOL, REL_TOL = 1e-5, 1e-4, 1e-4
+
+
+@pytest.fixture(scope="module")
+def B():
+    return dict(np.load(os.path.join(HERE, "golden", "bundled_golden.npz")))
+
+
+def up(a, k):
+    return np.ascontiguousarray(np.repeat(np.repeat(a, k, axis=0), k, axis=1))
+
+
+def c1_frames(B):
+    assert set(np.unique(B["c1_sigma10"]).tolist()) <= {1, 10}  # transform.cpp:56,73: sigma is 0.1 where mapped, else 1.0
+    s = np.where(B["c1_sigma10"] == 1, np.float32(0.1), np.float32(1.0)).astype(np.float32)
+    return [(up(B["c1_gray"][i], 2), up(B["c1_depth"][i], 2), up(s[i], 2)) for i in (0, 1)]
+
+
+def c2_gray(B):
+    c = B["c2_codes"]
+    g = (c.astype(np.float64) * (1.0 / 255.0)).astype(np.float32)  # convertTo(CV_32FC1, 1.0/255.0), loader.cpp:61
+    return np.where(c < 0, np.float32(-2.0), g).astype(np.float32)
+
+
+def log_meta(logs):
+    return np.array([[L["level"], L["iteration"], L["valid_pixels"]] for L in logs], np.int32).reshape(-1, 3)
+
+
+def maps_close(a, b):
+    a = np.asarray(a); b = np.asarray(b)
+    return a.tobytes() == b.tobytes() or bool(np.isclose(a, b, rtol=REL_TOL, atol=0).all())
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU: oracle == reference, bit for bit
+# ------------------------------------------------------------------------------------------------
+def test_oracle_c1_kinect_track(orc, B):
+    (g1, d1, s1), (g2, d2, s2) = c1_frames(B)
+    K = B["c1_K"]
+    pre = orc.frame_create(g1, K, 4, 1, d1, s1)
+    cur = orc.frame_create(g2, K, 4, 1, d2, s2)
+    assert [pre.image(l, "gray").shape for l in range(4)] == [(26, 32), (53, 64), (106, 128), (212, 256)]
+    xi, logs = orc.track(cur, pre)
+    assert np.array_equal(log_meta(logs), B["c1_log_meta"])
+    assert np.array_equal(np.array([L["residual"] for L in logs], np.float32), B["c1_log_residual"])
+    assert np.array_equal(np.array([L["update"] for L in logs], np.float32), B["c1_log_update"])
+    assert np.array_equal(xi, B["c1_xi"])
+    for lv in range(4):
+        im = {k: pre.image(lv, k) for k in ("gray", "depth", "sigma", "gradx", "grady")}
+        x = np.zeros(6, np.float32)
+        warped = orc.warp_image(x, im["gray"], im["depth"], pre.K(lv))
+        u, r, v, _ = orc.optimize(cur.image(lv, "gray"), warped, im["depth"], im["sigma"], im["gradx"], im["grady"], pre.K(lv), x, lv)
+        row = B["c1_gn%d" % lv]
+        assert v == int(row[7]) and v > 100
+        assert np.float32(r) == np.float32(row[6]) and np.array_equal(u, row[:6].astype(np.float32))
+
+
+def test_oracle_c2_logicool_vo(orc, B):
+    gray = c2_gray(B)
+    vo = orc.vo_create(B["c2_K"], 3, 2)
+    d0 = B["c2_init_depth"]; s0 = np.full_like(d0, 0.5)
+    pos = 0
+    for i in range(len(gray)):
+        T = vo.odometrize(up(gray[i], 4), d0 if i == 0 else None, s0 if i == 0 else None)
+        assert np.array_equal(T, B["c2_T"][i]), i
+        assert vo.last_was_keyframe() == bool(B["c2_keyframe"][i]) and vo.history_size() == int(B["c2_n_keyframes"][i])
+        n = int(B["c2_n_iters"][i])
+        logs = vo.last_log() if i else []
+        assert len(logs) == n
+        assert np.array_equal(log_meta(logs), B["c2_log_meta"][pos:pos + n])
+        for k, L in enumerate(logs):
+            assert L["residual"] == B["c2_log_residual"][pos + k] and np.array_equal(L["update"], B["c2_log_update"][pos + k])
+        pos += n
+        if i and not vo.last_was_keyframe():
+            assert vo.last_valid_update() == int(B["c2_valid_update"][i])
+    fr = vo.ref_frame()
+    assert np.array_equal(fr.image(2, "depth"), B["c2_kf_depth"]) and np.array_equal(fr.image(2, "sigma"), B["c2_kf_sigma"])
+    assert np.array_equal(fr.image(2, "age"), B["c2_kf_age"].astype(np.float32))
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU: CUDA path through the C ABI against the reference's outputs
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.gpu
+def test_gpu_c1_kinect_track(B):
+    """configs[0]: test/track.cpp — Frame(., 4, 1) on the registered 512x424 Kinect pair, Tracker::track."""
+    from conftest import make_dvo
+    (g1, d1, s1), (g2, d2, s2) = c1_frames(B)
+    dv = make_dvo(width=512, height=424, levels=4, culls=1, K=B["c1_K"])
+    pre = dv.frame_create(g1); dv.frame_set_depth(pre, d1, s1, None, full_res=True)
+    cur = dv.frame_create(g2); dv.frame_set_depth(cur, d2, s2, None, full_res=True)
+    assert [dv.level_size(l) for l in range(4)] in ([(32, 26), (64, 53), (128, 106), (256, 212)],
+                                                    [(26, 32), (53, 64), (106, 128), (212, 256)])
+    for lv in range(4):  # Track::optimize from xi = 0 at every level: valid count exact
+        upd, res, valid, _ = dv.gn_step(cur, pre, lv, np.zeros(6, np.float32))
+        row = B["c1_gn%d" % lv]
+        assert int(valid[0]) == int(row[7])
+        assert se3_norm(upd[0], row[:6]) <= UPD_TOL
+        assert abs(float(res[0]) - row[6]) <= 1e-6 * max(1.0, abs(row[6]))
+    xi, logs = dv.track(cur, pre)
+    assert np.array_equal(log_meta(logs[0]), B["c1_log_meta"])
+    for L, u, r in zip(logs[0], B["c1_log_update"], B["c1_log_residual"]):
+        assert se3_norm(L["update"], u) <= UPD_TOL
+        assert abs(L["residual"] - r) <= 1e-6 * max(1.0, abs(r))
+    assert se3_norm(xi[0], B["c1_xi"]) <= POSE_TOL
+    dv.close()
+
+
+@pytest.mark.gpu
+def test_gpu_c2_logicool_vo(B):
+    """configs[1]: main.cpp's loop on data/logicool0 (teacher-forced, see tests/test_gpu_vo.py)."""
+    from conftest import make_dvo
+    gray = c2_gray(B)
+    n = len(gray)
+    dv = make_dvo(width=640, height=480, levels=3, culls=2, K=B["c2_K"], max_frames=2, max_keyframes=n + 2)
+    d0 = B["c2_init_depth"]; s0 = np.full_like(d0, 0.5)
+    pos = 0
+    for i in range(n):
+        if i:
+            dv.vo_force_pose(B["c2_rel_xi"][i])
+        T = dv.vo_push(up(gray[i], 4), d0 if i == 0 else None, s0 if i == 0 else None)
+        st = dv.vo_state()
+        assert dv.vo_error() == 0
+        k = int(B["c2_n_iters"][i])
+        if i:
+            logs = dv.vo_last_log()[0]
+            assert np.array_equal(log_meta(logs), B["c2_log_meta"][pos:pos + k]), i
+            for L, u in zip(logs, B["c2_log_update"][pos:pos + k]):
+                assert se3_norm(L["update"], u) <= UPD_TOL
+            if k:
+                assert se3_norm(logs[-1]["xi_after"], B["c2_rel_xi"][i]) <= POSE_TOL
+        pos += k
+        assert bool(st["was_keyframe"][0]) == bool(B["c2_keyframe"][i])
+        assert int(st["n_keyframes"][0]) == int(B["c2_n_keyframes"][i])
+        if i and not B["c2_keyframe"][i]:
+            assert int(st["valid_updates"][0]) == int(B["c2_valid_update"][i])
+        assert np.abs(T[0] - B["c2_T"][i]).max() <= POSE_TOL
+    slot = dv.vo_ref_slot(0)
+    assert np.array_equal(dv.frame_download(slot, 2, "age")[0], B["c2_kf_age"].astype(np.float32))
+    assert maps_close(dv.frame_download(slot, 2, "depth")[0], B["c2_kf_depth"])
+    assert maps_close(dv.frame_download(slot, 2, "sigma")[0], B["c2_kf_sigma"])
+    dv.close()
