@@ -574,6 +574,23 @@ extern "C" int dvo_kernel_timing(dvo_ctx* ctx, int enable, dvo_kernel_time* out,
     return DVO_OK;
 }
 
+#ifdef DVO_TRK_PROF
+// experiment builds only (scripts/trk_phases.py): per-phase nanoseconds of stream 0 inside k_track
+extern "C" int dvo_debug_trk_prof(dvo_ctx* ctx, unsigned long long* out, int reset)
+{
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (out) CK(cudaMemcpyFromSymbol(out, g_trk_prof, sizeof(unsigned long long) * 8));
+    if (reset) { unsigned long long z[8] = {0}; CK(cudaMemcpyToSymbol(g_trk_prof, z, sizeof(z))); }
+    return DVO_OK;
+}
+extern "C" int dvo_debug_trk_streams(dvo_ctx* ctx, unsigned int* out, int n)
+{
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpyFromSymbol(out, g_trk_stream_ns, sizeof(unsigned int) * (size_t)(n < 1024 ? n : 1024)));
+    return DVO_OK;
+}
+#endif
+
 extern "C" int dvo_gn_timing(dvo_ctx* ctx, int enable, float* total_ms, int* launches)
 {
     if (enable) return dvo_kernel_timing(ctx, 1, nullptr, 0, nullptr);

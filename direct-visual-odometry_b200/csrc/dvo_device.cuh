@@ -188,7 +188,9 @@ __device__ inline void rodrigues(const float* w, float* R)
         R[0] = 1; R[1] = 0; R[2] = 0; R[3] = 0; R[4] = 1; R[5] = 0; R[6] = 0; R[7] = 0; R[8] = 1;
         return;
     }
-    double c = cos(theta), s = sin(theta), c1 = 1. - c, it = 1. / theta;
+    double c, s;
+    sincos(theta, &s, &c); // same reduction and kernels as sin() and cos(); one range reduction instead of two
+    const double c1 = 1. - c, it = 1. / theta;
     rx = __dmul_rn(rx, it); ry = __dmul_rn(ry, it); rz = __dmul_rn(rz, it);
     double rrt[9] = {__dmul_rn(rx, rx), __dmul_rn(rx, ry), __dmul_rn(rx, rz), __dmul_rn(rx, ry), __dmul_rn(ry, ry),
                      __dmul_rn(ry, rz), __dmul_rn(rx, rz), __dmul_rn(ry, rz), __dmul_rn(rz, rz)};
@@ -202,8 +204,11 @@ __device__ inline void rodrigues(const float* w, float* R)
 __device__ __forceinline__ float cosf_ref(float x) { return (float)cos((double)x); }
 __device__ __forceinline__ float sinf_ref(float x) { return (float)sin((double)x); }
 
-// se3::exp (se3.cpp:70-98); T: 16 floats row-major
-__device__ inline void se3_exp(const float* xi, float* T)
+// se3::exp (se3.cpp:70-98); T: 16 floats row-major.  Tn12 (optional) receives exp(-xi) as 12 floats from the same
+// transcendentals: cv::Rodrigues(-w) is bit for bit the transpose of cv::Rodrigues(w) (theta, c, s, r r^T are even in w,
+// [r]x is odd and rounding is symmetric), hat(-w)^2 == hat(w)^2 exactly, and the a/b, c/d factors depend on |w| only; the
+// V matrix and the translation of exp(-xi) are then evaluated with the negated operands in the reference's order.
+__device__ inline void se3_exp(const float* xi, float* T, float* Tn12 = nullptr)
 {
     const float* v = xi;
     const float* w = xi + 3;
@@ -212,11 +217,13 @@ __device__ inline void se3_exp(const float* xi, float* T)
     float wl = norm3(w);
     float R[9];
     rodrigues(w, R);
-    float t[3];
+    float t[3], tn[3];
     if (wl > 1e-6f) {
-        float a = 1.0f - cosf_ref(wl);
+        double sn, cs;
+        sincos((double)wl, &sn, &cs);
+        float a = 1.0f - (float)cs;
         float b = wl * wl;
-        float c = wl - sinf_ref(wl);
+        float c = wl - (float)sn;
         float d = wl * wl * wl;
         float w_hat2[9], V[9];
         mat3_mul(w_hat, w_hat, w_hat2);
@@ -234,13 +241,31 @@ __device__ inline void se3_exp(const float* xi, float* T)
             V[k] = m1 + m2;
         }
         mat3_vec(V, v, t);
+        if (Tn12) {
+            float wn[3] = {-w[0], -w[1], -w[2]}, vn[3] = {-v[0], -v[1], -v[2]}, wn_hat[9];
+            hat(wn, wn_hat);
+#pragma unroll
+            for (int k = 0; k < 9; k++) {
+                float eye = (k == 0 || k == 4 || k == 8) ? 1.0f : 0.0f;
+                float m1 = wn_hat[k] * alpha1f + eye;
+                float m2 = w_hat2[k] * (float)alpha2;
+                V[k] = m1 + m2;
+            }
+            mat3_vec(V, vn, tn);
+        }
     } else {
         t[0] = v[0]; t[1] = v[1]; t[2] = v[2];
+        tn[0] = -v[0]; tn[1] = -v[1]; tn[2] = -v[2];
     }
     T[0] = R[0]; T[1] = R[1]; T[2] = R[2];  T[3] = t[0];
     T[4] = R[3]; T[5] = R[4]; T[6] = R[5];  T[7] = t[1];
     T[8] = R[6]; T[9] = R[7]; T[10] = R[8]; T[11] = t[2];
     T[12] = 0;   T[13] = 0;   T[14] = 0;    T[15] = 1;
+    if (Tn12) {
+        Tn12[0] = R[0]; Tn12[1] = R[3]; Tn12[2] = R[6];  Tn12[3] = tn[0];
+        Tn12[4] = R[1]; Tn12[5] = R[4]; Tn12[6] = R[7];  Tn12[7] = tn[1];
+        Tn12[8] = R[2]; Tn12[9] = R[5]; Tn12[10] = R[8]; Tn12[11] = tn[2];
+    }
 }
 // so3::log (se3.cpp:31-43)
 __device__ inline void so3_log(const float* R, float* w)
@@ -269,7 +294,9 @@ __device__ inline void se3_log(const float* T, float* xi)
     float wl = norm3(w);
     float V_inv[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
     if (wl > 1e-6f) {
-        float k = 1.0f - (wl * cosf_ref(wl * 0.5f)) / (2.0f * sinf_ref(wl * 0.5f));
+        double snh, csh;
+        sincos((double)(wl * 0.5f), &snh, &csh);
+        float k = 1.0f - (wl * (float)csh) / (2.0f * (float)snh);
         float b = wl * wl;
         float w_hat2[9];
         mat3_mul(w_hat, w_hat, w_hat2);
@@ -292,6 +319,19 @@ __device__ inline void se3_concatenate(const float* a, const float* b, float* ou
 {
     float Ta[16], Tb[16], Tc[16];
     se3_exp(a, Ta);
+    se3_exp(b, Tb);
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+            Tc[i * 4 + j] = Ta[i * 4 + 0] * Tb[0 * 4 + j] + Ta[i * 4 + 1] * Tb[1 * 4 + j] + Ta[i * 4 + 2] * Tb[2 * 4 + j]
+                            + Ta[i * 4 + 3] * Tb[3 * 4 + j];
+    se3_log(Tc, out);
+}
+// se3::concatenate when exp(a) is already at hand (Ta: 16 floats, as se3_exp(a) returns it)
+__device__ inline void se3_concatenate_T(const float* Ta, const float* b, float* out)
+{
+    float Tb[16], Tc[16];
     se3_exp(b, Tb);
 #pragma unroll
     for (int i = 0; i < 4; i++)

@@ -14,7 +14,11 @@
 namespace dvo {
 
 constexpr int MAXL = DVO_MAX_LEVELS;
-constexpr int TRK_THREADS = 256; // threads per tracking CTA
+#ifndef DVO_TRK_THREADS
+#define DVO_TRK_THREADS 512
+#endif
+constexpr int TRK_THREADS = DVO_TRK_THREADS;   // threads per tracking CTA
+constexpr int TRK_MINB = 1024 / TRK_THREADS;   // <= 64 registers per thread: 1024 tracking threads per SM
 constexpr int NACC = 29;         // 21 J^T J + 6 J^T (w r) + sum r^2 + valid count
 
 // Geometry + constants, passed to kernels by value (__grid_constant__).

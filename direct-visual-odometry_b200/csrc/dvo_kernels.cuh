@@ -215,7 +215,7 @@ __global__ void __launch_bounds__(256) k_warp_image(const __grid_constant__ Cons
 // SVD back-substitution threshold (w_i <= 2*FLT_EPSILON*sum(w) dropped) so the minimum-norm
 // solution is returned like OpenCV's SVBkSb.
 // =============================================================================================
-__device__ inline void solve6_eigen(const double* H, const double* b, double* x)
+__device__ __noinline__ void solve6_eigen(const double* H, const double* b, double* x)
 {
     double A[36], V[36];
     for (int i = 0; i < 36; i++) { A[i] = H[i]; V[i] = 0; }
@@ -264,38 +264,55 @@ __device__ inline void solve6_eigen(const double* H, const double* b, double* x)
     }
 }
 
-__device__ inline void solve6(const double* H, const double* b, double* x)
+// H: upper triangle, row-major packed (21 values: 00 01 .. 05 11 12 .. 55), as the reduction delivers it.
+// Fully unrolled (everything in registers, no local-memory indexing) with one rsqrt per pivot: the diagonal of L is
+// only ever used as a divisor, so 1/L_jj is what is kept.  This runs on ONE thread per stream while the stream's other
+// threads wait, so its latency is on the critical path of every Gauss-Newton iteration.
+__device__ __forceinline__ int tri6(int p, int q) { return p * 6 - (p * (p - 1)) / 2 + (q - p); } // p <= q
+__device__ __noinline__ void solve6(const double* Hp, const double* b, double* x)
 {
-    double Lm[36];
+    double Lm[6][6], inv[6];
     double dmax = 0;
-    for (int i = 0; i < 6; i++) dmax = fmax(dmax, H[i * 6 + i]);
+#pragma unroll
+    for (int i = 0; i < 6; i++) dmax = fmax(dmax, Hp[tri6(i, i)]);
     bool ok = dmax > 0;
-    for (int j = 0; j < 6 && ok; j++) {
-        double sum = H[j * 6 + j];
-        for (int k = 0; k < j; k++) sum -= Lm[j * 6 + k] * Lm[j * 6 + k];
-        if (!(sum > dmax * 1e-11)) { ok = false; break; }
-        double ljj = sqrt(sum);
-        Lm[j * 6 + j] = ljj;
+    const double thr = dmax * 1e-11;
+#pragma unroll
+    for (int j = 0; j < 6; j++) {
+        double sum = Hp[tri6(j, j)];
+#pragma unroll
+        for (int k = 0; k < j; k++) sum -= Lm[j][k] * Lm[j][k];
+        ok = ok && (sum > thr);
+        inv[j] = rsqrt(sum);
+#pragma unroll
         for (int i = j + 1; i < 6; i++) {
-            double s2 = H[i * 6 + j];
-            for (int k = 0; k < j; k++) s2 -= Lm[i * 6 + k] * Lm[j * 6 + k];
-            Lm[i * 6 + j] = s2 / ljj;
+            double s2 = Hp[tri6(j, i)];
+#pragma unroll
+            for (int k = 0; k < j; k++) s2 -= Lm[i][k] * Lm[j][k];
+            Lm[i][j] = s2 * inv[j];
         }
     }
     if (!ok) {
+        double H[36];
+        for (int p = 0; p < 6; p++)
+            for (int q = p; q < 6; q++) H[p * 6 + q] = H[q * 6 + p] = Hp[tri6(p, q)];
         solve6_eigen(H, b, x);
         return;
     }
     double yv[6];
+#pragma unroll
     for (int i = 0; i < 6; i++) {
         double s2 = b[i];
-        for (int k = 0; k < i; k++) s2 -= Lm[i * 6 + k] * yv[k];
-        yv[i] = s2 / Lm[i * 6 + i];
+#pragma unroll
+        for (int k = 0; k < i; k++) s2 -= Lm[i][k] * yv[k];
+        yv[i] = s2 * inv[i];
     }
+#pragma unroll
     for (int i = 5; i >= 0; i--) {
         double s2 = yv[i];
-        for (int k = i + 1; k < 6; k++) s2 -= Lm[k * 6 + i] * x[k];
-        x[i] = s2 / Lm[i * 6 + i];
+#pragma unroll
+        for (int k = i + 1; k < 6; k++) s2 -= Lm[k][i] * x[k];
+        x[i] = s2 * inv[i];
     }
 }
 
@@ -337,7 +354,8 @@ struct TrackArgs {
 
 struct TrackCtl { // per-CTA copy of the stream's iteration state
     int level, iter, done;
-    float T[12];
+    float T[12];  // exp(-xi): what the pixels are warped with
+    float Tp[16]; // exp(xi): left operand of the next se3::concatenate (leader CTA only)
 };
 
 // One Gauss-Newton tail: solve, compose, log, stop rules (optimize.cpp:92-98, tracker.cpp:46-73).
@@ -349,12 +367,8 @@ __device__ __noinline__ void gn_tail(const Consts& c, const TrackArgs& a, TrackS
     float upd[6] = {0, 0, 0, 0, 0, 0};
     float residual = -1.0f; // optimize.cpp:92-93
     if (valid > 0) {
-        double H[36], bv[6], xs[6];
-        int idx = 0;
-        for (int p = 0; p < 6; p++)
-            for (int q = p; q < 6; q++) { H[p * 6 + q] = stot[idx]; H[q * 6 + p] = stot[idx]; idx++; }
-        for (int q = 0; q < 6; q++) bv[q] = stot[21 + q];
-        solve6(H, bv, xs);
+        double xs[6];
+        solve6(stot, stot + 21, xs);
         for (int q = 0; q < 6; q++) upd[q] = (float)xs[q];
         residual = (float)stot[27] / (float)valid; // optimize.cpp:98
     }
@@ -362,12 +376,15 @@ __device__ __noinline__ void gn_tail(const Consts& c, const TrackArgs& a, TrackS
     for (int q = 0; q < 6; q++) xi[q] = st->xi[q];
     const int n_total = st->n_total;
     const bool advance_pose = (st->mode == 0);
+    bool moved = false;
     if (advance_pose) {
-        se3_concatenate(xi, upd, xin); // tracker.cpp:46
+        se3_concatenate_T(ctl->Tp, upd, xin); // tracker.cpp:46; ctl->Tp = exp(xi) from the previous tail
         bool nan = false;
         for (int q = 0; q < 6; q++) nan |= isnan(xin[q]);
-        if (!nan) // tracker.cpp:47-51
+        if (!nan) { // tracker.cpp:47-51
             for (int q = 0; q < 6; q++) xi[q] = xin[q];
+            moved = true;
+        }
     }
     if (a.log && n_total < a.log_cap) {
         dvo_iter_log* L = a.log + (size_t)s * a.log_cap + n_total;
@@ -380,7 +397,7 @@ __device__ __noinline__ void gn_tail(const Consts& c, const TrackArgs& a, TrackS
         ctl->done = 1;
     } else {
         for (int q = 0; q < 6; q++) st->xi[q] = xi[q];
-        se3_exp_neg12(xi, ctl->T); // stuff.update(xi): the next iteration warps with exp(-xi)
+        if (moved) se3_exp(xi, ctl->Tp, ctl->T); // stuff.update(xi): the next iteration warps with exp(-xi)
         // stop rules, tracker.cpp:68-70 (time budget never reached)
         const bool stop = (norm_n(upd, 6) < st->stop_update) || (residual < st->stop_residual);
         int iter = ctl->iter + 1;
@@ -470,9 +487,17 @@ __device__ __noinline__ void vo_decide(const Consts& c, const TrackArgs& a, cons
     m->reg_slot = v->kf_slot;
 }
 
+#ifdef DVO_TRK_PROF
+__device__ unsigned int g_trk_stream_ns[1024]; // ns stream s spent in the last k_track launch
+__device__ unsigned long long g_trk_prof[8]; // ns of stream 0: [0] pixel loop, [1] reduce, [2] gn_tail, [3] iterations, [4] whole kernel
+__device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#define TRK_PROF(i, t0) do { if (s == 0 && b == 0 && tid == 0) { const unsigned long long t1_ = gtimer(); g_trk_prof[i] += t1_ - (t0); (t0) = t1_; } } while (0)
+#else
+#define TRK_PROF(i, t0) do { } while (0)
+#endif
 __device__ __forceinline__ unsigned int ld_volatile_u32(const unsigned int* p) { return *(const volatile unsigned int*)p; }
 
-__global__ void __launch_bounds__(TRK_THREADS, 2) k_track(const __grid_constant__ Consts c, const TrackArgs a)
+__global__ void __launch_bounds__(TRK_THREADS, TRK_MINB) k_track(const __grid_constant__ Consts c, const TrackArgs a)
 {
     const int s = blockIdx.y, b = blockIdx.x, B = a.B;
     const int tid = threadIdx.x;
@@ -482,6 +507,7 @@ __global__ void __launch_bounds__(TRK_THREADS, 2) k_track(const __grid_constant_
     __shared__ TrackCtl ctl;
     __shared__ double sred[TRK_THREADS / 32][NACC + 1];
     __shared__ double stot[32];
+    __shared__ __align__(16) double srow[TRK_THREADS / 32][32][10]; // row pitch 80 B: conflict-free 16 B stores
     __shared__ const float* s_obj;
     __shared__ const float* s_ref;
     __shared__ const float2* s_ds;
@@ -505,7 +531,7 @@ __global__ void __launch_bounds__(TRK_THREADS, 2) k_track(const __grid_constant_
         s_ds = a.slots[ref_slot].ds + off;
         float xi[6];
         for (int q = 0; q < 6; q++) xi[q] = a.xi0 ? a.xi0[6 * s + q] : 0.f;
-        se3_exp_neg12(xi, ctl.T);
+        se3_exp(xi, ctl.Tp, ctl.T);
         ctl.level = a.level0; ctl.iter = 0; ctl.done = done;
         s_gen0 = (B > 1) ? ld_volatile_u32(&st->gen) : 0u;
         if (leader) {
@@ -522,14 +548,26 @@ __global__ void __launch_bounds__(TRK_THREADS, 2) k_track(const __grid_constant_
     const float2* __restrict__ ref_ds = s_ds;
     const unsigned int gen0 = s_gen0;
     unsigned int epoch = 0;
+    // product pair of this lane: 0..20 = J_p J_q (p <= q, row-major upper triangle), 21..26 = J_q (w r)
+    int pair_p = 0, pair_q = 0;
+    {
+        const int L = tid & 31;
+        if (L < 21) {
+            int p = 0, rem = L;
+            while (rem >= 6 - p) { rem -= 6 - p; p++; }
+            pair_p = p; pair_q = p + rem;
+        } else if (L < 27) { pair_p = L - 21; pair_q = 6; }
+    }
 
+#ifdef DVO_TRK_PROF
+    unsigned long long tp = gtimer();
+    const unsigned long long tp_start = tp;
+#endif
     while (!ctl.done) {
         const int level = ctl.level;
         const LevelGeom g = c.lv[level];
         const LevelView lv = level_view(c, level);
-        float T[12];
-#pragma unroll
-        for (int q = 0; q < 12; q++) T[q] = ctl.T[q];
+        const float* sT = ctl.T; // exp(-xi), read from shared memory (broadcast) where it is used
         float step = c.step_default; // optimize.cpp:22-26
         if (level == 1) step = c.step_level1;
         if (level == 2) step = c.step_level2;
@@ -543,26 +581,34 @@ __global__ void __launch_bounds__(TRK_THREADS, 2) k_track(const __grid_constant_
         const int per = (count + B - 1) / B;
         const int j0 = b * per, j1 = min(count, j0 + per);
 
-        double acc[NACC];
-#pragma unroll
-        for (int k = 0; k < NACC; k++) acc[k] = 0.0;
+        // Normal equations, accumulated PER SUM instead of per pixel: the 32 pixels of a warp-batch leave their
+        // row {J[0..5], w r} (as doubles) in shared memory and lane L folds product pair L of all 32 rows into ONE
+        // fp64 accumulator (21 J^T J + 6 J^T (w r)).  29 per-thread accumulators would cost 58 registers and cap
+        // the kernel at 2 x 256 threads per SM; this way it fits 64 registers (1024 threads per SM).
+        const int lane = tid & 31, warp = tid >> 5;
+        double accL = 0.0, accR = 0.0; // lane's pair sum; this thread's sum of r^2
+        int nvalid = 0;
+        double(*rows)[10] = srow[warp];
 
-        if (j0 + tid < j1) {
-            int j = j0 + tid;
-            int y = ry0 + j / rw, x = rx0 + (j - (j / rw) * rw);
-            const int sx = TRK_THREADS % rw, sy = TRK_THREADS / rw;
-            for (; j < j1; j += TRK_THREADS) {
+        for (int jb = j0 + warp * 32; jb < j1; jb += TRK_THREADS) {
+            const int j = jb + lane;
+            bool ok = false;
+            float J[6], bw = 0.f;
+            int x = 0, y = 0;
+            if (j < j1) {
+                const int jy = j / rw;
+                y = ry0 + jy; x = rx0 + (j - jy * rw);
                 const size_t ti = top_index(lv, x, y);
                 const float2 dsr = __ldg(ref_ds + ti);
                 const float depth = level_value(lv, dsr.x);
                 const float I1 = level_value(lv, __ldg(obj_gray + ti));
-                bool ok = !(depth < c.min_depth_f) && !is_invalid(I1); // optimize.cpp:39,46
+                ok = !(depth < c.min_depth_f) && !is_invalid(I1); // optimize.cpp:39,46
                 if (ok) {
                     float X, Y, Z;
                     back_project(g, (float)x, (float)y, depth, X, Y, Z);
-                    const float tx = (T[0] * X + T[1] * Y + T[2] * Z) + T[3];
-                    const float ty = (T[4] * X + T[5] * Y + T[6] * Z) + T[7];
-                    const float tz = (T[8] * X + T[9] * Y + T[10] * Z) + T[11];
+                    const float tx = (sT[0] * X + sT[1] * Y + sT[2] * Z) + sT[3];
+                    const float ty = (sT[4] * X + sT[5] * Y + sT[6] * Z) + sT[7];
+                    const float tz = (sT[8] * X + sT[9] * Y + sT[10] * Z) + sT[11];
                     const float wx = tx * g.fx / tz + g.cx;
                     const float wy = ty * g.fy / tz + g.cy;
                     const Sample3 sm = sample_level<true>(ref_gray, lv, wx, wy);
@@ -572,7 +618,6 @@ __global__ void __launch_bounds__(TRK_THREADS, 2) k_track(const __grid_constant_
                     if (ok) {
                         const float fgx = g.fx * sm.gx, fgy = g.fy * sm.gy; // optimize.cpp:67-77
                         const float xz = X / Z, yz = Y / Z;
-                        float J[6];
                         J[0] = fgx / Z;
                         J[1] = fgy / Z;
                         J[2] = -(fgx * X + fgy * Y) / Z / Z;
@@ -582,38 +627,47 @@ __global__ void __launch_bounds__(TRK_THREADS, 2) k_track(const __grid_constant_
                         const float r = sm.I - I1;
                         const float sg0 = level_value(lv, dsr.y);
                         const float sg = (sg0 < c.sigma_lo) ? c.sigma_lo : (c.sigma_hi < sg0) ? c.sigma_hi : sg0; // std::clamp :83
-                        const float bw = r * (step / sg);
-                        double Jd[6];
-#pragma unroll
-                        for (int q = 0; q < 6; q++) Jd[q] = (double)J[q];
-                        int idx = 0;
-#pragma unroll
-                        for (int p = 0; p < 6; p++)
-#pragma unroll
-                            for (int q = p; q < 6; q++) { acc[idx] = fma(Jd[p], Jd[q], acc[idx]); idx++; }
-                        const double bd = (double)bw;
-#pragma unroll
-                        for (int q = 0; q < 6; q++) acc[21 + q] = fma(Jd[q], bd, acc[21 + q]);
-                        acc[27] += (double)(r * r);
-                        acc[28] += 1.0;
+                        bw = r * (step / sg);
+                        accR += (double)(r * r);
+                        nvalid++;
                     }
                 }
                 if (a.mask && ok) a.mask[(size_t)s * g.n + (size_t)y * g.w + x] = 1;
-                x += sx; y += sy;
-                if (x > rx1) { x -= rw; y++; }
+            }
+            const unsigned vm = __ballot_sync(0xffffffffu, ok);
+            if (vm) { // warp-uniform
+                double2* rw2 = reinterpret_cast<double2*>(rows[lane]);
+                if (ok) {
+                    rw2[0] = make_double2((double)J[0], (double)J[1]);
+                    rw2[1] = make_double2((double)J[2], (double)J[3]);
+                    rw2[2] = make_double2((double)J[4], (double)J[5]);
+                    rw2[3] = make_double2((double)bw, 0.0);
+                } else {
+                    rw2[0] = rw2[1] = rw2[2] = rw2[3] = make_double2(0.0, 0.0);
+                }
+                __syncwarp();
+                const double* pa = &rows[0][pair_p];
+                const double* pb = &rows[0][pair_q];
+#pragma unroll
+                for (int i = 0; i < 32; i++) accL = fma(pa[i * 10], pb[i * 10], accL);
+                __syncwarp();
             }
         }
 
         // ---- reduction in a fixed order (deterministic for a given B) ----
-        const int lane = tid & 31, warp = tid >> 5;
+        {
+            double vr = accR;
+            int vn = nvalid;
 #pragma unroll
-        for (int k = 0; k < NACC; k++) {
-            double v = acc[k];
-#pragma unroll
-            for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
-            if (lane == 0) sred[warp][k] = v;
+            for (int off = 16; off > 0; off >>= 1) {
+                vr += __shfl_down_sync(0xffffffffu, vr, off);
+                vn += __shfl_down_sync(0xffffffffu, vn, off);
+            }
+            if (lane < 27) sred[warp][lane] = accL;
+            if (lane == 0) { sred[warp][27] = vr; sred[warp][28] = (double)vn; }
         }
         __syncthreads();
+        TRK_PROF(0, tp);
         if (tid < NACC) {
             double v = 0;
 #pragma unroll
@@ -642,6 +696,7 @@ __global__ void __launch_bounds__(TRK_THREADS, 2) k_track(const __grid_constant_
             }
         }
         __syncthreads();
+        TRK_PROF(1, tp);
         if (leader) {
             if (tid == 0) {
                 gn_tail(c, a, st, s, stot, &ctl);
@@ -658,7 +713,15 @@ __global__ void __launch_bounds__(TRK_THREADS, 2) k_track(const __grid_constant_
             for (int q = 0; q < 12; q++) ctl.T[q] = __ldcg(&st->Tn[q]);
         }
         __syncthreads();
+        TRK_PROF(2, tp);
+#ifdef DVO_TRK_PROF
+        if (s == 0 && b == 0 && tid == 0) g_trk_prof[3]++;
+#endif
     }
+#ifdef DVO_TRK_PROF
+    if (s == 0 && b == 0 && tid == 0) g_trk_prof[4] += gtimer() - tp_start;
+    if (b == 0 && tid == 0 && s < 1024) g_trk_stream_ns[s] = (unsigned int)(gtimer() - tp_start);
+#endif
 
     // ---- VO epilogue (leader CTA of each stream) ----
     if (a.vo && leader) {

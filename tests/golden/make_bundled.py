@@ -151,6 +151,17 @@ def main():
     xi, logs = ref.track(cur, pre)                                           # Tracker::track(obj = cur, ref = pre)
     meta, res, upd = logs_to_arrays(logs)
     out.update(c1_xi=xi, c1_log_meta=meta, c1_log_residual=res, c1_log_update=upd)
+    # pose BEFORE every logged iteration (tracker.cpp:46-51: xi <- concatenate(xi, update) unless NaN), with the reference's
+    # own se3::concatenate: the reference's tracker DIVERGES on this pair (first update 1.4 m; README.md:4 says as much), so the
+    # CUDA path is compared iteration by iteration from these poses, not by a free run of a chaotic sequence
+    x = np.zeros(6, np.float32); before = []
+    for L in logs:
+        before.append(x.copy())
+        nx = ref.se3_concatenate(x, L["update"])
+        if not np.isnan(nx).any():
+            x = nx
+    assert np.array_equal(x, xi)
+    out.update(c1_log_xi_before=np.stack(before).astype(np.float32))
     for lv in range(4):                                                      # first iteration of every level from xi = 0
         u, r, v = ref.optimize(cur.image(lv, "gray"), pre.image(lv, "gray"), pre.image(lv, "depth"), pre.image(lv, "sigma"), pre.K(lv),
                                np.zeros(6, np.float32), lv)
