@@ -289,7 +289,10 @@ def run_gpu_arm(args, rank, world, local_rank, dist):
                       max_keyframes=n_total + W_ + E + 4)
     dv.vo_reserve(n_total + W_ + E + 2)
     frame_bytes = S * H_IN * W_IN * 4
-    h2d_bytes = S * (H_IN >> CULLS) * W_IN * 4 if (CULLS > 0 and H_IN % (1 << CULLS) == 0) else frame_bytes  # stage_gray_to()
+    e2e_u8 = (args.e2e_input == "gray8")
+    esz = 1 if e2e_u8 else 4   # bytes per pixel of the end-to-end pass's host frames
+    host_frame_bytes = S * H_IN * W_IN * esz
+    h2d_bytes = S * (H_IN >> CULLS) * W_IN * esz if (CULLS > 0 and H_IN % (1 << CULLS) == 0) else host_frame_bytes  # stage_gray_to()
     # global sequence ids are sharded id mod world (dvo_b200/shard.py); a rank's S local streams are ids
     # rank, rank + world, ... and the renderer seeds stream k of this context with seed0 + k: the bench uses the
     # contiguous relabelling 1000 + rank * S + k (any bijection of independent sequences gives the same workload)
@@ -307,14 +310,22 @@ def run_gpu_arm(args, rank, world, local_rank, dist):
     last = jl if jl < n_dev_frames else period - jl
     e2e_first = last + 1
     tmpd = dv.dev_alloc(frame_bytes)
+    ftmp = np.empty((S, H_IN, W_IN), np.float32) if e2e_u8 else None
     for i in range(W_ + E):
-        hp = lib.dvo_host_alloc(frame_bytes)
+        hp = lib.dvo_host_alloc(host_frame_bytes)
         if not hp:
             raise SystemExit("bench.py: pinned host allocation failed")
-        arr = np.ctypeslib.as_array(C.cast(hp, C.POINTER(C.c_float)), shape=(S, H_IN, W_IN))
         dv.synth_render_dev(tmpd, None, e2e_first + i, seed0, TRANS_STEP, ROT_STEP_DEG)
-        dv.copy_to_host(arr, tmpd)
+        if e2e_u8:   # 8-bit camera frames: the rendered intensity quantised to 0..255 (what cv::imread + cvtColor deliver)
+            arr = np.ctypeslib.as_array(C.cast(hp, C.POINTER(C.c_uint8)), shape=(S, H_IN, W_IN))
+            dv.copy_to_host(ftmp, tmpd)
+            np.multiply(ftmp, 255.0, out=ftmp); np.rint(ftmp, out=ftmp); np.clip(ftmp, 0, 255, out=ftmp)
+            arr[...] = ftmp
+        else:
+            arr = np.ctypeslib.as_array(C.cast(hp, C.POINTER(C.c_float)), shape=(S, H_IN, W_IN))
+            dv.copy_to_host(arr, tmpd)
         host.append((hp, arr))
+    del ftmp
     dv.dev_free(tmpd)
     d0, s0 = depth_prior(S, seed=4321 + rank)
     dv.sync()
@@ -388,14 +399,22 @@ def run_gpu_arm(args, rank, world, local_rank, dist):
     tps = [lib.dvo_host_alloc(S * 64) for _ in range(2)]
     Ts = [np.ctypeslib.as_array(C.cast(tp, C.POINTER(C.c_float)), shape=(S, 4, 4)) for tp in tps]
     pose_sum = 0.0
+    def submit(i):
+        if e2e_u8:
+            dv._ck(lib.dvo_vo_submit_gray8(dv.ctx, host[i][0], -1, tps[i & 1]))
+        else:
+            dv._ck(lib.dvo_vo_submit(dv.ctx, host[i][0], tps[i & 1]))
+
+    dv.kernel_timing(True)   # the warm-up steps double as a device-time probe of THIS part of the sequence
     for i in range(W_):
-        dv._ck(lib.dvo_vo_submit(dv.ctx, host[i][0], tps[i & 1]))
+        submit(i)
         dv._ck(lib.dvo_vo_collect(dv.ctx))
+    e2e_kernel_ms = sum(v[0] for v in dv.kernel_timing(False).values()) / max(W_, 1)
     barrier()
     t0 = time.perf_counter()
     pending = []
     for i in range(W_, W_ + E):
-        dv._ck(lib.dvo_vo_submit(dv.ctx, host[i][0], tps[i & 1]))
+        submit(i)
         pending.append(i & 1)
         if len(pending) == 2:
             dv._ck(lib.dvo_vo_collect(dv.ctx))
@@ -426,8 +445,14 @@ def run_gpu_arm(args, rank, world, local_rank, dist):
     res = dict(
         value=world * S * K_ / (ms * 1e-3), ms_per_step=ms / K_,
         e2e=dict(value=world * S * E / e2e_s, unit="frames/s", h2d_bytes_per_step=h2d_bytes, d2h_bytes_per_step=S * 64, steps=E,
-                 note="host frames are full 640x480 float32 (%d B/step); Convert::cullImage(gray, 2) samples every 4th row, so only those "
-                      "rows cross PCIe (cudaMemcpy2DAsync); 2 frames in flight (dvo_vo_submit/dvo_vo_collect)" % frame_bytes),
+                 host_input=args.e2e_input, ms_per_step=1e3 * e2e_s / E, kernel_ms_per_step_same_frames=e2e_kernel_ms,
+                 note="host frames are full 640x480 %s in pinned memory (%d B/step)%s; Convert::cullImage(gray, 2) samples every 4th row, "
+                      "so only those rows cross PCIe (cudaMemcpy2DAsync); 2 frames in flight (%s/dvo_vo_collect); these are frames %d.. of the "
+                      "sequences, where the epipolar searches are longer than over the first %d frames `value` averages "
+                      "(kernel_ms_per_step_same_frames = device time of the same part of the sequence)"
+                      % ("8-bit gray" if e2e_u8 else "float32", host_frame_bytes,
+                         ", converted on the device like Loader's convertTo(CV_32FC1, 1.0/255.0) (loader.cpp:61)" if e2e_u8 else "",
+                         "dvo_vo_submit_gray8" if e2e_u8 else "dvo_vo_submit", e2e_first + W_, n_total)),
         gpu_launches=int(l1 - l0), clocks=clocks,
         roofline=dict(kernel=top["kernel"], bound="hbm", achieved=top["achieved_gbs"], peak=peak, unit="GB/s", frac=top["frac"],
                       traffic=None, peak_source=peak_src, launches=top["launches"], avg_launch_us=top["avg_launch_us"],
@@ -447,6 +472,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--streams", type=int, default=256, help="independent sequences per GPU")
     ap.add_argument("--e2e-steps", type=int, default=12)
+    ap.add_argument("--e2e-input", default="gray8", choices=["gray8", "float32"],
+                    help="host frames of the end-to-end pass: 8-bit gray (camera / cv::imread form, converted on the device) or float32")
     ap.add_argument("--roofline-steps", type=int, default=4)
     ap.add_argument("--resident-frames", type=int, default=48, help="distinct frames per stream kept in HBM")
     ap.add_argument("--cpu-frames-per-step", type=int, default=1)

@@ -4,7 +4,9 @@
 #include "dvo_kernels.cuh"
 #include "dvo_synth.cuh"
 
+#include <algorithm>
 #include <cmath>
+#include <cstdint>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -383,31 +385,37 @@ struct KTimer { // records an event pair around one launch when timing is on
 
 // slot >= 0: that slot for every stream; slot < 0: each stream's current VO slot.
 // rows_only: gray_dev holds only the input rows that Convert::cullImage samples (host staging path).
-static int build_frame(dvo_ctx* ctx, int slot, const float* gray_dev, bool rows_only)
+static int build_frame(dvo_ctx* ctx, int slot, const float* gray_dev, bool rows_only, bool gray8 = false, int invalid_code = -1)
 {
     const Consts& c = ctx->c;
     const VoState* vo = slot < 0 ? ctx->d_vo : nullptr;
     const LevelGeom& gt = c.lv[c.L - 1];
     dim3 grid(cdiv(gt.n, 1024), c.S);
     KTimer t(ctx, K_CULL);
-    k_cull_gray<<<grid, 256, 0, ctx->stream>>>(c, gray_dev, rows_only ? gt.h : c.in_h, rows_only ? 0 : c.culls, ctx->d_slots, slot, vo);
+    if (gray8)
+        k_cull_gray8<<<grid, 256, 0, ctx->stream>>>(c, (const uint8_t*)gray_dev, rows_only ? gt.h : c.in_h, rows_only ? 0 : c.culls,
+                                                    invalid_code, ctx->d_slots, slot, vo);
+    else
+        k_cull_gray<<<grid, 256, 0, ctx->stream>>>(c, gray_dev, rows_only ? gt.h : c.in_h, rows_only ? 0 : c.culls, ctx->d_slots, slot, vo);
     KCHECK();
     return DVO_OK;
 }
 
 // Host frame -> device staging.  Convert::cullImage only samples rows that are multiples of 2^culls,
 // so when the geometry allows one uniform pitch only those rows cross PCIe (1/2^culls of the bytes).
-static int stage_gray_to(dvo_ctx* ctx, float* dst, cudaStream_t st, const float* gray, bool* rows_only)
+static int stage_gray_to(dvo_ctx* ctx, float* dst, cudaStream_t st, const void* gray, bool* rows_only, size_t elem = sizeof(float))
 {
     const Consts& c = ctx->c;
     const int step = 1 << c.culls;
     const LevelGeom& gt = c.lv[c.L - 1];
     if (c.culls > 0 && c.in_h % step == 0 && gt.h == c.in_h / step) {
-        CK(cudaMemcpy2DAsync(dst, sizeof(float) * (size_t)c.in_w, gray, sizeof(float) * (size_t)c.in_w * step,
-                             sizeof(float) * (size_t)c.in_w, (size_t)c.S * gt.h, cudaMemcpyHostToDevice, st));
+        const size_t row_bytes = elem * (size_t)c.in_w;
+        // one strided copy for all streams: the copy engine keeps the link full even on 640-byte rows (53.6 GB/s measured,
+        // scripts/micro/h2d_rows.cu; one call per image drops to 15 GB/s, zero-copy reads by the SMs to 13 GB/s)
+        CK(cudaMemcpy2DAsync(dst, row_bytes, gray, row_bytes * step, row_bytes, (size_t)c.S * gt.h, cudaMemcpyHostToDevice, st));
         *rows_only = true;
     } else {
-        CK(cudaMemcpyAsync(dst, gray, sizeof(float) * (size_t)c.S * c.in_w * c.in_h, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(dst, gray, elem * (size_t)c.S * c.in_w * c.in_h, cudaMemcpyHostToDevice, st));
         *rows_only = false;
     }
     return DVO_OK;
@@ -431,6 +439,17 @@ extern "C" int dvo_frame_create(dvo_ctx* ctx, int* slot, const float* gray)
     rc = find_free_slot(ctx, slot);
     if (rc) return rc;
     return build_frame(ctx, *slot, ctx->d_stage_in, rows_only);
+}
+
+extern "C" int dvo_frame_create_gray8(dvo_ctx* ctx, int* slot, const uint8_t* gray8, int invalid_code)
+{
+    ARG(slot && gray8 && invalid_code >= -1 && invalid_code <= 255, "bad argument");
+    bool rows_only = false;
+    int rc = stage_gray_to(ctx, ctx->d_stage_in, ctx->stream, gray8, &rows_only, 1);
+    if (rc) return rc;
+    rc = find_free_slot(ctx, slot);
+    if (rc) return rc;
+    return build_frame(ctx, *slot, ctx->d_stage_in, rows_only, true, invalid_code);
 }
 
 extern "C" int dvo_frame_release(dvo_ctx* ctx, int slot)
@@ -975,7 +994,7 @@ extern "C" int dvo_vo_force_pose(dvo_ctx* ctx, const float* rel_xi)
 // One odometrize for every stream, enqueued on the context's stream.  after_cull (nullable) is recorded
 // once the staging buffer has been consumed; sync_out = false leaves the pose read-back asynchronous.
 static int vo_push_impl(dvo_ctx* ctx, const float* gray_dev, const float* init_depth, const float* init_sigma, float* T_out,
-                        cudaEvent_t after_cull, bool sync_out)
+                        cudaEvent_t after_cull, bool sync_out, bool gray8 = false, int invalid_code = -1)
 {
     const Consts& c = ctx->c;
     ARG(gray_dev, "null gray");
@@ -994,7 +1013,7 @@ static int vo_push_impl(dvo_ctx* ctx, const float* gray_dev, const float* init_d
             sh.in_use = true;
         }
     }
-    int rc = build_frame(ctx, -1, gray_dev, ctx->rows_only_staged); // make_shared<Frame>(gray, K, 3, 2), system.hpp:47
+    int rc = build_frame(ctx, -1, gray_dev, ctx->rows_only_staged, gray8, invalid_code); // make_shared<Frame>(gray, K, 3, 2), system.hpp:47
     ctx->rows_only_staged = false;
     if (rc) return rc;
     if (after_cull) CK(cudaEventRecord(after_cull, ctx->stream));
@@ -1041,13 +1060,29 @@ extern "C" int dvo_vo_push(dvo_ctx* ctx, const float* gray, const float* init_de
     return vo_push_impl(ctx, ctx->d_stage_in, init_depth, init_sigma, T_out, ctx->copy_stream ? ctx->ev_consumed[0] : nullptr, true);
 }
 
+extern "C" int dvo_vo_push_gray8(dvo_ctx* ctx, const uint8_t* gray8, int invalid_code, const float* init_depth, const float* init_sigma,
+                                 float* T_out)
+{
+    ARG(gray8 && invalid_code >= -1 && invalid_code <= 255, "bad argument");
+    bool rows_only = false;
+    int rc = stage_gray_to(ctx, ctx->d_stage_in, ctx->stream, gray8, &rows_only, 1);
+    if (rc) return rc;
+    ctx->rows_only_staged = rows_only;
+    return vo_push_impl(ctx, ctx->d_stage_in, init_depth, init_sigma, T_out, ctx->copy_stream ? ctx->ev_consumed[0] : nullptr, true, true,
+                        invalid_code);
+}
+
 // Pipelined submission: two staging buffers filled on a copy stream, so frame n+1 crosses PCIe while
 // frame n's kernels run.
 static int pipe_init(dvo_ctx* ctx)
 {
     if (ctx->copy_stream) return DVO_OK;
     const Consts& c = ctx->c;
-    CK(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    {   // highest priority: the staging kernel's few CTAs must not queue behind the previous frame's 50 000-CTA grids
+        int lo = 0, hi = 0;
+        CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        CK(cudaStreamCreateWithPriority(&ctx->copy_stream, cudaStreamNonBlocking, hi));
+    }
     ctx->d_stage_pp[0] = ctx->d_stage_in;
     CK(cudaMalloc(&ctx->d_stage_pp[1], sizeof(float) * (size_t)c.S * c.in_w * c.in_h));
     for (int k = 0; k < 2; k++) {
@@ -1058,7 +1093,7 @@ static int pipe_init(dvo_ctx* ctx)
     return DVO_OK;
 }
 
-extern "C" int dvo_vo_submit(dvo_ctx* ctx, const float* gray, float* T_out)
+static int vo_submit_impl(dvo_ctx* ctx, const void* gray, float* T_out, bool gray8, int invalid_code)
 {
     ARG(gray, "null gray");
     if (ctx->pp_in_flight >= 2) {
@@ -1072,17 +1107,24 @@ extern "C" int dvo_vo_submit(dvo_ctx* ctx, const float* gray, float* T_out)
     // filled by a plain dvo_vo_push on the compute stream before
     CK(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_consumed[k], 0));
     bool rows_only = false;
-    rc = stage_gray_to(ctx, ctx->d_stage_pp[k], ctx->copy_stream, gray, &rows_only);
+    rc = stage_gray_to(ctx, ctx->d_stage_pp[k], ctx->copy_stream, gray, &rows_only, gray8 ? 1 : sizeof(float));
     if (rc) return rc;
     CK(cudaEventRecord(ctx->ev_copied[k], ctx->copy_stream));
     CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_copied[k], 0));
     ctx->rows_only_staged = rows_only;
-    rc = vo_push_impl(ctx, ctx->d_stage_pp[k], nullptr, nullptr, T_out, ctx->ev_consumed[k], false);
+    rc = vo_push_impl(ctx, ctx->d_stage_pp[k], nullptr, nullptr, T_out, ctx->ev_consumed[k], false, gray8, invalid_code);
     if (rc) return rc;
     CK(cudaEventRecord(ctx->ev_done[k], ctx->stream));
     ctx->pp_head++;
     ctx->pp_in_flight++;
     return DVO_OK;
+}
+
+extern "C" int dvo_vo_submit(dvo_ctx* ctx, const float* gray, float* T_out) { return vo_submit_impl(ctx, gray, T_out, false, -1); }
+extern "C" int dvo_vo_submit_gray8(dvo_ctx* ctx, const uint8_t* gray8, int invalid_code, float* T_out)
+{
+    ARG(invalid_code >= -1 && invalid_code <= 255, "bad invalid_code");
+    return vo_submit_impl(ctx, gray8, T_out, true, invalid_code);
 }
 
 extern "C" int dvo_vo_collect(dvo_ctx* ctx)

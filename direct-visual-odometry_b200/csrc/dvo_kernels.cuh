@@ -53,6 +53,37 @@ __global__ void __launch_bounds__(256) k_cull_gray(const __grid_constant__ Const
     }
 }
 
+// The same from 8-bit gray: Loader::getNormalizedImages' convertTo(CV_32FC1, 1.0/255.0) (loader.cpp:61; OpenCV's cvt_32f for
+// 8-bit input: one fp32 multiply by (float)(1.0/255.0)) fused with Convert::cullImage.  A warp reads 32 bytes spread over
+// 32 << culls contiguous bytes of one input row.
+__global__ void __launch_bounds__(256) k_cull_gray8(const __grid_constant__ Consts c, const uint8_t* __restrict__ in, int in_rows,
+                                                    int row_shift, int invalid_code, const SlotDev* __restrict__ slots, int fixed,
+                                                    const VoState* __restrict__ vo)
+{
+    const int s = blockIdx.y;
+    const SlotDev& slot = slots[vo ? vo_cur_slot(c, vo[s].n_kf) : fixed];
+    const LevelGeom g = c.lv[c.L - 1];
+    const uint8_t* __restrict__ src = in + (size_t)s * c.in_w * in_rows;
+    float* __restrict__ dst = slot.gray + (size_t)s * g.n;
+    const int sh = c.culls;
+    const int base = blockIdx.x * 1024 + threadIdx.x;
+    int v[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int i = base + k * 256;
+        v[k] = 0;
+        if (i < g.n) {
+            const int y = i / g.w, x = i - y * g.w;
+            v[k] = __ldcs(src + (size_t)(y << row_shift) * c.in_w + (x << sh));
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int i = base + k * 256;
+        if (i < g.n) dst[i] = (v[k] == invalid_code) ? DVO_INV : __fmul_rn((float)v[k], (float)(1.0 / 255.0));
+    }
+}
+
 // depth / sigma / age upload (Frame 6-arg ctor frame.hpp:91-106, updateDepthSigmaAge frame.cpp:47-54).
 // src arrays are [S][sh][sw]; shift = culls when full-res, 0 otherwise.  grid = (ceil(n_top/256), S)
 __global__ void __launch_bounds__(256) k_set_top(const __grid_constant__ Consts c, const SlotDev* __restrict__ slots, int fixed,

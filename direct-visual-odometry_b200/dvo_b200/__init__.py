@@ -47,6 +47,7 @@ EXPORTS = [
     "dvo_vo_last_slot", "dvo_vo_last_log", "dvo_vo_counters", "dvo_vo_error", "dvo_synth_render_dev", "dvo_dev_alloc", "dvo_dev_free",
     "dvo_copy_to_host", "dvo_copy_to_dev", "dvo_timer_start", "dvo_timer_stop", "dvo_launch_count", "dvo_gn_timing", "dvo_kernel_timing",
     "dvo_map_update_points", "dvo_se3_exp", "dvo_se3_log", "dvo_se3_concatenate", "dvo_vo_submit", "dvo_vo_collect",
+    "dvo_frame_create_gray8", "dvo_vo_push_gray8", "dvo_vo_submit_gray8",
 ]
 
 
@@ -117,6 +118,9 @@ def load_library(path=None):
     lib.dvo_se3_concatenate.argtypes = [C.c_void_p, F32P, F32P, F32P, C.c_int]
     lib.dvo_vo_submit.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     lib.dvo_vo_collect.argtypes = [C.c_void_p]
+    lib.dvo_frame_create_gray8.argtypes = [C.c_void_p, I32P, C.c_void_p, C.c_int]
+    lib.dvo_vo_push_gray8.argtypes = [C.c_void_p, C.c_void_p, C.c_int, F32P, F32P, F32P]
+    lib.dvo_vo_submit_gray8.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
     return lib
 
 
@@ -198,6 +202,21 @@ class Dvo:
         g = self._stack(gray, self.params.height, self.params.width)
         slot = C.c_int(-1)
         self._ck(self.lib.dvo_frame_create(self.ctx, C.byref(slot), g.ctypes.data_as(C.c_void_p)))
+        self._ck(self.lib.dvo_sync(self.ctx))
+        return slot.value
+
+    def _stack8(self, img):
+        a = np.ascontiguousarray(img, dtype=np.uint8)
+        if a.ndim == 2:
+            a = a[None]
+        assert a.shape == (self.S, self.params.height, self.params.width), a.shape
+        return a
+
+    def frame_create_gray8(self, gray8, invalid_code=-1):
+        """Frame from 8-bit gray: convertTo(CV_32FC1, 1.0/255.0) + cullImage on the device (loader.cpp:59-61)."""
+        g = self._stack8(gray8)
+        slot = C.c_int(-1)
+        self._ck(self.lib.dvo_frame_create_gray8(self.ctx, C.byref(slot), g.ctypes.data_as(C.c_void_p), int(invalid_code)))
         self._ck(self.lib.dvo_sync(self.ctx))
         return slot.value
 
@@ -336,6 +355,17 @@ class Dvo:
         self._ck(self.lib.dvo_vo_push(self.ctx, g.ctypes.data_as(C.c_void_p), _p(d), _p(s), _p(T)))
         if not want_pose:
             self._ck(self.lib.dvo_sync(self.ctx))  # g must outlive the async copy
+        return T
+
+    def vo_push_gray8(self, gray8, invalid_code=-1, init_depth=None, init_sigma=None, want_pose=True):
+        g = self._stack8(gray8)
+        w, h = self.level_size(self.L - 1)
+        d = self._stack(init_depth, h, w) if init_depth is not None else None
+        s = self._stack(init_sigma, h, w) if init_sigma is not None else None
+        T = np.empty((self.S, 4, 4), np.float32) if want_pose else None
+        self._ck(self.lib.dvo_vo_push_gray8(self.ctx, g.ctypes.data_as(C.c_void_p), int(invalid_code), _p(d), _p(s), _p(T)))
+        if not want_pose:
+            self._ck(self.lib.dvo_sync(self.ctx))
         return T
 
     def vo_state(self):

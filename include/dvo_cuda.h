@@ -100,6 +100,13 @@ void dvo_host_free(void* p);
  * gradients (Convert::gradiate convert.cpp:41-75) built on device.  gray: [n_streams][height][width]. */
 int dvo_frame_create(dvo_ctx* ctx, int* slot, const float* gray);
 int dvo_frame_create_dev(dvo_ctx* ctx, int* slot, const float* gray_dev);
+/* The same from 8-BIT gray, the form the reference's loader holds right after cv::cvtColor(BGR2GRAY)
+ * (src/core/loader.cpp:59-61,143-144): the device performs convertTo(CV_32FC1, 1.0/255.0) — for 8-bit input
+ * OpenCV multiplies in fp32, (float)code * (float)(1.0/255.0) — and then Convert::cullImage, so a quarter of the
+ * bytes cross PCIe.  gray8: [n_streams][height][width] uint8.  invalid_code (0..255, or -1 for none) marks pixels
+ * that are INVALID (-2.0, include/math/util.hpp:7): the border cv::remap(BORDER_CONSTANT, INVALID) leaves
+ * (loader.cpp:39-40) cannot be expressed in 8 bits otherwise. */
+int dvo_frame_create_gray8(dvo_ctx* ctx, int* slot, const uint8_t* gray8, int invalid_code);
 int dvo_frame_release(dvo_ctx* ctx, int slot);
 /* full_res != 0: arrays are input-sized and culled like the 6-arg Frame ctor (frame.hpp:91-106);
  * full_res == 0: arrays are finest-level sized (Frame::updateDepthSigmaAge, frame.cpp:47-54).
@@ -180,6 +187,12 @@ int dvo_vo_push_dev(dvo_ctx* ctx, const float* gray_dev, const float* init_depth
  * them in submission order.  Results are identical to dvo_vo_push. */
 int dvo_vo_submit(dvo_ctx* ctx, const float* gray, float* T_out);
 int dvo_vo_collect(dvo_ctx* ctx);
+/* dvo_vo_push / dvo_vo_submit from 8-bit gray frames (see dvo_frame_create_gray8): Loader::getNormalizedImages'
+ * convertTo (loader.cpp:61) runs on the device.  Results are bit-identical to feeding the float frames
+ * (float)code * (float)(1.0/255.0) to dvo_vo_push. */
+int dvo_vo_push_gray8(dvo_ctx* ctx, const uint8_t* gray8, int invalid_code, const float* init_depth, const float* init_sigma,
+                      float* T_out);
+int dvo_vo_submit_gray8(dvo_ctx* ctx, const uint8_t* gray8, int invalid_code, float* T_out);
 /* Supply the relative pose (frame-from-keyframe twist, [n_streams][6]) the NEXT dvo_vo_push uses for
  * Frame::updateXi (frame.cpp:7-14) and mapping instead of its own tracking result; the tracker still
  * runs and its iterations stay readable through dvo_vo_last_log.  Used for teacher-forced parity

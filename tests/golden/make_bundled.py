@@ -16,7 +16,7 @@ per-pixel registration restated below):
       VisualOdometry(K).odometrize per frame, K from external/camera-calibration/data/logicool_00/config.yaml.
 Only the pixels Frame(.) samples are stored (cullImage keeps the top-left pixel of every 2^culls block,
 convert.cpp:7-20): C1 at 256x212 (float32, registered gray is bilinear), C2 at 160x120 as int16 (u8 code or -1
-for the INVALID border, gray = code / 255 exactly as convertTo(CV_32FC1, 1.0/255.0))."""
+for the INVALID border, gray = (float)code * (float)(1.0/255.0) exactly as convertTo(CV_32FC1, 1.0/255.0))."""
 import os
 import sys
 
@@ -57,7 +57,9 @@ def read_list(info):
 def normalized_gray(path):
     img = cv2.imread(path, cv2.IMREAD_UNCHANGED)
     gray = cv2.cvtColor(img, cv2.COLOR_BGR2GRAY)          # loader.cpp:60 / :143 (4-channel input uses B, G, R)
-    return gray, (gray.astype(np.float64) * (1.0 / 255.0)).astype(np.float32)  # convertTo(CV_32FC1, 1.0/255.0)
+    # convertTo(CV_32FC1, 1.0/255.0) on 8-bit input multiplies in fp32 by (float)(1.0/255.0) (cvt_32f; checked against cv2 4.13:
+    # the double-precision product differs in the last bit for 126 of the 256 codes)
+    return gray, (gray.astype(np.float32) * np.float32(1.0 / 255.0)).astype(np.float32)
 
 
 def undistort_nearest(img, K, D, size, border):
@@ -113,7 +115,7 @@ def kinect_mapped(ref, cfg, rgb_path, depth_path):
     K2, D2 = f32(cfg["intrinsic2"]), f32(cfg["distortion2"])
     _, g = normalized_gray(rgb_path)
     dimg = cv2.imread(depth_path, cv2.IMREAD_UNCHANGED)
-    d = (dimg.astype(np.float64) * (1.0 / 5000.0)).astype(np.float32)       # loader.cpp:145
+    d = (dimg.astype(np.float32) * np.float32(1.0 / 5000.0)).astype(np.float32)   # loader.cpp:145 (fp32 multiply, as above)
     g_u = undistort_nearest(g, K1, D1, (1920, 1080), -2.0)
     d_u = undistort_nearest(d, K2, D2, (512, 424), 0)
     invT = np.eye(4, dtype=np.float32)
@@ -179,7 +181,7 @@ def main():
         und = undistort_nearest(u8.astype(np.int16), Ku, Du, (640, 480), -1)  # NEAREST picks whole pixels: remap the codes
         codes.append(np.ascontiguousarray(und[::4, ::4]))                     # what Frame(., 3, 2) samples
     codes = np.stack(codes).astype(np.int16)
-    gray = np.where(codes < 0, np.float32(-2.0), (codes.astype(np.float64) * (1.0 / 255.0)).astype(np.float32)).astype(np.float32)
+    gray = np.where(codes < 0, np.float32(-2.0), (codes.astype(np.float32) * np.float32(1.0 / 255.0)).astype(np.float32)).astype(np.float32)
     d0, s0 = synth.random_depth_prior((120, 160), seed=4321)                  # stands in for Scene's cv::randn prior
     ref.rng_reset()
     vo = ref.vo_create(K)

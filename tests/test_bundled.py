@@ -37,7 +37,7 @@ def c1_frames(B):
 
 def c2_gray(B):
     c = B["c2_codes"]
-    g = (c.astype(np.float64) * (1.0 / 255.0)).astype(np.float32)  # convertTo(CV_32FC1, 1.0/255.0), loader.cpp:61
+    g = (c.astype(np.float32) * np.float32(1.0 / 255.0)).astype(np.float32)  # convertTo(CV_32FC1, 1.0/255.0), loader.cpp:61 (fp32 multiply)
     return np.where(c < 0, np.float32(-2.0), g).astype(np.float32)
 
 
