@@ -748,7 +748,11 @@ static int enqueue_update(dvo_ctx* ctx, bool tables)
     }
     {
         KTimer t(ctx, K_MAP_APPLY);
-        k_map_update_apply<<<grid, MAPU_THREADS, 0, ctx->stream>>>(c, ctx->roi, ctx->d_slots, ctx->d_ms, ctx->d_flags, ctx->d_blockcnt, ctx->d_rng);
+        k_map_scan<<<c.S, 256, 0, ctx->stream>>>(c, ctx->roi, ctx->d_ms, ctx->d_blockcnt);
+        KCHECK();
+        dim3 agrid(cdiv(ctx->roi.nblk, APPLY_SUB), c.S);
+        k_map_update_apply<<<agrid, MAPU_THREADS * APPLY_SUB, 0, ctx->stream>>>(c, ctx->roi, ctx->d_slots, ctx->d_ms, ctx->d_flags,
+                                                                                 ctx->d_blockcnt, ctx->d_rng);
         KCHECK();
     }
     return DVO_OK;

@@ -1161,11 +1161,41 @@ __global__ void __launch_bounds__(MAPU_THREADS, DVO_MAPU_MINB) k_map_update(cons
     }
 }
 
+// Between the phases: per stream, the per-CTA reject counts become exclusive offsets (the row-major rank base of phase B) and
+// their total.  grid = S, 256 threads.  (Summing the preceding counts inside every phase-B CTA is quadratic in the CTA count:
+// fine for 196 CTAs at 160x120, hopeless for 129 600 at 3840x2160.)
+__global__ void __launch_bounds__(256) k_map_scan(const __grid_constant__ Consts c, const MapRoi roi, MapState* __restrict__ mst,
+                                                  unsigned int* __restrict__ blockcnt)
+{
+    const int s = blockIdx.x;
+    MapState* m = mst + s;
+    if (!m->do_update) return;
+    __shared__ unsigned int s_sum[256];
+    unsigned int* bc = blockcnt + (size_t)s * roi.nblk;
+    const int per = (roi.nblk + 255) / 256;
+    const int b0 = threadIdx.x * per, b1 = min(roi.nblk, b0 + per);
+    unsigned int sum = 0;
+    for (int b = b0; b < b1; b++) sum += bc[b];
+    s_sum[threadIdx.x] = sum;
+    __syncthreads();
+    unsigned int off = 0;
+    for (int k = 0; k < (int)threadIdx.x; k++) off += s_sum[k];
+    for (int b = b0; b < b1; b++) {
+        const unsigned int v = bc[b];
+        bc[b] = off;
+        off += v;
+    }
+    if (threadIdx.x == 255) m->n_reject = off;
+}
+
 // Mapper::update phase B: replay of the mt19937 stream for the rejected pixels in row-major order.
-// rank = (rejects in preceding blocks) + (rejects before this thread in the block).  grid = (roi.nblk, S)
-__global__ void __launch_bounds__(MAPU_THREADS) k_map_update_apply(const __grid_constant__ Consts c, const MapRoi roi, const SlotDev* __restrict__ slots,
-                                                          MapState* __restrict__ mst, const uint8_t* __restrict__ flags,
-                                                          const unsigned int* __restrict__ blockcnt, const uint32_t* __restrict__ rng_raw)
+// rank = (rejects in the preceding phase-A CTAs, k_map_scan) + (rejects before this thread in its phase-A CTA).
+// One CTA covers APPLY_SUB phase-A CTAs.   grid = (ceil(roi.nblk / APPLY_SUB), S)
+constexpr int APPLY_SUB = 4;
+__global__ void __launch_bounds__(MAPU_THREADS * APPLY_SUB) k_map_update_apply(const __grid_constant__ Consts c, const MapRoi roi,
+                                                          const SlotDev* __restrict__ slots, MapState* __restrict__ mst,
+                                                          const uint8_t* __restrict__ flags, const unsigned int* __restrict__ blockcnt,
+                                                          const uint32_t* __restrict__ rng_raw)
 {
     const int s = blockIdx.y;
     MapState* m = mst + s;
@@ -1177,28 +1207,17 @@ __global__ void __launch_bounds__(MAPU_THREADS) k_map_update_apply(const __grid_
         const int ry = j / roi.w;
         i = (roi.y0 + ry) * g.w + roi.x0 + (j - ry * roi.w);
     }
-    __shared__ unsigned int s_warp[MAPU_THREADS / 32];
-    __shared__ unsigned int s_base;
-    __shared__ unsigned int s_part[MAPU_THREADS / 32];
-    // offset of this block = sum of preceding block counts
-    unsigned int part = 0;
-    for (int b = threadIdx.x; b < (int)blockIdx.x; b += blockDim.x) part += blockcnt[(size_t)s * roi.nblk + b];
-    for (int off = 16; off > 0; off >>= 1) part += __shfl_down_sync(0xffffffffu, part, off);
+    constexpr int WPS = MAPU_THREADS / 32; // warps per phase-A CTA
+    __shared__ unsigned int s_warp[WPS * APPLY_SUB];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (lane == 0) s_part[warp] = part;
     const bool rej = (i >= 0) && (flags[(size_t)s * g.n + i] & 8);
     const unsigned int bal = __ballot_sync(0xffffffffu, rej);
     if (lane == 0) s_warp[warp] = __popc(bal);
     __syncthreads();
-    if (threadIdx.x == 0) {
-        unsigned int t = 0;
-        for (int k = 0; k < MAPU_THREADS / 32; k++) t += s_part[k];
-        s_base = t;
-    }
-    __syncthreads();
     if (rej) {
-        unsigned int rank = s_base + __popc(bal & ((1u << lane) - 1u));
-        for (int k = 0; k < warp; k++) rank += s_warp[k];
+        const int sub = blockIdx.x * APPLY_SUB + warp / WPS; // the phase-A CTA this pixel belonged to
+        unsigned int rank = blockcnt[(size_t)s * roi.nblk + sub] + __popc(bal & ((1u << lane) - 1u));
+        for (int k = (warp / WPS) * WPS; k < warp; k++) rank += s_warp[k];
         const unsigned long long pos = m->rng_pos + rank;
         if (pos >= c.rng_table) {
             atomicCAS(&m->err, 0, (int)DVO_ERR_RNG);
@@ -1214,11 +1233,8 @@ __global__ void __launch_bounds__(MAPU_THREADS) k_map_update_apply(const __grid_
     if (threadIdx.x == 0) {
         __threadfence();
         unsigned int t = atomicAdd(&m->ticket, 1u);
-        if (t == (unsigned)(roi.nblk - 1)) {
-            unsigned int total = 0;
-            for (int b = 0; b < roi.nblk; b++) total += blockcnt[(size_t)s * roi.nblk + b];
-            m->n_reject = total;
-            m->rng_pos += total;
+        if (t == gridDim.x - 1) {
+            m->rng_pos += m->n_reject;
             m->ticket = 0;
         }
     }

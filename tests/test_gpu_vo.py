@@ -22,7 +22,7 @@ UPD_TOL = 1e-5
 FORCED_TOL = 1e-6  # teacher-forced maps: bit-identical, or within 1e-6 relative (north_star allows 1e-4)
 
 
-def _run_pair(orc, g, K, d0, s0, levels=3, culls=2, n_streams=1, forced=True, **params):
+def _run_pair(orc, g, K, d0, s0, levels=3, culls=2, n_streams=1, forced=True, upd_tol=None, **params):
     """Runs oracle and GPU side by side.
 
     forced=True (teacher-forced): every frame the GPU tracker runs freely from the same keyframe
@@ -36,6 +36,7 @@ def _run_pair(orc, g, K, d0, s0, levels=3, culls=2, n_streams=1, forced=True, **
     forced=False: free-running; comparison stops being meaningful after the first flip, so the
     function returns the number of frames that agreed."""
     n, h, w = g.shape
+    upd_tol = UPD_TOL if upd_tol is None else upd_tol
     dv = make_dvo(width=w, height=h, levels=levels, culls=culls, K=K, n_streams=n_streams, max_frames=2,
                   max_keyframes=n + 2, **params)
     vo = orc.vo_create(K, levels, culls, orc.params(**params))
@@ -60,7 +61,7 @@ def _run_pair(orc, g, K, d0, s0, levels=3, culls=2, n_streams=1, forced=True, **
             if forced:
                 assert sched_g == sched_o, "frame %d: GN schedule / valid counts differ" % i
                 for a, b in zip(logs[s], o_log):
-                    assert se3_norm(a["update"], b["update"]) <= UPD_TOL, (i, a, b)
+                    assert se3_norm(a["update"], b["update"]) <= upd_tol, (i, a, b)
                     assert se3_norm(a["xi_after"], b["xi_after"]) <= POSE_TOL
             ok &= sched_g == sched_o and se3_norm(st["rel_xi"][s], o_rel) <= POSE_TOL
             if not ok and not forced:
