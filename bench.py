@@ -272,6 +272,102 @@ def peak_hbm():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def run_other_configs(lib):
+    """The single-stream configurations of BASELINE.json (the metric also names 1080p): device-resident, CUDA events on the
+    library's stream.  Reported beside the headline line, never instead of it.
+      C3  synthetic 1920x1080 sequence, full VO loop: Frame(gray, K, 3, 2) with the reference's ROIs scaled x3, and culls = 0;
+      C4  3840x2160 mapping-only: Mapper::update on dense hypotheses (rel_xi = (-0.1, 0, 0, 0, 0, 0)) + regularize."""
+    import dvo_b200
+    out = []
+    peak, _ = peak_hbm()
+
+    def Kf(w, h):
+        return np.array([[0.82 * w, 0, 0.5 * w - 0.5], [0, 0.82 * w, 0.5 * h - 0.5], [0, 0, 1]], np.float32)
+
+    # ---- C3
+    W, H, n_res, n_frames = 1920, 1080, 40, 500
+    for culls, sc in ((2, 3), (0, 12)):
+        roi = dict(roi_x0=20 * sc, roi_x1=140 * sc, roi_y0=20 * sc, roi_y1=100 * sc,
+                   map_roi_x0=16 * sc, map_roi_x1=144 * sc, map_roi_y0=12 * sc, map_roi_y1=108 * sc)
+        dv = dvo_b200.Dvo(lib=lib, n_streams=1, width=W, height=H, levels=3, culls=culls, K=Kf(W, H), max_frames=2,
+                          max_keyframes=n_frames + 8, rng_table=1 << 24, **roi)
+        dv.vo_reserve(n_frames + 4)
+        fb = W * H * 4
+        dev = dv.dev_alloc(fb * n_res); dd = dv.dev_alloc(fb)
+        for i in range(n_res):
+            dv.synth_render_dev(dev + i * fb, dd if i == 0 else None, i, 1234, 0.002, 0.07)
+        d0 = np.empty((1, H, W), np.float32)
+        dv.copy_to_host(d0, dd)
+        d0 = np.ascontiguousarray(d0[0, ::1 << culls, ::1 << culls])
+
+        def fptr(i):
+            per = 2 * (n_res - 1)
+            j = i % per
+            return dev + (j if j < n_res else per - j) * fb
+
+        dv.vo_push_dev(dev, d0, np.full_like(d0, 0.1))
+        for f in range(1, 4):
+            dv.vo_push_dev(fptr(f))
+        c0 = dv.vo_counters()
+        dv.timer_start()
+        for f in range(4, 4 + n_frames):
+            dv.vo_push_dev(fptr(f))
+        ms = dv.timer_stop()
+        c1 = dv.vo_counters()
+        err = dv.vo_error()
+        it = int((c1["gn_iters"] - c0["gn_iters"]).sum())
+        out.append(dict(workload="C3: synthetic 1920x1080, %d frames, 1 stream, Frame(gray,K,3,%d) -> %dx%d finest level, full VO loop"
+                                 % (n_frames, culls, W >> culls, H >> culls),
+                        value=n_frames / (ms * 1e-3), unit="frames/s", ms_per_frame=ms / n_frames, gn_iters_per_s=it / (ms * 1e-3),
+                        gn_iters_per_frame=it / float(n_frames), frames_update=int((c1["n_update"] - c0["n_update"]).sum()),
+                        frames_propagate=int((c1["n_propagate"] - c0["n_propagate"]).sum()), device_error=int(err)))
+        dv.dev_free(dev); dv.dev_free(dd)
+        dv.close()
+    # ---- C4
+    W, H = 3840, 2160
+    roi = dict(map_roi_x0=0, map_roi_x1=W - 1, map_roi_y0=0, map_roi_y1=H - 1)
+    dv = dvo_b200.Dvo(lib=lib, n_streams=1, width=W, height=H, levels=1, culls=0, K=Kf(W, H), max_frames=3, rng_table=1 << 24, **roi)
+    fb = W * H * 4
+    gd = dv.dev_alloc(fb)
+    g = np.empty((2, 1, H, W), np.float32)
+    for i in range(2):   # two views of the C3 scene (frames 0 and 12 of its trajectory)
+        dv.synth_render_dev(gd, None, 12 * i, 1234, 0.002, 0.07)
+        dv.copy_to_host(g[i], gd)
+    dv.dev_free(gd)
+    rng = np.random.default_rng(4321)
+    depth = np.maximum(rng.normal(1.5, 0.5, (H, W)), 0.5).astype(np.float32)
+    sigma = np.full((H, W), 0.5, np.float32); age = np.zeros((H, W), np.float32)
+    ref = dv.frame_create(g[0][0]); obj = dv.frame_create(g[1][0])
+    rel = np.array([-0.1, 0, 0, 0, 0, 0], np.float32); zero = np.zeros(6, np.float32)
+    dv.frame_set_xi(ref, zero, zero); dv.frame_set_xi(obj, rel, rel)
+    reps = 5
+    tot = {}
+    for r in range(reps + 1):
+        dv.frame_set_depth(ref, depth, sigma, age)
+        if r:
+            dv.kernel_timing(True)
+        vu, _ = dv.map_update(obj, ref, [ref], want_mask=False)
+        dv.map_regularize(ref)
+        if r:
+            for k, (ms, n) in dv.kernel_timing(False).items():
+                a = tot.setdefault(k, [0.0, 0]); a[0] += ms; a[1] += n
+    dv.close()
+    n = W * H
+    algb = {"k_map_update": 40 * n, "k_map_update_apply": n, "k_regularize": 12 * n, "k_regularize_commit": 8 * n}
+    ks = []
+    for k, (ms, cnt) in sorted(tot.items(), key=lambda kv: -kv[1][0]):
+        if cnt and k in algb:
+            us = 1e3 * ms / cnt
+            ks.append(dict(kernel=k, avg_launch_us=us, algorithmic_bytes_per_launch=algb[k], achieved_gbs=algb[k] / us / 1e3,
+                           frac=algb[k] / us / 1e3 / peak))
+    upd_ms = sum(v[0] for v in tot.values()) / reps
+    out.append(dict(workload="C4: mapping-only 3840x2160, dense hypotheses (depth = max(N(1.5, 0.5), 0.5), sigma = 0.5), ROI = frame, "
+                             "Mapper::update + regularize, %d repetitions" % reps,
+                    value=1e3 / upd_ms, unit="frames/s", ms_per_frame=upd_ms, pixels_per_s=n / (upd_ms * 1e-3), valid_updates=int(vu[0]),
+                    kernels=ks))
+    return out
+
+
 def run_gpu_arm(args, rank, world, local_rank, dist):
     import dvo_b200
     lib = dvo_b200.load_library()
@@ -480,6 +576,7 @@ def main():
     ap.add_argument("--cpu-kind", default="reference", choices=["reference", "port"],
                     help="CPU arm: the reference's own sources (oracle/_ref) or the C restatement (oracle/dvo_oracle.c)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-other-configs", action="store_true", help="skip the single-stream 1080p / 4K configurations (N = 1 only)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else max(args.warmup, 1)
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -517,11 +614,16 @@ def main():
         if info["kind"] == "reference":   # the restatement beside it: what the same algorithm costs without per-pixel se3::exp
             fps2, _, info2 = run_cpu_arm(steps=12, warmup=1, frames_per_step=4, kind="port")
             cpu["port_value"] = fps2; cpu["port_sample"] = info2["sample"]
+    other = None
+    if rank == 0 and world == 1 and not args.no_other_configs:
+        import dvo_b200
+        other = run_other_configs(dvo_b200.load_library())
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
     if rank == 0:
         line = dict(base, impl="b200", **res)
+        line["other_configs"] = other
         line["cpu_baseline"] = cpu
         print(json.dumps(line), flush=True)
 

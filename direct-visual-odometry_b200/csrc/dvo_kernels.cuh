@@ -930,20 +930,29 @@ __device__ __forceinline__ void warp_search(SearchSmem& sm, bool active, const f
             float ptx = cpt.x, pty = cpt.y;
             const float dx = sm.dirx[p], dy = sm.diry[p], ogp = sm.og[p];
             const float* __restrict__ img = sm.born[p];
-            // the reference's loop body (implement.cpp:121-140) for steps b0+1 .. b0+cnt: the tap pt + dir is, bit for
-            // bit, the next step's centre tap and is carried over instead of re-sampled
-            float carry = 0.f;
+            // the reference's loop body (implement.cpp:121-140) for steps b0+1 .. b0+cnt.  It samples pt - dir, pt, pt + dir at
+            // every step ("TODO: 1/N" in the reference).  pt + dir is, bit for bit, the next step's pt (pt += dir), so the centre
+            // tap is the previous step's third tap; and pt - dir rounds back to the previous pt unless the forward addition hit a
+            // rounding tie or crossed a binade (fl(fl(p + d) - d) == p when the rounding error of p + d is below half an ulp of p),
+            // which is CHECKED per step: equal coordinates -> the tap of two steps ago is reused, otherwise it is sampled.  One new
+            // tap per step instead of three, results bit-identical.
+            float prevx = ptx, prevy = pty;                    // pt of the previous step (the checkpoint itself for k = 1)
+            float c_prev = subpixel_dense(img, w, h, ptx, pty); // tap at prev
+            ptx += dx;
+            pty += dy;
+            float c_cur = subpixel_dense(img, w, h, ptx + dx * 0.0f, pty + dy * 0.0f); // tap at pt (k = 1)
             unsigned long long kbest = ~0ull;
 #pragma unroll(SEARCH_UNROLL)
             for (int k = 1; k <= cnt; k++) {
+                const float s2 = subpixel_dense(img, w, h, ptx + dx * 1.0f, pty + dy * 1.0f);
+                const float bx = ptx + dx * -1.0f, by = pty + dy * -1.0f;
+                const float s0 = (bx == prevx && by == prevy) ? c_prev : subpixel_dense(img, w, h, bx, by);
+                const unsigned long long key = ((unsigned long long)__float_as_uint(search_ssd(s0, c_cur, s2, ogp)) << 32) | (unsigned)(b0 + k);
+                if (key < kbest) kbest = key;
+                c_prev = c_cur; c_cur = s2;
+                prevx = ptx; prevy = pty;
                 ptx += dx;
                 pty += dy;
-                const float s0 = subpixel_dense(img, w, h, ptx + dx * -1.0f, pty + dy * -1.0f);
-                const float s1 = (k > 1) ? carry : subpixel_dense(img, w, h, ptx + dx * 0.0f, pty + dy * 0.0f);
-                const float s2 = subpixel_dense(img, w, h, ptx + dx * 1.0f, pty + dy * 1.0f);
-                carry = s2;
-                const unsigned long long key = ((unsigned long long)__float_as_uint(search_ssd(s0, s1, s2, ogp)) << 32) | (unsigned)(b0 + k);
-                if (key < kbest) kbest = key;
             }
             // lanes [hp, rend) form this lane's run: smallest ssd of the run, at its earliest step
             const unsigned above = (hp == 31) ? 0u : (heads >> (hp + 1)) << (hp + 1);
