@@ -105,6 +105,22 @@ __device__ __forceinline__ float subpixel_dense(const float* __restrict__ img, i
     return bilerp(g0, g1, g2, g3, hh, v);
 }
 
+// Branch-free form for the epipolar search loop (bit-identical results).  trunc_x86 + in_range collapse into float compares:
+// for finite p, 0 <= (int)p < w  <=>  -1 < p < w, and NaN / inf / out-of-int-range p fail the compares just as cvttss2si's
+// INT_MIN fails in_range.  The border rule (taps outside the image take the (x0, y0) value) becomes zero offsets plus one select,
+// so the four loads issue back to back without control flow.  wf = (float)w, hf = (float)h (exact: sizes < 2^24).
+__device__ __forceinline__ float subpixel_dense_nb(const float* __restrict__ img, int w, int h, float wf, float hf, float px, float py)
+{
+    if (!(px > -1.0f && px < wf && py > -1.0f && py < hf)) return DVO_INV;
+    const int x0 = __float2int_rz(px), y0 = __float2int_rz(py);
+    const float hh = px - (float)x0, v = py - (float)y0;
+    const float* __restrict__ p = img + (y0 * w + x0);
+    const int ox = (x0 + 1 < w) ? 1 : 0, oy = (y0 + 1 < h) ? w : 0;
+    const float g0 = __ldg(p), g1 = __ldg(p + ox), g2 = __ldg(p + oy), g3r = __ldg(p + oy + ox);
+    const float g3 = (ox != 0 && oy != 0) ? g3r : g0;
+    return bilerp(g0, g1, g2, g3, hh, v);
+}
+
 // The same, split into position, loads and arithmetic, so that a caller can put several samples' loads in
 // flight before consuming any of them, or take the four texels from elsewhere when (x0, y0) coincide.
 struct TapPos {

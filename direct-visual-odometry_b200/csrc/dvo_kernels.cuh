@@ -854,7 +854,9 @@ __device__ __forceinline__ float search_ssd(float s0, float s1, float s2, float 
     const float d0 = s0 - og, d1 = s1 - og, d2 = s2 - og;
     float ssd = (float)__dadd_rn(0.0, __dmul_rn(1.0 * 1 / 3, (double)(d0 * d0))); // :134
     ssd = (float)__dadd_rn((double)ssd, __dmul_rn(1.0 * 2 / 3, (double)(d1 * d1)));
-    ssd = (float)__dadd_rn((double)ssd, __dmul_rn(1.0 * 3 / 3, (double)(d2 * d2)));
+    // third term: weight 3/3 = 1.0, i.e. (float)((double)ssd + (double)(d2 * d2)).  For two non-negative floats that equals the
+    // float sum: the double sum is exact unless the exponents are > 29 bits apart, and then both roundings return ssd itself.
+    ssd = __fadd_rn(ssd, d2 * d2);
     return ssd;
 }
 
@@ -937,16 +939,17 @@ __device__ __forceinline__ void warp_search(SearchSmem& sm, bool active, const f
             // which is CHECKED per step: equal coordinates -> the tap of two steps ago is reused, otherwise it is sampled.  One new
             // tap per step instead of three, results bit-identical.
             float prevx = ptx, prevy = pty;                    // pt of the previous step (the checkpoint itself for k = 1)
-            float c_prev = subpixel_dense(img, w, h, ptx, pty); // tap at prev
+            const float wf = (float)w, hf = (float)h;
+            float c_prev = subpixel_dense_nb(img, w, h, wf, hf, ptx, pty); // tap at prev
             ptx += dx;
             pty += dy;
-            float c_cur = subpixel_dense(img, w, h, ptx + dx * 0.0f, pty + dy * 0.0f); // tap at pt (k = 1)
+            float c_cur = subpixel_dense_nb(img, w, h, wf, hf, ptx + dx * 0.0f, pty + dy * 0.0f); // tap at pt (k = 1)
             unsigned long long kbest = ~0ull;
 #pragma unroll(SEARCH_UNROLL)
             for (int k = 1; k <= cnt; k++) {
-                const float s2 = subpixel_dense(img, w, h, ptx + dx * 1.0f, pty + dy * 1.0f);
+                const float s2 = subpixel_dense_nb(img, w, h, wf, hf, ptx + dx * 1.0f, pty + dy * 1.0f);
                 const float bx = ptx + dx * -1.0f, by = pty + dy * -1.0f;
-                const float s0 = (bx == prevx && by == prevy) ? c_prev : subpixel_dense(img, w, h, bx, by);
+                const float s0 = (bx == prevx && by == prevy) ? c_prev : subpixel_dense_nb(img, w, h, wf, hf, bx, by);
                 const unsigned long long key = ((unsigned long long)__float_as_uint(search_ssd(s0, c_cur, s2, ogp)) << 32) | (unsigned)(b0 + k);
                 if (key < kbest) kbest = key;
                 c_prev = c_cur; c_cur = s2;
