@@ -272,6 +272,20 @@ def peak_hbm():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of `kernel` from the newest committed `ncu --set full` capture
+    (profiles/*_traffic.json, written by scripts/ncu_summary.py traffic).  A captured launch is ONE frame of the same workload."""
+    import glob
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "*_traffic.json")), reverse=True):
+        try:
+            k = json.load(open(path))["kernels"].get(kernel)
+            if k:
+                return k["dram_bytes"], os.path.basename(path)
+        except Exception:
+            continue
+    return None, None
+
+
 def run_other_configs(lib):
     """The single-stream configurations of BASELINE.json (the metric also names 1080p): device-resident, CUDA events on the
     library's stream.  Reported beside the headline line, never instead of it.
@@ -538,6 +552,7 @@ def run_gpu_arm(args, rank, world, local_rank, dist):
         table.append(dict(kernel=name, launches=kn, avg_launch_us=1e3 * kms / kn if kn else None, share=kms / tot_ms,
                           algorithmic_bytes_per_launch=b / kn if kn else None, achieved_gbs=gbs, frac=gbs / peak, bytes_model=what))
     top = table[0]
+    traffic, traffic_src = ncu_traffic(top["kernel"])
     res = dict(
         value=world * S * K_ / (ms * 1e-3), ms_per_step=ms / K_,
         e2e=dict(value=world * S * E / e2e_s, unit="frames/s", h2d_bytes_per_step=h2d_bytes, d2h_bytes_per_step=S * 64, steps=E,
@@ -551,7 +566,7 @@ def run_gpu_arm(args, rank, world, local_rank, dist):
                          "dvo_vo_submit_gray8" if e2e_u8 else "dvo_vo_submit", e2e_first + W_, n_total)),
         gpu_launches=int(l1 - l0), clocks=clocks,
         roofline=dict(kernel=top["kernel"], bound="hbm", achieved=top["achieved_gbs"], peak=peak, unit="GB/s", frac=top["frac"],
-                      traffic=None, peak_source=peak_src, launches=top["launches"], avg_launch_us=top["avg_launch_us"],
+                      traffic=traffic, traffic_source=traffic_src, peak_source=peak_src, launches=top["launches"], avg_launch_us=top["avg_launch_us"],
                       algorithmic_bytes_per_launch=top["algorithmic_bytes_per_launch"], share_of_step=top["share"],
                       bytes_model=top["bytes_model"]),
         kernels=table,

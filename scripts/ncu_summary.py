@@ -2,6 +2,8 @@
 """Summaries of ncu output for profiles/ (run here, no GPU needed).
   launches <launches.csv>            per-kernel count / total / average / share of device time
   full <prof.ncu-rep>                selected raw metrics per profiled launch
+  traffic <prof.ncu-rep>             JSON {kernel: {dram_bytes, dram_read, dram_write, duration_us}} of the FIRST captured launch of each
+                                     kernel (dram__bytes_read.sum + dram__bytes_write.sum) - bench.py's roofline.traffic reads it
 """
 import collections
 import csv
@@ -44,5 +46,23 @@ def full(path):
                 print("   %-70s %s %s" % (k, r[idx[k]], rows[1][idx[k]]))
 
 
+def traffic(path):
+    import json
+    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(out)))
+    idx = {h: i for i, h in enumerate(rows[0])}
+    unit = rows[1]
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    res = collections.OrderedDict()
+    for r in rows[2:]:
+        k = r[idx["Kernel Name"]].split("(")[0]
+        if k in res:
+            continue
+        rd = float(r[idx["dram__bytes_read.sum"]]) * scale[unit[idx["dram__bytes_read.sum"]]]
+        wr = float(r[idx["dram__bytes_write.sum"]]) * scale[unit[idx["dram__bytes_write.sum"]]]
+        res[k] = dict(dram_bytes=rd + wr, dram_read=rd, dram_write=wr, duration_us=float(r[idx["gpu__time_duration.sum"]]))
+    print(json.dumps(dict(source=path.split("/")[-1], how="ncu --set full --clock-control none, first captured launch of each kernel", kernels=res), indent=1))
+
+
 if __name__ == "__main__":
-    {"launches": launches, "full": full}[sys.argv[1]](sys.argv[2])
+    {"launches": launches, "full": full, "traffic": traffic}[sys.argv[1]](sys.argv[2])
