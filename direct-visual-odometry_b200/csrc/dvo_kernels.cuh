@@ -389,9 +389,25 @@ struct TrackCtl { // per-CTA copy of the stream's iteration state
     float Tp[16]; // exp(xi): left operand of the next se3::concatenate (leader CTA only)
 };
 
+#ifdef DVO_TRK_PROF
+__device__ unsigned int g_trk_stream_ns[1024]; // ns stream s spent in the last k_track launch
+__device__ unsigned long long g_trk_prof[8]; // ns of stream 0: [0] pixel loop, [1] reduce, [2] gn_tail, [3] iterations, [4] whole kernel, [5] tail: solve, [6] tail: concatenate, [7] tail: exp + rest
+__device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#define TRK_PROF(i, t0) do { if (s == 0 && b == 0 && tid == 0) { const unsigned long long t1_ = gtimer(); g_trk_prof[i] += t1_ - (t0); (t0) = t1_; } } while (0)
+#else
+#define TRK_PROF(i, t0) do { } while (0)
+#endif
+#ifdef DVO_TRK_PROF
+#define TAIL_PROF(i, t0) do { if (s == 0) { const unsigned long long t1_ = gtimer(); g_trk_prof[i] += t1_ - (t0); (t0) = t1_; } } while (0)
+#else
+#define TAIL_PROF(i, t0) do { } while (0)
+#endif
 // One Gauss-Newton tail: solve, compose, log, stop rules (optimize.cpp:92-98, tracker.cpp:46-73).
 __device__ __noinline__ void gn_tail(const Consts& c, const TrackArgs& a, TrackState* st, int s, const double* stot, TrackCtl* ctl)
 {
+#ifdef DVO_TRK_PROF
+    unsigned long long tq = gtimer();
+#endif
     const int level = ctl->level;
     const LevelGeom& g = c.lv[level];
     const int valid = (int)stot[28];
@@ -403,6 +419,7 @@ __device__ __noinline__ void gn_tail(const Consts& c, const TrackArgs& a, TrackS
         for (int q = 0; q < 6; q++) upd[q] = (float)xs[q];
         residual = (float)stot[27] / (float)valid; // optimize.cpp:98
     }
+    TAIL_PROF(5, tq);
     float xi[6], xin[6];
     for (int q = 0; q < 6; q++) xi[q] = st->xi[q];
     const int n_total = st->n_total;
@@ -417,6 +434,7 @@ __device__ __noinline__ void gn_tail(const Consts& c, const TrackArgs& a, TrackS
             moved = true;
         }
     }
+    TAIL_PROF(6, tq);
     if (a.log && n_total < a.log_cap) {
         dvo_iter_log* L = a.log + (size_t)s * a.log_cap + n_total;
         L->level = level; L->iteration = ctl->iter; L->valid_pixels = valid; L->residual = residual;
@@ -442,6 +460,7 @@ __device__ __noinline__ void gn_tail(const Consts& c, const TrackArgs& a, TrackS
     // publish for the other CTAs of the stream and for the host
     st->level = ctl->level; st->iter = ctl->iter; st->done = ctl->done;
     for (int q = 0; q < 12; q++) st->Tn[q] = ctl->T[q];
+    TAIL_PROF(7, tq);
 }
 
 // pose table of Mapper::update (mapper.cpp:107): r_xi = concatenate(obj.m_xi, -born.m_xi) depends on the
@@ -518,14 +537,6 @@ __device__ __noinline__ void vo_decide(const Consts& c, const TrackArgs& a, cons
     m->reg_slot = v->kf_slot;
 }
 
-#ifdef DVO_TRK_PROF
-__device__ unsigned int g_trk_stream_ns[1024]; // ns stream s spent in the last k_track launch
-__device__ unsigned long long g_trk_prof[8]; // ns of stream 0: [0] pixel loop, [1] reduce, [2] gn_tail, [3] iterations, [4] whole kernel
-__device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
-#define TRK_PROF(i, t0) do { if (s == 0 && b == 0 && tid == 0) { const unsigned long long t1_ = gtimer(); g_trk_prof[i] += t1_ - (t0); (t0) = t1_; } } while (0)
-#else
-#define TRK_PROF(i, t0) do { } while (0)
-#endif
 __device__ __forceinline__ unsigned int ld_volatile_u32(const unsigned int* p) { return *(const volatile unsigned int*)p; }
 
 __global__ void __launch_bounds__(TRK_THREADS, TRK_MINB) k_track(const __grid_constant__ Consts c, const TrackArgs a)
@@ -536,9 +547,10 @@ __global__ void __launch_bounds__(TRK_THREADS, TRK_MINB) k_track(const __grid_co
     TrackState* __restrict__ st = a.st + s;
 
     __shared__ TrackCtl ctl;
-    __shared__ double sred[TRK_THREADS / 32][NACC + 1];
+    __shared__ __align__(16) double sC[TRK_THREADS / 32][64]; // per-warp X^T X
+    __shared__ int scnt[TRK_THREADS / 32];
     __shared__ double stot[32];
-    __shared__ __align__(16) double srow[TRK_THREADS / 32][32][10]; // row pitch 80 B: conflict-free 16 B stores
+    __shared__ __align__(16) float srow[TRK_THREADS / 32][32 * 8];  // per-warp X: 32 pixels x {J[0..5], w r, r}
     __shared__ const float* s_obj;
     __shared__ const float* s_ref;
     __shared__ const float2* s_ds;
@@ -579,17 +591,6 @@ __global__ void __launch_bounds__(TRK_THREADS, TRK_MINB) k_track(const __grid_co
     const float2* __restrict__ ref_ds = s_ds;
     const unsigned int gen0 = s_gen0;
     unsigned int epoch = 0;
-    // product pair of this lane: 0..20 = J_p J_q (p <= q, row-major upper triangle), 21..26 = J_q (w r)
-    int pair_p = 0, pair_q = 0;
-    {
-        const int L = tid & 31;
-        if (L < 21) {
-            int p = 0, rem = L;
-            while (rem >= 6 - p) { rem -= 6 - p; p++; }
-            pair_p = p; pair_q = p + rem;
-        } else if (L < 27) { pair_p = L - 21; pair_q = 6; }
-    }
-
 #ifdef DVO_TRK_PROF
     unsigned long long tp = gtimer();
     const unsigned long long tp_start = tp;
@@ -612,27 +613,49 @@ __global__ void __launch_bounds__(TRK_THREADS, TRK_MINB) k_track(const __grid_co
         const int per = (count + B - 1) / B;
         const int j0 = b * per, j1 = min(count, j0 + per);
 
-        // Normal equations, accumulated PER SUM instead of per pixel: the 32 pixels of a warp-batch leave their
-        // row {J[0..5], w r} (as doubles) in shared memory and lane L folds product pair L of all 32 rows into ONE
-        // fp64 accumulator (21 J^T J + 6 J^T (w r)).  29 per-thread accumulators would cost 58 registers and cap
-        // the kernel at 2 x 256 threads per SM; this way it fits 64 registers (1024 threads per SM).
+        // Normal equations on the fp64 TENSOR CORES.  With X the 32 x 8 matrix of a warp-batch (row = pixel, columns J[0..5], w r, r)
+        // the iteration needs X^T X: 21 J^T J + 6 J^T (w r) + sum r^2 are all entries of that 8 x 8 product.  Each lane leaves its
+        // row as floats in shared memory and the warp issues 8 mma.sync.m8n8k4.f64 (4 pixels each): A (8 x 4, row-major) and B
+        // (4 x 8, column-major) want X[k][r] on lane 4 r + k BOTH, so one conflict-free LDS.32 + F2D feeds both operands and the
+        // 8 x 8 fp64 accumulator is 2 registers pairs per lane.  Exact fp64 FMAs like the scalar code, ~30 instructions per batch
+        // instead of 110 (one accumulator per sum through shared memory) or 58 registers (29 accumulators per thread).
         const int lane = tid & 31, warp = tid >> 5;
-        double accL = 0.0, accR = 0.0; // lane's pair sum; this thread's sum of r^2
+        double c0 = 0.0, c1 = 0.0; // C[lane >> 2][2 (lane & 3) + {0, 1}] of X^T X
         int nvalid = 0;
-        double(*rows)[10] = srow[warp];
+        float* rows = srow[warp];  // [32 pixels][8]
+        const int frag_ofs = (lane & 3) * 8 + (lane >> 2); // X[k = lane & 3][r = lane >> 2] within a group of 4 pixels
 
+        // A warp-batch is two dependent gathers deep (depth -> warp -> 12 gray taps) and a frame is only ~50 batches per warp, so
+        // the first gather of batch k + 1 is requested before batch k is processed; pixel coordinates advance incrementally.
+        int jn = j0 + warp * 32 + lane, xn = 0, yn = 0;
+        float2 dsr_n = make_float2(0.f, 0.f);
+        float i1_n = 0.f;
+        if (jn < j1) {
+            const int jy = jn / rw;
+            yn = ry0 + jy; xn = rx0 + (jn - jy * rw);
+            const size_t ti = top_index(lv, xn, yn);
+            dsr_n = __ldg(ref_ds + ti);
+            i1_n = __ldg(obj_gray + ti);
+        }
+        const int step_x = TRK_THREADS % max(rw, 1), step_y = TRK_THREADS / max(rw, 1);
         for (int jb = j0 + warp * 32; jb < j1; jb += TRK_THREADS) {
-            const int j = jb + lane;
+            const int j = jn;
+            const int x = xn, y = yn;
+            const float2 dsr = dsr_n;
+            const float i1_raw = i1_n;
+            jn += TRK_THREADS;
+            xn += step_x; yn += step_y;
+            if (xn > rx1) { xn -= rw; yn++; }
+            if (jn < j1) {
+                const size_t ti = top_index(lv, xn, yn);
+                dsr_n = __ldg(ref_ds + ti);
+                i1_n = __ldg(obj_gray + ti);
+            }
             bool ok = false;
-            float J[6], bw = 0.f;
-            int x = 0, y = 0;
+            float J[6], bw = 0.f, rr = 0.f;
             if (j < j1) {
-                const int jy = j / rw;
-                y = ry0 + jy; x = rx0 + (j - jy * rw);
-                const size_t ti = top_index(lv, x, y);
-                const float2 dsr = __ldg(ref_ds + ti);
                 const float depth = level_value(lv, dsr.x);
-                const float I1 = level_value(lv, __ldg(obj_gray + ti));
+                const float I1 = level_value(lv, i1_raw);
                 ok = !(depth < c.min_depth_f) && !is_invalid(I1); // optimize.cpp:39,46
                 if (ok) {
                     float X, Y, Z;
@@ -659,7 +682,7 @@ __global__ void __launch_bounds__(TRK_THREADS, TRK_MINB) k_track(const __grid_co
                         const float sg0 = level_value(lv, dsr.y);
                         const float sg = (sg0 < c.sigma_lo) ? c.sigma_lo : (c.sigma_hi < sg0) ? c.sigma_hi : sg0; // std::clamp :83
                         bw = r * (step / sg);
-                        accR += (double)(r * r);
+                        rr = r;
                         nvalid++;
                     }
                 }
@@ -667,42 +690,53 @@ __global__ void __launch_bounds__(TRK_THREADS, TRK_MINB) k_track(const __grid_co
             }
             const unsigned vm = __ballot_sync(0xffffffffu, ok);
             if (vm) { // warp-uniform
-                double2* rw2 = reinterpret_cast<double2*>(rows[lane]);
+                float4* rw4 = reinterpret_cast<float4*>(rows + lane * 8);
                 if (ok) {
-                    rw2[0] = make_double2((double)J[0], (double)J[1]);
-                    rw2[1] = make_double2((double)J[2], (double)J[3]);
-                    rw2[2] = make_double2((double)J[4], (double)J[5]);
-                    rw2[3] = make_double2((double)bw, 0.0);
+                    rw4[0] = make_float4(J[0], J[1], J[2], J[3]);
+                    rw4[1] = make_float4(J[4], J[5], bw, rr);
                 } else {
-                    rw2[0] = rw2[1] = rw2[2] = rw2[3] = make_double2(0.0, 0.0);
+                    rw4[0] = rw4[1] = make_float4(0.f, 0.f, 0.f, 0.f);
                 }
                 __syncwarp();
-                const double* pa = &rows[0][pair_p];
-                const double* pb = &rows[0][pair_q];
 #pragma unroll
-                for (int i = 0; i < 32; i++) accL = fma(pa[i * 10], pb[i * 10], accL);
+                for (int m = 0; m < 8; m++) {
+                    if ((vm >> (4 * m)) & 0xfu) { // warp-uniform: skip groups of 4 pixels without a valid one
+                        const double xv = (double)rows[m * 32 + frag_ofs];
+                        asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
+                            : "+d"(c0), "+d"(c1) : "d"(xv), "d"(xv));
+                    }
+                }
                 __syncwarp();
             }
         }
 
         // ---- reduction in a fixed order (deterministic for a given B) ----
         {
-            double vr = accR;
-            int vn = nvalid;
-#pragma unroll
-            for (int off = 16; off > 0; off >>= 1) {
-                vr += __shfl_down_sync(0xffffffffu, vr, off);
-                vn += __shfl_down_sync(0xffffffffu, vn, off);
-            }
-            if (lane < 27) sred[warp][lane] = accL;
-            if (lane == 0) { sred[warp][27] = vr; sred[warp][28] = (double)vn; }
+            const int vn = __reduce_add_sync(0xffffffffu, nvalid);
+            double2* cw = reinterpret_cast<double2*>(sC[warp] + (lane >> 2) * 8 + 2 * (lane & 3));
+            *cw = make_double2(c0, c1);
+            if (lane == 0) scnt[warp] = vn;
         }
         __syncthreads();
         TRK_PROF(0, tp);
         if (tid < NACC) {
+            // sum k: 0..20 = (J^T J)[p][q], p <= q, row-major upper triangle; 21..26 = (J^T (w r))[q]; 27 = sum r^2; 28 = valid pixels
+            int e = 63;
+            if (tid < 21) {
+                int p = 0, rem = tid;
+                while (rem >= 6 - p) { rem -= 6 - p; p++; }
+                e = p * 8 + p + rem;
+            } else if (tid < 27) e = (tid - 21) * 8 + 6;
             double v = 0;
+            if (tid == 28) {
+                int n = 0;
 #pragma unroll
-            for (int wv = 0; wv < TRK_THREADS / 32; wv++) v += sred[wv][tid];
+                for (int wv = 0; wv < TRK_THREADS / 32; wv++) n += scnt[wv];
+                v = (double)n;
+            } else {
+#pragma unroll
+                for (int wv = 0; wv < TRK_THREADS / 32; wv++) v += sC[wv][e];
+            }
             if (B == 1) stot[tid] = v;
             else a.partials[((size_t)s * B + b) * 32 + tid] = v;
         }

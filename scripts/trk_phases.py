@@ -38,6 +38,7 @@ for i in range(frames):
     if i % 20 == 19:
         lib.dvo_debug_trk_prof(dv.ctx, st, 1)
         n = 20.0
-        print("frames %3d-%3d (per frame, stream 0): loop %.1f us  reduce %.1f us  tail %.1f us  iterations %.2f  kernel %.1f us" % (
-            i - 19, i, st[0] / n / 1e3, st[1] / n / 1e3, st[2] / n / 1e3, st[3] / n, st[4] / n / 1e3))
+        print("frames %3d-%3d (per frame, stream 0): loop %.1f us  reduce %.1f us  tail %.1f us (solve %.1f  concatenate %.1f  exp+rest %.1f)  "
+              "iterations %.2f  kernel %.1f us" % (i - 19, i, st[0] / n / 1e3, st[1] / n / 1e3, st[2] / n / 1e3, st[5] / n / 1e3, st[6] / n / 1e3,
+                                                  st[7] / n / 1e3, st[3] / n, st[4] / n / 1e3))
 dv.close()
