@@ -615,6 +615,8 @@ def main():
 
     dist = None
     if world > 1:
+        # stdout carries exactly ONE line (the JSON): NCCL's banner / debug lines ("NCCL version ...") go to stderr
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         import torch
         import torch.distributed as td
         torch.cuda.set_device(local_rank)

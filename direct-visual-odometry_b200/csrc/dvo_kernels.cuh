@@ -1115,7 +1115,10 @@ __global__ void k_map_prepare(const __grid_constant__ Consts c, MapState* __rest
 
 // The ROI of Mapper::update (mapper.cpp:90) clipped to the image; threads are laid out over it in
 // row-major order, which is also the reference's visiting order restricted to the ROI.
-constexpr int MAPU_THREADS = 64; // small blocks: a block waits for its slowest epipolar search
+#ifndef DVO_MAPU_THREADS
+#define DVO_MAPU_THREADS 64
+#endif
+constexpr int MAPU_THREADS = DVO_MAPU_THREADS; // small blocks: a block waits for its slowest epipolar search
 struct MapRoi {
     int x0, y0, w, h, n; // origin, size, pixel count
     int nblk;            // blocks of MAPU_THREADS covering it
@@ -1237,7 +1240,7 @@ __global__ void __launch_bounds__(256) k_map_scan(const __grid_constant__ Consts
 // Mapper::update phase B: replay of the mt19937 stream for the rejected pixels in row-major order.
 // rank = (rejects in the preceding phase-A CTAs, k_map_scan) + (rejects before this thread in its phase-A CTA).
 // One CTA covers APPLY_SUB phase-A CTAs.   grid = (ceil(roi.nblk / APPLY_SUB), S)
-constexpr int APPLY_SUB = 4;
+constexpr int APPLY_SUB = 256 / MAPU_THREADS;
 __global__ void __launch_bounds__(MAPU_THREADS * APPLY_SUB) k_map_update_apply(const __grid_constant__ Consts c, const MapRoi roi,
                                                           const SlotDev* __restrict__ slots, MapState* __restrict__ mst,
                                                           const uint8_t* __restrict__ flags, const unsigned int* __restrict__ blockcnt,
