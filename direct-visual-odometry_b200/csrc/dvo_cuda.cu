@@ -47,6 +47,7 @@ struct dvo_ctx {
     unsigned int* d_blockcnt = nullptr;
     int nblk_top = 0;
     int* d_winner = nullptr;
+    int* d_remap = nullptr;        // [n_top] source pixel of every finest-level pixel (bgr8 ingest), built on first use
     float* d_tmp = nullptr;
     uint32_t* d_rng = nullptr;
     float* d_stage_in = nullptr;   // [S][in_h][in_w]
@@ -292,7 +293,7 @@ extern "C" void dvo_destroy(dvo_ctx* ctx)
     for (auto& s : ctx->slots) if (s.base) cudaFree(s.base);
     cudaFree(ctx->d_slots); cudaFree(ctx->d_ts); cudaFree(ctx->d_ms); cudaFree(ctx->d_vo); cudaFree(ctx->d_hist);
     cudaFree(ctx->d_tab); cudaFree(ctx->d_partials); cudaFree(ctx->d_log); cudaFree(ctx->d_flags); cudaFree(ctx->d_mask);
-    cudaFree(ctx->d_blockcnt); cudaFree(ctx->d_winner); cudaFree(ctx->d_tmp); cudaFree(ctx->d_rng); cudaFree(ctx->d_stage_in);
+    cudaFree(ctx->d_blockcnt); cudaFree(ctx->d_winner); cudaFree(ctx->d_remap); cudaFree(ctx->d_tmp); cudaFree(ctx->d_rng); cudaFree(ctx->d_stage_in);
     for (int k = 0; k < 3; k++) cudaFree(ctx->d_stage[k]);
     cudaFree(ctx->d_small); cudaFree(ctx->d_ismall); cudaFree(ctx->d_forced);
     if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
@@ -385,16 +386,19 @@ struct KTimer { // records an event pair around one launch when timing is on
 
 // slot >= 0: that slot for every stream; slot < 0: each stream's current VO slot.
 // rows_only: gray_dev holds only the input rows that Convert::cullImage samples (host staging path).
-static int build_frame(dvo_ctx* ctx, int slot, const float* gray_dev, bool rows_only, bool gray8 = false, int invalid_code = -1)
+// kind: 0 float gray, 1 8-bit gray (aux = invalid_code), 2 8-bit BGR / BGRA (aux = channels; whole frames, through the remap index)
+static int build_frame(dvo_ctx* ctx, int slot, const float* gray_dev, bool rows_only, int kind = 0, int aux = -1)
 {
     const Consts& c = ctx->c;
     const VoState* vo = slot < 0 ? ctx->d_vo : nullptr;
     const LevelGeom& gt = c.lv[c.L - 1];
     dim3 grid(cdiv(gt.n, 1024), c.S);
     KTimer t(ctx, K_CULL);
-    if (gray8)
+    if (kind == 2)
+        k_cull_bgr8<<<dim3(cdiv(gt.n, 256), c.S), 256, 0, ctx->stream>>>(c, (const uint8_t*)gray_dev, aux, ctx->d_remap, ctx->d_slots, slot, vo);
+    else if (kind == 1)
         k_cull_gray8<<<grid, 256, 0, ctx->stream>>>(c, (const uint8_t*)gray_dev, rows_only ? gt.h : c.in_h, rows_only ? 0 : c.culls,
-                                                    invalid_code, ctx->d_slots, slot, vo);
+                                                    aux, ctx->d_slots, slot, vo);
     else
         k_cull_gray<<<grid, 256, 0, ctx->stream>>>(c, gray_dev, rows_only ? gt.h : c.in_h, rows_only ? 0 : c.culls, ctx->d_slots, slot, vo);
     KCHECK();
@@ -449,7 +453,54 @@ extern "C" int dvo_frame_create_gray8(dvo_ctx* ctx, int* slot, const uint8_t* gr
     if (rc) return rc;
     rc = find_free_slot(ctx, slot);
     if (rc) return rc;
-    return build_frame(ctx, *slot, ctx->d_stage_in, rows_only, true, invalid_code);
+    return build_frame(ctx, *slot, ctx->d_stage_in, rows_only, 1, invalid_code);
+}
+
+// ---- 8-bit BGR ingest: Loader::getNormalizedUndistortedImages on the device ------------------------
+static int remap_build(dvo_ctx* ctx, const float* map_x, const float* map_y)
+{
+    const Consts& c = ctx->c;
+    const LevelGeom& gt = c.lv[c.L - 1];
+    if (!ctx->d_remap) CK(cudaMalloc(&ctx->d_remap, sizeof(int) * (size_t)gt.n));
+    float *dx = nullptr, *dy = nullptr;
+    if (map_x) { // the two staging planes hold [S][in_h][in_w] floats each: room for one map
+        const size_t b = sizeof(float) * (size_t)c.in_w * c.in_h;
+        dx = ctx->d_stage[0]; dy = ctx->d_stage[1];
+        CK(cudaMemcpyAsync(dx, map_x, b, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(dy, map_y, b, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    k_build_remap<<<cdiv(gt.n, 256), 256, 0, ctx->stream>>>(c, dx, dy, ctx->d_remap);
+    KCHECK();
+    CK(cudaStreamSynchronize(ctx->stream));
+    return DVO_OK;
+}
+
+extern "C" int dvo_set_undistort_map(dvo_ctx* ctx, const float* map_x, const float* map_y)
+{
+    ARG((map_x == nullptr) == (map_y == nullptr), "give both maps or neither");
+    return remap_build(ctx, map_x, map_y);
+}
+
+static int stage_bgr(dvo_ctx* ctx, float* dst, cudaStream_t st, const uint8_t* bgr8, int channels)
+{
+    const Consts& c = ctx->c;
+    ARG(bgr8 && (channels == 3 || channels == 4), "bgr8: null frame or channels not 3 / 4");
+    if (!ctx->d_remap) { // no map given: identity (Loader::getNormalizedImages)
+        int rc = remap_build(ctx, nullptr, nullptr);
+        if (rc) return rc;
+    }
+    CK(cudaMemcpyAsync(dst, bgr8, (size_t)c.S * c.in_w * c.in_h * channels, cudaMemcpyHostToDevice, st));
+    return DVO_OK;
+}
+
+extern "C" int dvo_frame_create_bgr8(dvo_ctx* ctx, int* slot, const uint8_t* bgr8, int channels)
+{
+    ARG(slot, "null argument");
+    int rc = stage_bgr(ctx, ctx->d_stage_in, ctx->stream, bgr8, channels);
+    if (rc) return rc;
+    rc = find_free_slot(ctx, slot);
+    if (rc) return rc;
+    return build_frame(ctx, *slot, ctx->d_stage_in, false, 2, channels);
 }
 
 extern "C" int dvo_frame_release(dvo_ctx* ctx, int slot)
@@ -998,7 +1049,7 @@ extern "C" int dvo_vo_force_pose(dvo_ctx* ctx, const float* rel_xi)
 // One odometrize for every stream, enqueued on the context's stream.  after_cull (nullable) is recorded
 // once the staging buffer has been consumed; sync_out = false leaves the pose read-back asynchronous.
 static int vo_push_impl(dvo_ctx* ctx, const float* gray_dev, const float* init_depth, const float* init_sigma, float* T_out,
-                        cudaEvent_t after_cull, bool sync_out, bool gray8 = false, int invalid_code = -1)
+                        cudaEvent_t after_cull, bool sync_out, int kind = 0, int aux = -1)
 {
     const Consts& c = ctx->c;
     ARG(gray_dev, "null gray");
@@ -1017,7 +1068,7 @@ static int vo_push_impl(dvo_ctx* ctx, const float* gray_dev, const float* init_d
             sh.in_use = true;
         }
     }
-    int rc = build_frame(ctx, -1, gray_dev, ctx->rows_only_staged, gray8, invalid_code); // make_shared<Frame>(gray, K, 3, 2), system.hpp:47
+    int rc = build_frame(ctx, -1, gray_dev, ctx->rows_only_staged, kind, aux); // make_shared<Frame>(gray, K, 3, 2), system.hpp:47
     ctx->rows_only_staged = false;
     if (rc) return rc;
     if (after_cull) CK(cudaEventRecord(after_cull, ctx->stream));
@@ -1072,8 +1123,18 @@ extern "C" int dvo_vo_push_gray8(dvo_ctx* ctx, const uint8_t* gray8, int invalid
     int rc = stage_gray_to(ctx, ctx->d_stage_in, ctx->stream, gray8, &rows_only, 1);
     if (rc) return rc;
     ctx->rows_only_staged = rows_only;
-    return vo_push_impl(ctx, ctx->d_stage_in, init_depth, init_sigma, T_out, ctx->copy_stream ? ctx->ev_consumed[0] : nullptr, true, true,
+    return vo_push_impl(ctx, ctx->d_stage_in, init_depth, init_sigma, T_out, ctx->copy_stream ? ctx->ev_consumed[0] : nullptr, true, 1,
                         invalid_code);
+}
+
+extern "C" int dvo_vo_push_bgr8(dvo_ctx* ctx, const uint8_t* bgr8, int channels, const float* init_depth, const float* init_sigma,
+                                float* T_out)
+{
+    int rc = stage_bgr(ctx, ctx->d_stage_in, ctx->stream, bgr8, channels);
+    if (rc) return rc;
+    ctx->rows_only_staged = false;
+    return vo_push_impl(ctx, ctx->d_stage_in, init_depth, init_sigma, T_out, ctx->copy_stream ? ctx->ev_consumed[0] : nullptr, true, 2,
+                        channels);
 }
 
 // Pipelined submission: two staging buffers filled on a copy stream, so frame n+1 crosses PCIe while
@@ -1097,7 +1158,7 @@ static int pipe_init(dvo_ctx* ctx)
     return DVO_OK;
 }
 
-static int vo_submit_impl(dvo_ctx* ctx, const void* gray, float* T_out, bool gray8, int invalid_code)
+static int vo_submit_impl(dvo_ctx* ctx, const void* gray, float* T_out, int kind, int aux)
 {
     ARG(gray, "null gray");
     if (ctx->pp_in_flight >= 2) {
@@ -1111,12 +1172,20 @@ static int vo_submit_impl(dvo_ctx* ctx, const void* gray, float* T_out, bool gra
     // filled by a plain dvo_vo_push on the compute stream before
     CK(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_consumed[k], 0));
     bool rows_only = false;
-    rc = stage_gray_to(ctx, ctx->d_stage_pp[k], ctx->copy_stream, gray, &rows_only, gray8 ? 1 : sizeof(float));
+    if (kind == 2) {
+        if (!ctx->d_remap) { // before the copy stream is involved: remap_build works on the compute stream
+            rc = remap_build(ctx, nullptr, nullptr);
+            if (rc) return rc;
+        }
+        rc = stage_bgr(ctx, ctx->d_stage_pp[k], ctx->copy_stream, (const uint8_t*)gray, aux);
+    } else {
+        rc = stage_gray_to(ctx, ctx->d_stage_pp[k], ctx->copy_stream, gray, &rows_only, kind == 1 ? 1 : sizeof(float));
+    }
     if (rc) return rc;
     CK(cudaEventRecord(ctx->ev_copied[k], ctx->copy_stream));
     CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_copied[k], 0));
     ctx->rows_only_staged = rows_only;
-    rc = vo_push_impl(ctx, ctx->d_stage_pp[k], nullptr, nullptr, T_out, ctx->ev_consumed[k], false, gray8, invalid_code);
+    rc = vo_push_impl(ctx, ctx->d_stage_pp[k], nullptr, nullptr, T_out, ctx->ev_consumed[k], false, kind, aux);
     if (rc) return rc;
     CK(cudaEventRecord(ctx->ev_done[k], ctx->stream));
     ctx->pp_head++;
@@ -1124,11 +1193,16 @@ static int vo_submit_impl(dvo_ctx* ctx, const void* gray, float* T_out, bool gra
     return DVO_OK;
 }
 
-extern "C" int dvo_vo_submit(dvo_ctx* ctx, const float* gray, float* T_out) { return vo_submit_impl(ctx, gray, T_out, false, -1); }
+extern "C" int dvo_vo_submit(dvo_ctx* ctx, const float* gray, float* T_out) { return vo_submit_impl(ctx, gray, T_out, 0, -1); }
+extern "C" int dvo_vo_submit_bgr8(dvo_ctx* ctx, const uint8_t* bgr8, int channels, float* T_out)
+{
+    ARG(channels == 3 || channels == 4, "channels not 3 / 4");
+    return vo_submit_impl(ctx, bgr8, T_out, 2, channels);
+}
 extern "C" int dvo_vo_submit_gray8(dvo_ctx* ctx, const uint8_t* gray8, int invalid_code, float* T_out)
 {
     ARG(invalid_code >= -1 && invalid_code <= 255, "bad invalid_code");
-    return vo_submit_impl(ctx, gray8, T_out, true, invalid_code);
+    return vo_submit_impl(ctx, gray8, T_out, 1, invalid_code);
 }
 
 extern "C" int dvo_vo_collect(dvo_ctx* ctx)

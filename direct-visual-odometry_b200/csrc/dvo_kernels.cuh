@@ -84,6 +84,47 @@ __global__ void __launch_bounds__(256) k_cull_gray8(const __grid_constant__ Cons
     }
 }
 
+// Undistortion map -> source index of every finest-level pixel: cv::remap(INTER_NEAREST) reads source pixel
+// (saturate_cast<short>(map_x), saturate_cast<short>(map_y)) = cvRound (round-half-even) clamped to short, BORDER_CONSTANT outside
+// the image; Convert::cullImage then keeps destination pixel (x << culls, y << culls).  idx = sy * in_w + sx, or -1.  grid = ceil(n_top/256)
+__global__ void __launch_bounds__(256) k_build_remap(const __grid_constant__ Consts c, const float* __restrict__ map_x,
+                                                     const float* __restrict__ map_y, int* __restrict__ idx)
+{
+    const LevelGeom g = c.lv[c.L - 1];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= g.n) return;
+    const int y = i / g.w, x = i - y * g.w;
+    const size_t src = (size_t)(y << c.culls) * c.in_w + (x << c.culls);
+    int sx = x << c.culls, sy = y << c.culls;
+    if (map_x) {
+        sx = max(-32768, min(32767, round_x86(map_x[src])));
+        sy = max(-32768, min(32767, round_x86(map_y[src]))); // NaN: cvRound gives INT_MIN -> -32768 -> outside
+    }
+    idx[i] = (sx >= 0 && sx < c.in_w && sy >= 0 && sy < c.in_h) ? sy * c.in_w + sx : -1;
+}
+
+// Loader::getNormalizedUndistortedImages + Frame ctor from 8-bit BGR(A): gather through the index map, cvtColor(BGR2GRAY) in
+// OpenCV's 15-bit fixed point, convertTo(1/255) as one fp32 multiply, INVALID outside the source image.  grid = (ceil(n_top/256), S)
+__global__ void __launch_bounds__(256) k_cull_bgr8(const __grid_constant__ Consts c, const uint8_t* __restrict__ in, int channels,
+                                                   const int* __restrict__ idx, const SlotDev* __restrict__ slots, int fixed,
+                                                   const VoState* __restrict__ vo)
+{
+    const int s = blockIdx.y;
+    const SlotDev& slot = slots[vo ? vo_cur_slot(c, vo[s].n_kf) : fixed];
+    const LevelGeom g = c.lv[c.L - 1];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= g.n) return;
+    const int si = __ldg(idx + i);
+    float v = DVO_INV;
+    if (si >= 0) {
+        const uint8_t* __restrict__ p = in + ((size_t)s * c.in_w * c.in_h + (size_t)si) * channels;
+        const int b = __ldcs(p), gg = __ldcs(p + 1), r = __ldcs(p + 2);
+        const int code = (b * 3735 + gg * 19235 + r * 9798 + (1 << 14)) >> 15;
+        v = __fmul_rn((float)code, (float)(1.0 / 255.0));
+    }
+    slot.gray[(size_t)s * g.n + i] = v;
+}
+
 // depth / sigma / age upload (Frame 6-arg ctor frame.hpp:91-106, updateDepthSigmaAge frame.cpp:47-54).
 // src arrays are [S][sh][sw]; shift = culls when full-res, 0 otherwise.  grid = (ceil(n_top/256), S)
 __global__ void __launch_bounds__(256) k_set_top(const __grid_constant__ Consts c, const SlotDev* __restrict__ slots, int fixed,

@@ -48,6 +48,7 @@ EXPORTS = [
     "dvo_copy_to_host", "dvo_copy_to_dev", "dvo_timer_start", "dvo_timer_stop", "dvo_launch_count", "dvo_gn_timing", "dvo_kernel_timing",
     "dvo_map_update_points", "dvo_se3_exp", "dvo_se3_log", "dvo_se3_concatenate", "dvo_vo_submit", "dvo_vo_collect",
     "dvo_frame_create_gray8", "dvo_vo_push_gray8", "dvo_vo_submit_gray8",
+    "dvo_set_undistort_map", "dvo_frame_create_bgr8", "dvo_vo_push_bgr8", "dvo_vo_submit_bgr8",
 ]
 
 
@@ -121,6 +122,10 @@ def load_library(path=None):
     lib.dvo_frame_create_gray8.argtypes = [C.c_void_p, I32P, C.c_void_p, C.c_int]
     lib.dvo_vo_push_gray8.argtypes = [C.c_void_p, C.c_void_p, C.c_int, F32P, F32P, F32P]
     lib.dvo_vo_submit_gray8.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+    lib.dvo_set_undistort_map.argtypes = [C.c_void_p, F32P, F32P]
+    lib.dvo_frame_create_bgr8.argtypes = [C.c_void_p, I32P, C.c_void_p, C.c_int]
+    lib.dvo_vo_push_bgr8.argtypes = [C.c_void_p, C.c_void_p, C.c_int, F32P, F32P, F32P]
+    lib.dvo_vo_submit_bgr8.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
     return lib
 
 
@@ -219,6 +224,41 @@ class Dvo:
         self._ck(self.lib.dvo_frame_create_gray8(self.ctx, C.byref(slot), g.ctypes.data_as(C.c_void_p), int(invalid_code)))
         self._ck(self.lib.dvo_sync(self.ctx))
         return slot.value
+
+    def set_undistort_map(self, map_x=None, map_y=None):
+        """The CV_32FC1 maps of cv::initUndistortRectifyMap (Loader::createUndistortMap, loader.cpp:15-30); None = identity."""
+        if map_x is None:
+            self._ck(self.lib.dvo_set_undistort_map(self.ctx, None, None))
+            return
+        mx = _f32(map_x); my = _f32(map_y)
+        assert mx.shape == my.shape == (self.params.height, self.params.width)
+        self._ck(self.lib.dvo_set_undistort_map(self.ctx, _p(mx), _p(my)))
+
+    def _stack_bgr(self, img):
+        a = np.ascontiguousarray(img, dtype=np.uint8)
+        if a.ndim == 3:
+            a = a[None]
+        assert a.shape[:3] == (self.S, self.params.height, self.params.width) and a.shape[3] in (3, 4), a.shape
+        return a
+
+    def frame_create_bgr8(self, bgr8):
+        """Frame from the 8-bit BGR / BGRA image: cvtColor + convertTo + remap(NEAREST) + cullImage on the device (loader.cpp:32-63)."""
+        g = self._stack_bgr(bgr8)
+        slot = C.c_int(-1)
+        self._ck(self.lib.dvo_frame_create_bgr8(self.ctx, C.byref(slot), g.ctypes.data_as(C.c_void_p), g.shape[3]))
+        self._ck(self.lib.dvo_sync(self.ctx))
+        return slot.value
+
+    def vo_push_bgr8(self, bgr8, init_depth=None, init_sigma=None, want_pose=True):
+        g = self._stack_bgr(bgr8)
+        w, h = self.level_size(self.L - 1)
+        d = self._stack(init_depth, h, w) if init_depth is not None else None
+        s = self._stack(init_sigma, h, w) if init_sigma is not None else None
+        T = np.empty((self.S, 4, 4), np.float32) if want_pose else None
+        self._ck(self.lib.dvo_vo_push_bgr8(self.ctx, g.ctypes.data_as(C.c_void_p), g.shape[3], _p(d), _p(s), _p(T)))
+        if not want_pose:
+            self._ck(self.lib.dvo_sync(self.ctx))
+        return T
 
     def frame_release(self, slot):
         self._ck(self.lib.dvo_frame_release(self.ctx, slot))

@@ -107,6 +107,17 @@ int dvo_frame_create_dev(dvo_ctx* ctx, int* slot, const float* gray_dev);
  * that are INVALID (-2.0, include/math/util.hpp:7): the border cv::remap(BORDER_CONSTANT, INVALID) leaves
  * (loader.cpp:39-40) cannot be expressed in 8 bits otherwise. */
 int dvo_frame_create_gray8(dvo_ctx* ctx, int* slot, const uint8_t* gray8, int invalid_code);
+/* The whole of Loader::getNormalizedUndistortedImages (src/core/loader.cpp:32-42,55-63) on the device, from the 8-bit BGR (or
+ * BGRA: the Kinect PNGs are 4-channel) frame cv::imread returns:
+ *   cv::cvtColor(BGR2GRAY)            8-bit fixed point, (3735 B + 19235 G + 9798 R + 2^14) >> 15 (OpenCV 4's RGB2Gray<uchar>)
+ *   convertTo(CV_32FC1, 1.0/255.0)    one fp32 multiply
+ *   cv::remap(map_x, map_y, INTER_NEAREST, BORDER_CONSTANT, INVALID)   source pixel (cvRound(map_x), cvRound(map_y)), -2.0 outside
+ *   Convert::cullImage                only the sampled pixels are ever computed
+ * dvo_set_undistort_map takes the two CV_32FC1 maps ([height][width] each) exactly as cv::initUndistortRectifyMap produced them
+ * (Loader::createUndistortMap, loader.cpp:15-30); NULL, NULL selects the identity (getNormalizedImages only).  The bgr8 entry
+ * points need channels = 3 or 4; bgr8: [n_streams][height][width][channels] uint8. */
+int dvo_set_undistort_map(dvo_ctx* ctx, const float* map_x, const float* map_y);
+int dvo_frame_create_bgr8(dvo_ctx* ctx, int* slot, const uint8_t* bgr8, int channels);
 int dvo_frame_release(dvo_ctx* ctx, int slot);
 /* full_res != 0: arrays are input-sized and culled like the 6-arg Frame ctor (frame.hpp:91-106);
  * full_res == 0: arrays are finest-level sized (Frame::updateDepthSigmaAge, frame.cpp:47-54).
@@ -193,6 +204,10 @@ int dvo_vo_collect(dvo_ctx* ctx);
 int dvo_vo_push_gray8(dvo_ctx* ctx, const uint8_t* gray8, int invalid_code, const float* init_depth, const float* init_sigma,
                       float* T_out);
 int dvo_vo_submit_gray8(dvo_ctx* ctx, const uint8_t* gray8, int invalid_code, float* T_out);
+/* ... and from 8-bit BGR / BGRA frames through the undistortion map (see dvo_frame_create_bgr8).  The whole frame crosses PCIe
+ * (3 or 4 bytes per input pixel), so this form is for hosts that cannot spare the cores for cvtColor + remap. */
+int dvo_vo_push_bgr8(dvo_ctx* ctx, const uint8_t* bgr8, int channels, const float* init_depth, const float* init_sigma, float* T_out);
+int dvo_vo_submit_bgr8(dvo_ctx* ctx, const uint8_t* bgr8, int channels, float* T_out);
 /* Supply the relative pose (frame-from-keyframe twist, [n_streams][6]) the NEXT dvo_vo_push uses for
  * Frame::updateXi (frame.cpp:7-14) and mapping instead of its own tracking result; the tracker still
  * runs and its iterations stay readable through dvo_vo_last_log.  Used for teacher-forced parity
