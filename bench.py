@@ -399,10 +399,13 @@ def run_gpu_arm(args, rank, world, local_rank, dist):
                       max_keyframes=n_total + W_ + E + 4)
     dv.vo_reserve(n_total + W_ + E + 2)
     frame_bytes = S * H_IN * W_IN * 4
-    e2e_u8 = (args.e2e_input == "gray8")
-    esz = 1 if e2e_u8 else 4   # bytes per pixel of the end-to-end pass's host frames
+    e2e_bgr = (args.e2e_input == "bgr8")
+    e2e_u8 = (args.e2e_input == "gray8") or e2e_bgr
+    esz = 3 if e2e_bgr else 1 if e2e_u8 else 4   # bytes per pixel of the end-to-end pass's host frames
     host_frame_bytes = S * H_IN * W_IN * esz
     h2d_bytes = S * (H_IN >> CULLS) * W_IN * esz if (CULLS > 0 and H_IN % (1 << CULLS) == 0) else host_frame_bytes  # stage_gray_to()
+    if e2e_bgr:
+        h2d_bytes = host_frame_bytes   # the undistortion gather can touch any source pixel: whole BGR frames cross PCIe
     # global sequence ids are sharded id mod world (dvo_b200/shard.py); a rank's S local streams are ids
     # rank, rank + world, ... and the renderer seeds stream k of this context with seed0 + k: the bench uses the
     # contiguous relabelling 1000 + rank * S + k (any bijection of independent sequences gives the same workload)
@@ -427,10 +430,10 @@ def run_gpu_arm(args, rank, world, local_rank, dist):
             raise SystemExit("bench.py: pinned host allocation failed")
         dv.synth_render_dev(tmpd, None, e2e_first + i, seed0, TRANS_STEP, ROT_STEP_DEG)
         if e2e_u8:   # 8-bit camera frames: the rendered intensity quantised to 0..255 (what cv::imread + cvtColor deliver)
-            arr = np.ctypeslib.as_array(C.cast(hp, C.POINTER(C.c_uint8)), shape=(S, H_IN, W_IN))
+            arr = np.ctypeslib.as_array(C.cast(hp, C.POINTER(C.c_uint8)), shape=(S, H_IN, W_IN, 3) if e2e_bgr else (S, H_IN, W_IN))
             dv.copy_to_host(ftmp, tmpd)
             np.multiply(ftmp, 255.0, out=ftmp); np.rint(ftmp, out=ftmp); np.clip(ftmp, 0, 255, out=ftmp)
-            arr[...] = ftmp
+            arr[...] = ftmp[..., None] if e2e_bgr else ftmp   # B = G = R: cvtColor returns the same code
         else:
             arr = np.ctypeslib.as_array(C.cast(hp, C.POINTER(C.c_float)), shape=(S, H_IN, W_IN))
             dv.copy_to_host(arr, tmpd)
@@ -510,7 +513,9 @@ def run_gpu_arm(args, rank, world, local_rank, dist):
     Ts = [np.ctypeslib.as_array(C.cast(tp, C.POINTER(C.c_float)), shape=(S, 4, 4)) for tp in tps]
     pose_sum = 0.0
     def submit(i):
-        if e2e_u8:
+        if e2e_bgr:
+            dv._ck(lib.dvo_vo_submit_bgr8(dv.ctx, host[i][0], 3, tps[i & 1]))
+        elif e2e_u8:
             dv._ck(lib.dvo_vo_submit_gray8(dv.ctx, host[i][0], -1, tps[i & 1]))
         else:
             dv._ck(lib.dvo_vo_submit(dv.ctx, host[i][0], tps[i & 1]))
@@ -561,9 +566,10 @@ def run_gpu_arm(args, rank, world, local_rank, dist):
                       "so only those rows cross PCIe (cudaMemcpy2DAsync); 2 frames in flight (%s/dvo_vo_collect); these are frames %d.. of the "
                       "sequences, where the epipolar searches are longer than over the first %d frames `value` averages "
                       "(kernel_ms_per_step_same_frames = device time of the same part of the sequence)"
-                      % ("8-bit gray" if e2e_u8 else "float32", host_frame_bytes,
+                      % ("8-bit BGR (cvtColor + remap on the device too, whole frames cross PCIe)" if e2e_bgr else "8-bit gray" if e2e_u8 else "float32",
+                         host_frame_bytes,
                          ", converted on the device like Loader's convertTo(CV_32FC1, 1.0/255.0) (loader.cpp:61)" if e2e_u8 else "",
-                         "dvo_vo_submit_gray8" if e2e_u8 else "dvo_vo_submit", e2e_first + W_, n_total)),
+                         "dvo_vo_submit_bgr8" if e2e_bgr else "dvo_vo_submit_gray8" if e2e_u8 else "dvo_vo_submit", e2e_first + W_, n_total)),
         gpu_launches=int(l1 - l0), clocks=clocks,
         roofline=dict(kernel=top["kernel"], bound="hbm", achieved=top["achieved_gbs"], peak=peak, unit="GB/s", frac=top["frac"],
                       traffic=traffic, traffic_source=traffic_src, peak_source=peak_src, launches=top["launches"], avg_launch_us=top["avg_launch_us"],
@@ -583,7 +589,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--streams", type=int, default=256, help="independent sequences per GPU")
     ap.add_argument("--e2e-steps", type=int, default=12)
-    ap.add_argument("--e2e-input", default="gray8", choices=["gray8", "float32"],
+    ap.add_argument("--e2e-input", default="gray8", choices=["gray8", "float32", "bgr8"],
                     help="host frames of the end-to-end pass: 8-bit gray (camera / cv::imread form, converted on the device) or float32")
     ap.add_argument("--roofline-steps", type=int, default=4)
     ap.add_argument("--resident-frames", type=int, default=48, help="distinct frames per stream kept in HBM")
