@@ -48,6 +48,13 @@ struct dvo_ctx {
     int nblk_top = 0;
     int* d_winner = nullptr;
     int* d_remap = nullptr;        // [n_top] source pixel of every finest-level pixel (bgr8 ingest), built on first use
+    // Kinect ingest (dvo_kinect_configure)
+    bool kin_ready = false;
+    KinectDev kin{};
+    int* d_kin_cidx = nullptr;     // [color_h][color_w]
+    int* d_kin_didx = nullptr;     // [n_top]
+    uint8_t* d_kin_color = nullptr; // [S][color_h][color_w][channels]
+    uint16_t* d_kin_depth = nullptr; // [S][in_h][in_w]
     float* d_tmp = nullptr;
     uint32_t* d_rng = nullptr;
     float* d_stage_in = nullptr;   // [S][in_h][in_w]
@@ -293,7 +300,8 @@ extern "C" void dvo_destroy(dvo_ctx* ctx)
     for (auto& s : ctx->slots) if (s.base) cudaFree(s.base);
     cudaFree(ctx->d_slots); cudaFree(ctx->d_ts); cudaFree(ctx->d_ms); cudaFree(ctx->d_vo); cudaFree(ctx->d_hist);
     cudaFree(ctx->d_tab); cudaFree(ctx->d_partials); cudaFree(ctx->d_log); cudaFree(ctx->d_flags); cudaFree(ctx->d_mask);
-    cudaFree(ctx->d_blockcnt); cudaFree(ctx->d_winner); cudaFree(ctx->d_remap); cudaFree(ctx->d_tmp); cudaFree(ctx->d_rng); cudaFree(ctx->d_stage_in);
+    cudaFree(ctx->d_blockcnt); cudaFree(ctx->d_winner); cudaFree(ctx->d_remap);
+    cudaFree(ctx->d_kin_cidx); cudaFree(ctx->d_kin_didx); cudaFree(ctx->d_kin_color); cudaFree(ctx->d_kin_depth); cudaFree(ctx->d_tmp); cudaFree(ctx->d_rng); cudaFree(ctx->d_stage_in);
     for (int k = 0; k < 3; k++) cudaFree(ctx->d_stage[k]);
     cudaFree(ctx->d_small); cudaFree(ctx->d_ismall); cudaFree(ctx->d_forced);
     if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
@@ -501,6 +509,68 @@ extern "C" int dvo_frame_create_bgr8(dvo_ctx* ctx, int* slot, const uint8_t* bgr
     rc = find_free_slot(ctx, slot);
     if (rc) return rc;
     return build_frame(ctx, *slot, ctx->d_stage_in, false, 2, channels);
+}
+
+// ---- Kinect ingest: KinectLoader::getMappedImages + mapDepthtoGray + Frame(gray, depth, sigma, ...) ------------------
+extern "C" int dvo_kinect_configure(dvo_ctx* ctx, const dvo_kinect_params* kp, const float* rgb_map_x, const float* rgb_map_y,
+                                    const float* depth_map_x, const float* depth_map_y)
+{
+    const Consts& c = ctx->c;
+    ARG(kp && rgb_map_x && rgb_map_y && depth_map_x && depth_map_y, "null argument");
+    ARG(kp->color_width > 0 && kp->color_height > 0 && kp->color_width < 32768 && kp->color_height < 32768 &&
+        (kp->channels == 3 || kp->channels == 4), "bad colour image geometry");
+    const LevelGeom& gt = c.lv[c.L - 1];
+    const size_t cn = (size_t)kp->color_width * kp->color_height;
+    cudaFree(ctx->d_kin_cidx); cudaFree(ctx->d_kin_didx); cudaFree(ctx->d_kin_color); cudaFree(ctx->d_kin_depth);
+    ctx->d_kin_cidx = ctx->d_kin_didx = nullptr; ctx->d_kin_color = nullptr; ctx->d_kin_depth = nullptr;
+    ctx->kin_ready = false;
+    CK(cudaMalloc(&ctx->d_kin_cidx, sizeof(int) * cn));
+    CK(cudaMalloc(&ctx->d_kin_didx, sizeof(int) * (size_t)gt.n));
+    CK(cudaMalloc(&ctx->d_kin_color, (size_t)c.S * cn * kp->channels));
+    CK(cudaMalloc(&ctx->d_kin_depth, sizeof(uint16_t) * (size_t)c.S * c.in_w * c.in_h));
+    float *mx = nullptr, *my = nullptr; // temporary device copies of the colour maps
+    CK(cudaMalloc(&mx, sizeof(float) * cn));
+    CK(cudaMalloc(&my, sizeof(float) * cn));
+    CK(cudaMemcpyAsync(mx, rgb_map_x, sizeof(float) * cn, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(my, rgb_map_y, sizeof(float) * cn, cudaMemcpyHostToDevice, ctx->stream));
+    k_build_remap_full<<<cdiv((int)cn, 256), 256, 0, ctx->stream>>>(mx, my, kp->color_width, kp->color_height, ctx->d_kin_cidx);
+    KCHECK();
+    // depth maps: only the pixels Convert::cullImage keeps (the generic builder, into the Kinect's own index)
+    const size_t db = sizeof(float) * (size_t)c.in_w * c.in_h;
+    CK(cudaMemcpyAsync(ctx->d_stage[0], depth_map_x, db, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->d_stage[1], depth_map_y, db, cudaMemcpyHostToDevice, ctx->stream));
+    k_build_remap<<<cdiv(gt.n, 256), 256, 0, ctx->stream>>>(c, ctx->d_stage[0], ctx->d_stage[1], ctx->d_kin_didx);
+    KCHECK();
+    CK(cudaStreamSynchronize(ctx->stream));
+    cudaFree(mx); cudaFree(my);
+    KinectDev& k = ctx->kin;
+    k.cw = kp->color_width; k.ch = kp->color_height; k.channels = kp->channels;
+    k.fx = kp->rgb_K[0]; k.fy = kp->rgb_K[4]; k.cx = kp->rgb_K[2]; k.cy = kp->rgb_K[5];
+    k.dfx = ctx->P.K[0]; k.dfy = ctx->P.K[4]; k.dcx = ctx->P.K[2]; k.dcy = ctx->P.K[5];
+    for (int r = 0; r < 3; r++)
+        for (int q = 0; q < 4; q++) k.T[r * 4 + q] = kp->invT[r * 4 + q];
+    k.cidx = ctx->d_kin_cidx; k.didx = ctx->d_kin_didx;
+    ctx->kin_ready = true;
+    return DVO_OK;
+}
+
+extern "C" int dvo_frame_create_kinect(dvo_ctx* ctx, int* slot, const uint8_t* bgr8, const uint16_t* depth16)
+{
+    const Consts& c = ctx->c;
+    ARG(slot && bgr8 && depth16, "null argument");
+    if (!ctx->kin_ready) {
+        ctx->err = "dvo_frame_create_kinect: call dvo_kinect_configure first";
+        return DVO_ERR_STATE;
+    }
+    const KinectDev& k = ctx->kin;
+    CK(cudaMemcpyAsync(ctx->d_kin_color, bgr8, (size_t)c.S * k.cw * k.ch * k.channels, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->d_kin_depth, depth16, sizeof(uint16_t) * (size_t)c.S * c.in_w * c.in_h, cudaMemcpyHostToDevice, ctx->stream));
+    int rc = find_free_slot(ctx, slot);
+    if (rc) return rc;
+    const LevelGeom& gt = c.lv[c.L - 1];
+    k_kinect_frame<<<dim3(cdiv(gt.n, 256), c.S), 256, 0, ctx->stream>>>(c, k, ctx->d_kin_color, ctx->d_kin_depth, ctx->slots[*slot].dev);
+    KCHECK();
+    return DVO_OK;
 }
 
 extern "C" int dvo_frame_release(dvo_ctx* ctx, int slot)

@@ -125,6 +125,79 @@ __global__ void __launch_bounds__(256) k_cull_bgr8(const __grid_constant__ Const
     slot.gray[(size_t)s * g.n + i] = v;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Kinect ingest: KinectLoader::getMappedImages + Transform::mapDepthtoGray + Frame(gray, depth, sigma, K, ...).
+// ---------------------------------------------------------------------------------------------
+struct KinectDev {
+    int cw, ch, channels;   // colour image
+    float fx, fy, cx, cy;   // colour intrinsics
+    float dfx, dfy, dcx, dcy; // depth intrinsics at full resolution (dvo_params.K)
+    float T[12];            // invT rows [R | t]
+    const int* cidx;        // [ch][cw] source pixel of every UNDISTORTED colour pixel (cv::remap NEAREST), -1 = border (INVALID)
+    const int* didx;        // [n_top] source pixel of every sampled undistorted depth pixel, -1 = border (depth 0)
+};
+// full-resolution variant of k_build_remap (the registration's taps land anywhere in the colour image)   grid = ceil(w h / 256)
+__global__ void __launch_bounds__(256) k_build_remap_full(const float* __restrict__ map_x, const float* __restrict__ map_y, int w, int h,
+                                                          int* __restrict__ idx)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= w * h) return;
+    const int sx = max(-32768, min(32767, round_x86(map_x[i])));
+    const int sy = max(-32768, min(32767, round_x86(map_y[i])));
+    idx[i] = (sx >= 0 && sx < w && sy >= 0 && sy < h) ? sy * w + sx : -1;
+}
+// pixel (x, y) of the undistorted, normalised colour image (loader.cpp:110-113 applied to loader.cpp:143-144)
+__device__ __forceinline__ float kinect_gray_at(const KinectDev& k, const uint8_t* __restrict__ img, int x, int y)
+{
+    const int si = __ldg(k.cidx + y * k.cw + x);
+    if (si < 0) return DVO_INV;
+    const uint8_t* __restrict__ p = img + (size_t)si * k.channels;
+    const int code = (__ldg(p) * 3735 + __ldg(p + 1) * 19235 + __ldg(p + 2) * 9798 + (1 << 14)) >> 15;
+    return __fmul_rn((float)code, (float)(1.0 / 255.0));
+}
+// grid = (ceil(n_top/256), S)
+__global__ void __launch_bounds__(256) k_kinect_frame(const __grid_constant__ Consts c, const KinectDev k, const uint8_t* __restrict__ bgr,
+                                                      const uint16_t* __restrict__ depth16, SlotDev slot)
+{
+    const int s = blockIdx.y;
+    const LevelGeom g = c.lv[c.L - 1];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= g.n) return;
+    const int y = i / g.w, x = i - y * g.w;
+    const int X = x << c.culls, Y = y << c.culls; // the pixel of the full depth image that Convert::cullImage keeps
+    const int di = __ldg(k.didx + i);
+    const float depth = di >= 0 ? __fmul_rn((float)depth16[(size_t)s * c.in_w * c.in_h + di], (float)(1.0 / 5000.0)) : 0.f; // loader.cpp:145,113
+    float gray = DVO_INV, sigma = 1.0f; // transform.cpp:60-61
+    if (!(fabsf(depth) < 1e-6f)) {      // math::isEpsilon, transform.cpp:67
+        // backProject with the FULL-resolution depth intrinsics (transform.cpp:25-28): registration happens before Frame culls
+        const float Xc = depth * ((float)X - k.dcx) / k.dfx;
+        const float Yc = depth * ((float)Y - k.dcy) / k.dfy;
+        const float tx = (k.T[0] * Xc + k.T[1] * Yc + k.T[2] * depth) + k.T[3];   // transform.cpp:7-12
+        const float ty = (k.T[4] * Xc + k.T[5] * Yc + k.T[6] * depth) + k.T[7];
+        const float tz = (k.T[8] * Xc + k.T[9] * Yc + k.T[10] * depth) + k.T[11];
+        const float px = tx * k.fx / tz + k.cx, py = ty * k.fy / tz + k.cy;        // transform.cpp:30-33
+        // Convert::getSubpixel (convert.cpp:127-177) on the undistorted colour image
+        const uint8_t* __restrict__ img = bgr + (size_t)s * k.cw * k.ch * k.channels;
+        const int x0 = trunc_x86(px), y0 = trunc_x86(py);
+        if (in_range(x0, y0, k.cw, k.ch)) {
+            const float hh = px - (float)x0, v = py - (float)y0;
+            float t[4];
+            t[0] = t[1] = t[2] = t[3] = kinect_gray_at(k, img, x0, y0);
+            const bool xin = x0 + 1 < k.cw, yin = y0 + 1 < k.ch;
+            if (xin) t[1] = kinect_gray_at(k, img, x0 + 1, y0);
+            if (yin) t[2] = kinect_gray_at(k, img, x0, y0 + 1);
+            if (xin && yin) t[3] = kinect_gray_at(k, img, x0 + 1, y0 + 1);
+            if (repair_taps(t)) gray = bilerp(t[0], t[1], t[2], t[3], hh, v);
+        }
+        sigma = 0.1f; // transform.cpp:73
+    }
+    // Frame(gray, depth, sigma, K, levels, culls): every plane point-sampled through Convert::getPixel (frame.hpp:91-106)
+    const bool culled = c.culls > 0;
+    slot.gray[(size_t)s * g.n + i] = culled ? get_pixel_value(gray) : gray;
+    slot.ds[(size_t)s * g.n + i] = make_float2(culled ? get_pixel_value(depth) : depth, sigma);
+    slot.age[(size_t)s * g.n + i] = 0.f;
+}
+
 // depth / sigma / age upload (Frame 6-arg ctor frame.hpp:91-106, updateDepthSigmaAge frame.cpp:47-54).
 // src arrays are [S][sh][sw]; shift = culls when full-res, 0 otherwise.  grid = (ceil(n_top/256), S)
 __global__ void __launch_bounds__(256) k_set_top(const __grid_constant__ Consts c, const SlotDev* __restrict__ slots, int fixed,

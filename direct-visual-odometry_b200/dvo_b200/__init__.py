@@ -33,6 +33,10 @@ class DvoParams(C.Structure):
     ]
 
 
+class DvoKinectParams(C.Structure):
+    _fields_ = [("color_width", C.c_int), ("color_height", C.c_int), ("channels", C.c_int), ("rgb_K", C.c_float * 9), ("invT", C.c_float * 16)]
+
+
 class DvoIterLog(C.Structure):
     _fields_ = [("level", C.c_int), ("iteration", C.c_int), ("valid_pixels", C.c_int), ("residual", C.c_float),
                 ("update", C.c_float * 6), ("xi_after", C.c_float * 6)]
@@ -49,6 +53,7 @@ EXPORTS = [
     "dvo_map_update_points", "dvo_se3_exp", "dvo_se3_log", "dvo_se3_concatenate", "dvo_vo_submit", "dvo_vo_collect",
     "dvo_frame_create_gray8", "dvo_vo_push_gray8", "dvo_vo_submit_gray8",
     "dvo_set_undistort_map", "dvo_frame_create_bgr8", "dvo_vo_push_bgr8", "dvo_vo_submit_bgr8",
+    "dvo_kinect_configure", "dvo_frame_create_kinect",
 ]
 
 
@@ -123,6 +128,8 @@ def load_library(path=None):
     lib.dvo_vo_push_gray8.argtypes = [C.c_void_p, C.c_void_p, C.c_int, F32P, F32P, F32P]
     lib.dvo_vo_submit_gray8.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
     lib.dvo_set_undistort_map.argtypes = [C.c_void_p, F32P, F32P]
+    lib.dvo_kinect_configure.argtypes = [C.c_void_p, C.POINTER(DvoKinectParams), F32P, F32P, F32P, F32P]
+    lib.dvo_frame_create_kinect.argtypes = [C.c_void_p, I32P, C.c_void_p, C.c_void_p]
     lib.dvo_frame_create_bgr8.argtypes = [C.c_void_p, I32P, C.c_void_p, C.c_int]
     lib.dvo_vo_push_bgr8.argtypes = [C.c_void_p, C.c_void_p, C.c_int, F32P, F32P, F32P]
     lib.dvo_vo_submit_bgr8.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
@@ -259,6 +266,32 @@ class Dvo:
         if not want_pose:
             self._ck(self.lib.dvo_sync(self.ctx))
         return T
+
+    def kinect_configure(self, color_size, channels, rgb_K, invT, rgb_maps, depth_maps):
+        """KinectLoader::createUndistortMap's four CV_32FC1 maps + the calibration that Transform::mapDepthtoGray uses."""
+        kp = DvoKinectParams()
+        kp.color_width, kp.color_height = int(color_size[0]), int(color_size[1]); kp.channels = int(channels)
+        kp.rgb_K[:] = [float(v) for v in np.asarray(rgb_K, np.float32).reshape(9)]
+        kp.invT[:] = [float(v) for v in np.asarray(invT, np.float32).reshape(16)]
+        m = [_f32(a) for a in (rgb_maps[0], rgb_maps[1], depth_maps[0], depth_maps[1])]
+        assert m[0].shape == m[1].shape == (kp.color_height, kp.color_width)
+        assert m[2].shape == m[3].shape == (self.params.height, self.params.width)
+        self._ck(self.lib.dvo_kinect_configure(self.ctx, C.byref(kp), _p(m[0]), _p(m[1]), _p(m[2]), _p(m[3])))
+        self._kinect = (kp.color_height, kp.color_width, kp.channels)
+
+    def frame_create_kinect(self, bgr8, depth16):
+        """Frame from one raw Kinect pair: getMappedImages + mapDepthtoGray + Frame(gray, depth, sigma, K, levels, culls)."""
+        ch_, cw_, cc = self._kinect
+        b = np.ascontiguousarray(bgr8, dtype=np.uint8); d = np.ascontiguousarray(depth16, dtype=np.uint16)
+        if b.ndim == 3:
+            b = b[None]
+        if d.ndim == 2:
+            d = d[None]
+        assert b.shape == (self.S, ch_, cw_, cc) and d.shape == (self.S, self.params.height, self.params.width), (b.shape, d.shape)
+        slot = C.c_int(-1)
+        self._ck(self.lib.dvo_frame_create_kinect(self.ctx, C.byref(slot), b.ctypes.data_as(C.c_void_p), d.ctypes.data_as(C.c_void_p)))
+        self._ck(self.lib.dvo_sync(self.ctx))
+        return slot.value
 
     def frame_release(self, slot):
         self._ck(self.lib.dvo_frame_release(self.ctx, slot))

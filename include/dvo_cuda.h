@@ -127,6 +127,25 @@ int dvo_frame_download(dvo_ctx* ctx, int slot, int level, int kind, float* out);
 int dvo_frame_set_xi(dvo_ctx* ctx, int slot, const float* xi /*[n_streams][6]*/, const float* rel_xi /*nullable*/);
 int dvo_frame_get_xi(dvo_ctx* ctx, int slot, float* xi, float* rel_xi /*nullable*/);
 
+/* ---- Kinect ingest: Core::KinectLoader::getMappedImages (src/core/loader.cpp:90-147) + Transform::mapDepthtoGray
+ * (src/core/transform.cpp:53-78) + the 6-argument Frame ctor (include/system/frame.hpp:91-106), on the device -------------------
+ * The context's width x height is the DEPTH camera's image (512 x 424 for Kinect v2) and dvo_params.K its intrinsics.  Per
+ * finest-level pixel:  depth = remap_nearest(depth16 * (float)(1.0/5000.0), depth maps, border 0);  |depth| < 1e-6 -> gray INVALID,
+ * sigma 1.0;  otherwise  x_c = invT * backProject(depth_K, x, depth),  gray = Convert::getSubpixel(undistorted colour image,
+ * project(rgb_K, x_c)) with sigma 0.1, where the undistorted colour image is never materialised: each of the four taps goes
+ * through the colour remap index to the 8-bit BGR(A) pixel (cvtColor + convertTo as in dvo_frame_create_bgr8).
+ * maps: CV_32FC1 as cv::initUndistortRectifyMap returns them (KinectLoader::createUndistortMap, loader.cpp:77-88); invT: row-major
+ * 4x4 (Calibration::ExtrinsicParams::invT, params_struct.hpp:38-46). */
+typedef struct dvo_kinect_params {
+    int color_width, color_height, channels; /* 1920, 1080, 4 for the bundled data */
+    float rgb_K[9];                          /* colour intrinsics */
+    float invT[16];                          /* depth camera -> colour camera */
+} dvo_kinect_params;
+int dvo_kinect_configure(dvo_ctx* ctx, const dvo_kinect_params* kp, const float* rgb_map_x, const float* rgb_map_y,
+                         const float* depth_map_x, const float* depth_map_y);
+/* bgr8: [n_streams][color_height][color_width][channels] uint8; depth16: [n_streams][height][width] uint16 (1/5000 m). */
+int dvo_frame_create_kinect(dvo_ctx* ctx, int* slot, const uint8_t* bgr8, const uint16_t* depth16);
+
 /* ---- tracking ------------------------------------------------------------------------------- */
 /* Transform::warpImage(xi, gray, depth, K) (src/core/transform.cpp:35-51) of ref_slot at `level`.
  * xi: [n_streams][6]; out: [n_streams][h][w]. */
