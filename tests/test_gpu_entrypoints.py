@@ -115,3 +115,32 @@ def test_submit_collect_equals_push(seq160):
         assert a.tobytes() == b.tobytes()
     for a, b in zip(ma, mb):
         assert a.tobytes() == b.tobytes()
+
+
+def test_error_behaviour_of_the_ingest_entry_points():
+    """Misuse returns a negative dvo_status with a message (the reference would abort() or read out of bounds): nothing is computed."""
+    import ctypes as C
+    import dvo_b200
+    dv = make_dvo(width=64, height=48, levels=2, culls=1)
+    lib = dv.lib
+    slot = C.c_int(-1)
+    z8 = np.zeros((1, 48, 64, 4), np.uint8)
+    # Kinect frame before dvo_kinect_configure: call-sequence error
+    rc = lib.dvo_frame_create_kinect(dv.ctx, C.byref(slot), z8.ctypes.data_as(C.c_void_p), z8.ctypes.data_as(C.c_void_p))
+    assert rc == -6 and b"dvo_kinect_configure" in lib.dvo_last_error(dv.ctx)
+    # channels other than 3 / 4, invalid_code outside -1..255, one map without the other
+    assert lib.dvo_frame_create_bgr8(dv.ctx, C.byref(slot), z8.ctypes.data_as(C.c_void_p), 2) < 0
+    assert lib.dvo_frame_create_gray8(dv.ctx, C.byref(slot), z8.ctypes.data_as(C.c_void_p), 256) < 0
+    m = np.zeros((48, 64), np.float32)
+    assert lib.dvo_set_undistort_map(dv.ctx, m.ctypes.data_as(C.POINTER(C.c_float)), None) < 0
+    # three frames in flight
+    with pytest.raises(dvo_b200.DvoError):
+        hp = lib.dvo_host_alloc(64 * 48 * 4)
+        try:
+            dv._ck(lib.dvo_vo_submit(dv.ctx, hp, None)); dv._ck(lib.dvo_vo_submit(dv.ctx, hp, None)); dv._ck(lib.dvo_vo_submit(dv.ctx, hp, None))
+        finally:
+            while lib.dvo_vo_collect(dv.ctx) == 0:
+                pass
+            lib.dvo_host_free(hp)
+    assert slot.value == -1   # no slot was ever handed out
+    dv.close()
