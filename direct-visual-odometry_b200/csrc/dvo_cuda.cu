@@ -740,8 +740,8 @@ extern "C" int dvo_gn_timing(dvo_ctx* ctx, int enable, float* total_ms, int* lau
     if (rc) return rc;
     if (total_ms) *total_ms = 0;
     if (launches) *launches = 0;
-    for (int k = 0; k < n; k++)
-        if (!strcmp(kt[k].name, "k_track")) {
+    for (int k = 0; k < n && k < K_COUNT; k++)
+        if (!strncmp(kt[k].name, "k_track", sizeof(kt[k].name))) {
             if (total_ms) *total_ms = kt[k].total_ms;
             if (launches) *launches = kt[k].launches;
         }
