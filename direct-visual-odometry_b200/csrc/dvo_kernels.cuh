@@ -501,6 +501,11 @@ struct TrackCtl { // per-CTA copy of the stream's iteration state
     int level, iter, done;
     float T[12];  // exp(-xi): what the pixels are warped with
     float Tp[16]; // exp(xi): left operand of the next se3::concatenate (leader CTA only)
+    // the leader's copy of what the tail reads every iteration (TrackState in global memory is written, never read back)
+    float xi[6];
+    int n_total, px_total, mode;
+    double stop_update;
+    float stop_residual;
 };
 
 #ifdef DVO_TRK_PROF
@@ -535,9 +540,9 @@ __device__ __noinline__ void gn_tail(const Consts& c, const TrackArgs& a, TrackS
     }
     TAIL_PROF(5, tq);
     float xi[6], xin[6];
-    for (int q = 0; q < 6; q++) xi[q] = st->xi[q];
-    const int n_total = st->n_total;
-    const bool advance_pose = (st->mode == 0);
+    for (int q = 0; q < 6; q++) xi[q] = ctl->xi[q];
+    const int n_total = ctl->n_total;
+    const bool advance_pose = (ctl->mode == 0);
     bool moved = false;
     if (advance_pose) {
         se3_concatenate_T(ctl->Tp, upd, xin); // tracker.cpp:46; ctl->Tp = exp(xi) from the previous tail
@@ -554,15 +559,16 @@ __device__ __noinline__ void gn_tail(const Consts& c, const TrackArgs& a, TrackS
         L->level = level; L->iteration = ctl->iter; L->valid_pixels = valid; L->residual = residual;
         for (int q = 0; q < 6; q++) { L->update[q] = upd[q]; L->xi_after[q] = xi[q]; }
     }
-    st->n_total = n_total + 1;
-    st->px_total += g.n;
+    ctl->n_total = n_total + 1;
+    ctl->px_total += g.n;
+    st->n_total = ctl->n_total;
+    st->px_total = ctl->px_total;
     if (!advance_pose) {
         ctl->done = 1;
     } else {
-        for (int q = 0; q < 6; q++) st->xi[q] = xi[q];
-        if (moved) se3_exp(xi, ctl->Tp, ctl->T); // stuff.update(xi): the next iteration warps with exp(-xi)
+        for (int q = 0; q < 6; q++) { st->xi[q] = xi[q]; ctl->xi[q] = xi[q]; }
         // stop rules, tracker.cpp:68-70 (time budget never reached)
-        const bool stop = (norm_n(upd, 6) < st->stop_update) || (residual < st->stop_residual);
+        const bool stop = (norm_n(upd, 6) < ctl->stop_update) || (residual < ctl->stop_residual);
         int iter = ctl->iter + 1;
         if (stop || iter >= c.max_iter) {
             iter = 0;
@@ -570,6 +576,8 @@ __device__ __noinline__ void gn_tail(const Consts& c, const TrackArgs& a, TrackS
             if (ctl->level >= c.L) ctl->done = 1;
         }
         ctl->iter = iter;
+        // stuff.update(xi): the next iteration warps with exp(-xi) - not needed after the last iteration of the last level
+        if (moved && !ctl->done) se3_exp(xi, ctl->Tp, ctl->T);
     }
     // publish for the other CTAs of the stream and for the host
     st->level = ctl->level; st->iter = ctl->iter; st->done = ctl->done;
@@ -690,6 +698,8 @@ __global__ void __launch_bounds__(TRK_THREADS, TRK_MINB) k_track(const __grid_co
         for (int q = 0; q < 6; q++) xi[q] = a.xi0 ? a.xi0[6 * s + q] : 0.f;
         se3_exp(xi, ctl.Tp, ctl.T);
         ctl.level = a.level0; ctl.iter = 0; ctl.done = done;
+        for (int q = 0; q < 6; q++) ctl.xi[q] = xi[q];
+        ctl.n_total = 0; ctl.px_total = 0; ctl.mode = a.mode; ctl.stop_update = a.stop_update; ctl.stop_residual = a.stop_residual;
         s_gen0 = (B > 1) ? ld_volatile_u32(&st->gen) : 0u;
         if (leader) {
             for (int q = 0; q < 6; q++) st->xi[q] = xi[q];
