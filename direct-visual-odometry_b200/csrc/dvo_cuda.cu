@@ -625,6 +625,122 @@ extern "C" int dvo_frame_download(dvo_ctx* ctx, int slot, int level, int kind, f
     return DVO_OK;
 }
 
+extern "C" int dvo_visualize(dvo_ctx* ctx, int slot, int level, int kind, uint8_t* bgr_out)
+{
+    int rc = check_slot(ctx, slot);
+    if (rc) return rc;
+    const Consts& c = ctx->c;
+    ARG(level >= 0 && level < c.L && bgr_out, "bad level");
+    ARG(kind >= DVO_VIS_GRAY && kind <= DVO_VIS_AGE, "bad visualisation kind");
+    ARG(kind != DVO_VIS_AGE || level == c.L - 1, "age exists on the finest level only");
+    const LevelGeom& g = c.lv[level];
+    uint8_t* d_out = reinterpret_cast<uint8_t*>(ctx->d_stage[0]); // 3 B per pixel of a level fit the 4 B per input pixel staged there
+    dim3 grid(cdiv(g.n, 256), c.S);
+    k_visualize<<<grid, 256, 0, ctx->stream>>>(c, ctx->slots[slot].dev, level, kind, d_out);
+    KCHECK();
+    CK(cudaMemcpyAsync(bgr_out, d_out, (size_t)3 * c.S * g.n, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return DVO_OK;
+}
+
+// ---- headless outputs: host side ----------------------------------------------------------------
+extern "C" int dvo_inverse_pose(const float T[16], float out[16])
+{
+    if (!T || !out) return DVO_ERR_ARG;
+    float r[16] = {0};
+    for (int i = 0; i < 3; i++) {
+        for (int j = 0; j < 3; j++) r[i * 4 + j] = T[j * 4 + i];
+        r[i * 4 + 3] = -T[i * 4 + 3];
+    }
+    memcpy(out, r, sizeof(r));
+    return DVO_OK;
+}
+
+extern "C" int dvo_write_trajectory_csv(const char* path, const float* T, int n, int first_frame, int append)
+{
+    if (!path || (!T && n > 0) || n < 0) return DVO_ERR_ARG;
+    FILE* f = fopen(path, append ? "a" : "w");
+    if (!f) return DVO_ERR_ARG;
+    for (int k = 0; k < n; k++) {
+        fprintf(f, "%d", first_frame + k);
+        for (int q = 0; q < 16; q++) fprintf(f, ",%.9g", (double)T[(size_t)k * 16 + q]);
+        fputc('\n', f);
+    }
+    return fclose(f) == 0 ? DVO_OK : DVO_ERR_ARG;
+}
+
+namespace {
+struct PngOut {
+    FILE* f;
+    uint32_t crc_table[256];
+    PngOut(FILE* f_) : f(f_)
+    {
+        for (uint32_t n = 0; n < 256; n++) {
+            uint32_t c = n;
+            for (int k = 0; k < 8; k++) c = (c & 1) ? 0xedb88320u ^ (c >> 1) : c >> 1;
+            crc_table[n] = c;
+        }
+    }
+    uint32_t crc(uint32_t c, const uint8_t* p, size_t n) const
+    {
+        for (size_t i = 0; i < n; i++) c = crc_table[(c ^ p[i]) & 0xff] ^ (c >> 8);
+        return c;
+    }
+    static void be32(uint8_t* p, uint32_t v) { p[0] = (uint8_t)(v >> 24); p[1] = (uint8_t)(v >> 16); p[2] = (uint8_t)(v >> 8); p[3] = (uint8_t)v; }
+    bool chunk(const char type[4], const std::vector<uint8_t>& data) const
+    {
+        uint8_t hd[8], tl[4];
+        be32(hd, (uint32_t)data.size());
+        memcpy(hd + 4, type, 4);
+        uint32_t c = crc(0xffffffffu, hd + 4, 4);
+        c = crc(c, data.data(), data.size()) ^ 0xffffffffu;
+        be32(tl, c);
+        return fwrite(hd, 1, 8, f) == 8 && (data.empty() || fwrite(data.data(), 1, data.size(), f) == data.size()) && fwrite(tl, 1, 4, f) == 4;
+    }
+};
+} // namespace
+
+extern "C" int dvo_write_png(const char* path, const uint8_t* bgr, int width, int height)
+{
+    if (!path || !bgr || width <= 0 || height <= 0) return DVO_ERR_ARG;
+    // raw scanlines: filter byte 0 + RGB
+    const size_t row = 1 + (size_t)3 * width;
+    std::vector<uint8_t> raw(row * height);
+    for (int y = 0; y < height; y++) {
+        uint8_t* d = raw.data() + row * y;
+        *d++ = 0;
+        const uint8_t* s = bgr + (size_t)3 * width * y;
+        for (int x = 0; x < width; x++) { d[0] = s[2]; d[1] = s[1]; d[2] = s[0]; d += 3; s += 3; }
+    }
+    // zlib stream of stored blocks
+    std::vector<uint8_t> z;
+    z.reserve(raw.size() + raw.size() / 65535 * 5 + 16);
+    z.push_back(0x78); z.push_back(0x01);
+    uint32_t a = 1, b = 0;
+    for (size_t pos = 0; pos < raw.size();) {
+        const size_t n = raw.size() - pos < 65535 ? raw.size() - pos : 65535;
+        z.push_back(pos + n == raw.size() ? 1 : 0);
+        z.push_back((uint8_t)(n & 0xff)); z.push_back((uint8_t)(n >> 8));
+        z.push_back((uint8_t)(~n & 0xff)); z.push_back((uint8_t)((~n >> 8) & 0xff));
+        z.insert(z.end(), raw.begin() + pos, raw.begin() + pos + n);
+        for (size_t i = 0; i < n; i++) { a = (a + raw[pos + i]) % 65521u; b = (b + a) % 65521u; }
+        pos += n;
+    }
+    uint8_t ad[4];
+    PngOut::be32(ad, (b << 16) | a);
+    z.insert(z.end(), ad, ad + 4);
+    FILE* f = fopen(path, "wb");
+    if (!f) return DVO_ERR_ARG;
+    PngOut png(f);
+    static const uint8_t sig[8] = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
+    std::vector<uint8_t> ihdr(13);
+    PngOut::be32(ihdr.data(), (uint32_t)width); PngOut::be32(ihdr.data() + 4, (uint32_t)height);
+    ihdr[8] = 8; ihdr[9] = 2; ihdr[10] = 0; ihdr[11] = 0; ihdr[12] = 0; // 8-bit RGB, deflate, no filter, no interlace
+    bool ok = fwrite(sig, 1, 8, f) == 8 && png.chunk("IHDR", ihdr) && png.chunk("IDAT", z) && png.chunk("IEND", std::vector<uint8_t>());
+    ok = (fclose(f) == 0) && ok;
+    return ok ? DVO_OK : DVO_ERR_ARG;
+}
+
 extern "C" int dvo_frame_set_xi(dvo_ctx* ctx, int slot, const float* xi, const float* rel_xi)
 {
     int rc = check_slot(ctx, slot);

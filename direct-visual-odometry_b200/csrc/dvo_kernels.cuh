@@ -259,6 +259,98 @@ __global__ void __launch_bounds__(256) k_extract(const __grid_constant__ Consts 
     out[(size_t)s * g.n + i] = r;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Draw::visualize* (src/core/draw.cpp:7-100), headless: the BGR bytes cv::imshow would be handed.
+// OpenCV pieces restated (pinned against cv2 4.13, tests/golden/make_draw.py):
+//   convertTo(CV_8UC1, a, b) = saturate_cast<uchar>(cvRound(fma(v, a, b)));
+//   8-bit COLOR_HSV2BGR       = float HSV2RGB on (h * 6/180, s/255, v/255), fused 1 - s h, results * 255 truncated.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint8_t cv_convert_8u(float v, float a, float b)
+{
+    const int q = round_x86(__fmaf_rn(v, a, b));
+    return (uint8_t)(q < 0 ? 0 : q > 255 ? 255 : q);
+}
+__device__ __forceinline__ uint8_t uchar_cast(float v) { return (uint8_t)(trunc_x86(v) & 0xff); } // static_cast<unsigned char>(float) on x86
+__device__ __forceinline__ void cv_hsv2bgr_8u(uint8_t H, uint8_t S, uint8_t V, uint8_t* bgr)
+{
+    const float s = (float)S * (1.f / 255.f), v = (float)V * (1.f / 255.f);
+    float h = (float)H * (6.f / 180.f);
+    if (h >= 6.f) h -= 6.f;
+    int sector = (int)floorf(h);
+    h -= (float)sector;
+    if ((unsigned)sector >= 6u) { sector = 0; h = 0.f; }
+    const float t0 = v, t1 = v * (1.f - s), t2 = v * __fmaf_rn(-s, h, 1.f), t3 = v * __fmaf_rn(-s, 1.f - h, 1.f);
+    float b, g, r; // sector_data = {1,3,0},{1,0,2},{3,0,1},{0,2,1},{0,1,3},{2,1,0}
+    switch (sector) {
+    case 0: b = t1; g = t3; r = t0; break;
+    case 1: b = t1; g = t0; r = t2; break;
+    case 2: b = t3; g = t0; r = t1; break;
+    case 3: b = t0; g = t2; r = t1; break;
+    case 4: b = t0; g = t1; r = t3; break;
+    default: b = t2; g = t1; r = t0; break;
+    }
+    const float o[3] = {b, g, r};
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        const int q = (int)(o[k] * 255.f);
+        bgr[k] = (uint8_t)(q < 0 ? 0 : q > 255 ? 255 : q);
+    }
+}
+
+// kind: dvo_vis_kind.  grid = (ceil(n_l/256), S); out: [S][n_l][3]
+__global__ void __launch_bounds__(256) k_visualize(const __grid_constant__ Consts c, SlotDev slot, int l, int kind, uint8_t* __restrict__ out)
+{
+    const int s = blockIdx.y;
+    const LevelGeom g = c.lv[l];
+    const LevelView v = level_view(c, l);
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= g.n) return;
+    const int y = i / g.w, x = i - y * g.w;
+    const size_t nt = (size_t)c.lv[c.L - 1].n;
+    const size_t ti = (size_t)s * nt + top_index(v, x, y);
+    uint8_t p[3] = {0, 0, 0};
+    switch (kind) {
+    case DVO_VIS_GRAY: { // draw.cpp:7-19
+        const float t = level_value(v, slot.gray[ti]);
+        p[0] = p[1] = p[2] = cv_convert_8u(t, 255.f, 0.f);
+        if (is_invalid(t) || t != t) p[0] = 255;
+        break;
+    }
+    case DVO_VIS_DEPTH: case DVO_VIS_DEPTH_SIGMA: { // draw.cpp:32-67
+        const float2 d = slot.ds[ti];
+        const float t = level_value(v, d.x);
+        if (t < 1e-6f) break;
+        float hx = (t - 0.70f) * 70.0f;
+        hx = hx < 0.0f ? 0.0f : (180.0f < hx ? 180.0f : hx); // std::clamp
+        uint8_t vv = 255;
+        if (kind == DVO_VIS_DEPTH_SIGMA) {
+            const float sg = level_value(v, d.y);
+            vv = uchar_cast(-500 * (sg < 0.5f ? sg : 0.5f) + 255);
+        }
+        cv_hsv2bgr_8u(uchar_cast(hx), 255, vv, p);
+        break;
+    }
+    case DVO_VIS_DEPTH_RAW: { // draw.cpp:21-29
+        const float t = level_value(v, slot.ds[ti].x);
+        float q = t < 2.5f ? t : 2.5f;
+        q = q > 0.5f ? q : 0.5f;
+        p[0] = p[1] = p[2] = cv_convert_8u(q, 100.f, 0.f);
+        break;
+    }
+    case DVO_VIS_SIGMA: p[0] = p[1] = p[2] = cv_convert_8u(level_value(v, slot.ds[ti].y), -500.f, 255.f); break; // draw.cpp:69-75
+    case DVO_VIS_GRADX: case DVO_VIS_GRADY: { // draw.cpp:77-91
+        const float t = kind == DVO_VIS_GRADX ? grad_x_at(slot.gray + (size_t)s * nt, v, x, y) : grad_y_at(slot.gray + (size_t)s * nt, v, x, y);
+        if (is_invalid(t)) { p[0] = 255; break; }
+        p[1] = uchar_cast(255 * (t > 0.0f ? t : 0.0f));
+        p[2] = uchar_cast(-255 * (t < 0.0f ? t : 0.0f));
+        break;
+    }
+    default: p[0] = p[1] = p[2] = cv_convert_8u(slot.age[ti], 10.f, 0.f); break; // draw.cpp:94-100
+    }
+    uint8_t* o = out + ((size_t)s * g.n + i) * 3;
+    o[0] = p[0]; o[1] = p[1]; o[2] = p[2];
+}
+
 // =============================================================================================
 // Sampling of {gray, gradX, gradY} of one level at a warped point.  Convert::getSubpixel for the
 // gray channel (with the invalid-tap repair automaton) and Convert::getSubpixelFromDense for the two

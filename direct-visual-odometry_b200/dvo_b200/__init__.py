@@ -16,6 +16,7 @@ I32P = C.POINTER(C.c_int)
 U8P = C.POINTER(C.c_uint8)
 
 IMG = {"gray": 0, "depth": 1, "sigma": 2, "gradx": 3, "grady": 4, "age": 5}
+VIS = {"gray": 0, "depth": 1, "depth_sigma": 2, "depth_raw": 3, "sigma": 4, "gradx": 5, "grady": 6, "age": 7}  # dvo_vis_kind
 
 
 class DvoParams(C.Structure):
@@ -45,7 +46,7 @@ class DvoIterLog(C.Structure):
 EXPORTS = [
     "dvo_device_count", "dvo_set_device", "dvo_params_default", "dvo_create", "dvo_destroy", "dvo_last_error", "dvo_sync", "dvo_level_size", "dvo_level_K",
     "dvo_host_alloc", "dvo_host_free", "dvo_frame_create", "dvo_frame_create_dev", "dvo_frame_release",
-    "dvo_frame_set_depth", "dvo_frame_download", "dvo_frame_set_xi", "dvo_frame_get_xi", "dvo_warp_image",
+    "dvo_frame_set_depth", "dvo_frame_download", "dvo_visualize", "dvo_inverse_pose", "dvo_write_trajectory_csv", "dvo_write_png", "dvo_frame_set_xi", "dvo_frame_get_xi", "dvo_warp_image",
     "dvo_gn_step", "dvo_track", "dvo_map_propagate", "dvo_map_update", "dvo_map_regularize", "dvo_rng_position",
     "dvo_mask_compact", "dvo_vo_reset", "dvo_vo_reserve", "dvo_vo_force_pose", "dvo_vo_push", "dvo_vo_push_dev", "dvo_vo_state", "dvo_vo_ref_slot",
     "dvo_vo_last_slot", "dvo_vo_last_log", "dvo_vo_counters", "dvo_vo_error", "dvo_synth_render_dev", "dvo_dev_alloc", "dvo_dev_free",
@@ -83,6 +84,10 @@ def load_library(path=None):
     lib.dvo_frame_release.argtypes = [C.c_void_p, C.c_int]
     lib.dvo_frame_set_depth.argtypes = [C.c_void_p, C.c_int, F32P, F32P, F32P, C.c_int]
     lib.dvo_frame_download.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, F32P]
+    lib.dvo_visualize.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
+    lib.dvo_inverse_pose.argtypes = [F32P, F32P]
+    lib.dvo_write_trajectory_csv.argtypes = [C.c_char_p, F32P, C.c_int, C.c_int, C.c_int]
+    lib.dvo_write_png.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int]
     lib.dvo_frame_set_xi.argtypes = [C.c_void_p, C.c_int, F32P, F32P]
     lib.dvo_frame_get_xi.argtypes = [C.c_void_p, C.c_int, F32P, F32P]
     lib.dvo_warp_image.argtypes = [C.c_void_p, C.c_int, C.c_int, F32P, F32P]
@@ -309,6 +314,28 @@ class Dvo:
         out = np.empty((self.S, h, w), np.float32)
         self._ck(self.lib.dvo_frame_download(self.ctx, slot, level, IMG[kind], _p(out)))
         return out
+
+    def visualize(self, slot, level, kind):
+        """Draw::visualize* (src/core/draw.cpp:7-100) of one level: (S, h, w, 3) BGR bytes."""
+        w, h = self.level_size(level)
+        out = np.empty((self.S, h, w, 3), np.uint8)
+        self._ck(self.lib.dvo_visualize(self.ctx, slot, level, VIS[kind], out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def inverse_pose(self, T):
+        """Convert::inversePose (src/core/convert.cpp:31-39)."""
+        T = _f32(np.asarray(T, np.float32).reshape(4, 4)); out = np.empty((4, 4), np.float32)
+        self._ck(self.lib.dvo_inverse_pose(_p(T), _p(out)))
+        return out
+
+    def write_trajectory_csv(self, path, T, first_frame=0, append=False):
+        T = _f32(np.asarray(T, np.float32).reshape(-1, 16))
+        self._ck(self.lib.dvo_write_trajectory_csv(os.fsencode(path), _p(T), len(T), int(first_frame), 1 if append else 0))
+
+    def write_png(self, path, bgr):
+        bgr = np.ascontiguousarray(bgr, np.uint8)
+        assert bgr.ndim == 3 and bgr.shape[2] == 3
+        self._ck(self.lib.dvo_write_png(os.fsencode(path), bgr.ctypes.data_as(C.c_void_p), bgr.shape[1], bgr.shape[0]))
 
     def frame_set_xi(self, slot, xi=None, rel_xi=None):
         a = _f32(np.broadcast_to(np.asarray(xi, np.float32).reshape(-1, 6), (self.S, 6))) if xi is not None else None

@@ -125,6 +125,29 @@ int dvo_frame_release(dvo_ctx* ctx, int slot);
 int dvo_frame_set_depth(dvo_ctx* ctx, int slot, const float* depth, const float* sigma, const float* age, int full_res);
 int dvo_frame_download(dvo_ctx* ctx, int slot, int level, int kind, float* out);
 int dvo_frame_set_xi(dvo_ctx* ctx, int slot, const float* xi /*[n_streams][6]*/, const float* rel_xi /*nullable*/);
+/* ---- headless outputs -------------------------------------------------------------
+ * Draw::visualize* (include/core/draw.hpp:9-23, src/core/draw.cpp:7-100) of one level of a frame slot, computed on the device:
+ * the 8-bit BGR image cv::imshow would be handed (invalid pixels blue, depth as hue, ...).  bgr_out: [n_streams][h_l][w_l][3]. */
+typedef enum dvo_vis_kind {
+    DVO_VIS_GRAY = 0,        /* visualizeGray(gray)            draw.cpp:7-19  */
+    DVO_VIS_DEPTH = 1,       /* visualizeDepth(depth)          draw.cpp:32-48 */
+    DVO_VIS_DEPTH_SIGMA = 2, /* visualizeDepth(depth, sigma)   draw.cpp:50-67 */
+    DVO_VIS_DEPTH_RAW = 3,   /* visualizeDepthRaw(depth)       draw.cpp:21-29 */
+    DVO_VIS_SIGMA = 4,       /* visualizeSigma(sigma)          draw.cpp:69-75 */
+    DVO_VIS_GRADX = 5,       /* visualizeGradient(gradX)       draw.cpp:77-91 */
+    DVO_VIS_GRADY = 6,       /* visualizeGradient(gradY)                      */
+    DVO_VIS_AGE = 7          /* visualizeAge(age), finest level draw.cpp:94-100 */
+} dvo_vis_kind;
+int dvo_visualize(dvo_ctx* ctx, int slot, int level, int kind, uint8_t* bgr_out);
+/* Convert::inversePose (src/core/convert.cpp:31-39): R^T and -t (not -R^T t) in a 4x4 whose last row stays ZERO, as the reference
+ * builds it; main.cpp:50-51 pushes that matrix on the trajectory it draws.  Host arithmetic (16 floats). */
+int dvo_inverse_pose(const float T[16], float out[16]);
+/* The trajectory main.cpp:50-53,76-86 hands to the GLFW drawer, as a file: one line per pose, `frame,t00,...,t33` (%.9g).
+ * append != 0 adds to an existing file; first_frame numbers the first row. */
+int dvo_write_trajectory_csv(const char* path, const float* T /*[n][16]*/, int n, int first_frame, int append);
+/* 8-bit BGR image (dvo_visualize's layout, one stream) -> PNG file (RGB, stored deflate blocks: no zlib dependency). */
+int dvo_write_png(const char* path, const uint8_t* bgr, int width, int height);
+
 int dvo_frame_get_xi(dvo_ctx* ctx, int slot, float* xi, float* rel_xi /*nullable*/);
 
 /* ---- Kinect ingest: Core::KinectLoader::getMappedImages (src/core/loader.cpp:90-147) + Transform::mapDepthtoGray

@@ -1200,3 +1200,85 @@ int orc_vo_odometrize(orc_vo* vo, const float* gray, int w, int h, const float* 
     orc_se3_exp(frame->xi, T_out); /* :73 */
     return 0;
 }
+
+/* ------------------------------------------------------------------------------------------ */
+/* Draw — src/core/draw.cpp (headless: the BGR bytes cv::imshow would get)                    */
+/* ------------------------------------------------------------------------------------------ */
+
+/* cv::Mat::convertTo(CV_8UC1, a, b) on CV_32F: saturate_cast<uchar>(src * a + b) in float, rounded half to even (cvRound).
+ * OpenCV's vector body uses v_fma where the CPU has FMA3 (cv2 4.13 here does), its scalar tail a separate multiply and add;
+ * the two differ only for b != 0 (visualizeSigma).  The fused form is the one restated. */
+uint8_t orc_convert_8u(float v, float a, float b)
+{
+    const float r = fmaf(v, a, b);
+    if (!(r > -2147483648.0f && r < 2147483648.0f)) return 0; /* cvRound -> INT_MIN -> saturates to 0 */
+    const long q = lrintf(r);
+    return (uint8_t)(q < 0 ? 0 : q > 255 ? 255 : q);
+}
+
+/* cv::cvtColor(CV_8UC3, COLOR_HSV2BGR), H in [0, 180]: OpenCV 4.x HSV2RGB_b = float HSV2RGB with hscale 6/180 on
+ * (h, s / 255, v / 255), tab[] with fused 1 - s h, results * 255 TRUNCATED (v_trunc in the vector body). */
+void orc_hsv2bgr_8u(uint8_t H, uint8_t S, uint8_t V, uint8_t bgr[3])
+{
+    static const int sector_data[6][3] = {{1, 3, 0}, {1, 0, 2}, {3, 0, 1}, {0, 2, 1}, {0, 1, 3}, {2, 1, 0}};
+    const float s = (float)S * (1.f / 255.f), v = (float)V * (1.f / 255.f);
+    float h = (float)H * (6.f / 180.f);
+    if (h >= 6.f) h -= 6.f;
+    int sector = (int)floorf(h);
+    h -= (float)sector;
+    if ((unsigned)sector >= 6u) { sector = 0; h = 0.f; }
+    float tab[4];
+    tab[0] = v;
+    tab[1] = v * (1.f - s);
+    tab[2] = v * fmaf(-s, h, 1.f);
+    tab[3] = v * fmaf(-s, 1.f - h, 1.f);
+    for (int k = 0; k < 3; k++) {
+        const float x = tab[sector_data[sector][k]] * 255.f;
+        const int q = (int)x;
+        bgr[k] = (uint8_t)(q < 0 ? 0 : q > 255 ? 255 : q);
+    }
+}
+
+/* static_cast<unsigned char>(float) as x86 compiles it: cvttss2si, low byte */
+static uint8_t uchar_cast(float v) { return (uint8_t)(orc_trunc(v) & 0xff); }
+
+void orc_visualize(int kind, const float* src, const float* aux, int n, uint8_t* bgr)
+{
+    for (int i = 0; i < n; i++) {
+        const float t = src[i];
+        uint8_t* p = bgr + 3 * (size_t)i;
+        switch (kind) {
+        case 0: { /* draw.cpp:7-19 */
+            p[0] = p[1] = p[2] = orc_convert_8u(t, 255.f, 0.f);
+            if (!(t > ORC_INVALID)) p[0] = 255;
+            break;
+        }
+        case 1: case 2: { /* draw.cpp:32-67 */
+            if (t < 1e-6f) { p[0] = p[1] = p[2] = 0; break; }
+            float x = (t - 0.70f) * 70.0f;
+            x = x < 0.0f ? 0.0f : (180.0f < x ? 180.0f : x); /* std::clamp */
+            const uint8_t hh = uchar_cast(x);
+            uint8_t vv = 255;
+            if (kind == 2) { const float sg = aux[i]; vv = uchar_cast(-500 * (sg < 0.5f ? sg : 0.5f) + 255); }
+            orc_hsv2bgr_8u(hh, 255, vv, p);
+            break;
+        }
+        case 3: { /* draw.cpp:21-29: cv::min(., 2.5f), cv::max(., 0.5f), convertTo(CV_8UC1, 100) */
+            float x = t < 2.5f ? t : 2.5f; /* cv::min / cv::max with a scalar: std::min(a, b) = b < a ? b : a */
+            x = x > 0.5f ? x : 0.5f;
+            if (t != t) x = 0.5f;
+            p[0] = p[1] = p[2] = orc_convert_8u(x, 100.f, 0.f);
+            break;
+        }
+        case 4: p[0] = p[1] = p[2] = orc_convert_8u(t, -500.f, 255.f); break; /* draw.cpp:69-75 */
+        case 5: { /* draw.cpp:77-91 */
+            p[0] = p[1] = p[2] = 0;
+            if (t <= ORC_INVALID) { p[0] = 255; break; }
+            p[1] = uchar_cast(255 * (t > 0.0f ? t : 0.0f));
+            p[2] = uchar_cast(-255 * (t < 0.0f ? t : 0.0f));
+            break;
+        }
+        default: p[0] = p[1] = p[2] = orc_convert_8u(t, 10.f, 0.f); break; /* draw.cpp:94-100 */
+        }
+    }
+}

@@ -145,6 +145,14 @@ int orc_mapper_update(float* depth, float* sigma, float* age, int w, int h, cons
                       const float obj_xi[6], const float rel_xi[6], const float K[9],
                       const orc_params* P, orc_rng* rng, uint8_t* mask, int* valid_update);
 
+/* Draw::visualize* (src/core/draw.cpp:7-100): float image -> 8-bit BGR, n pixels.  kind: 0 visualizeGray, 1 visualizeDepth(depth),
+ * 2 visualizeDepth(depth, sigma), 3 visualizeDepthRaw, 4 visualizeSigma, 5 visualizeGradient, 6 visualizeAge.  `aux` = sigma for
+ * kind 2, else unused.  OpenCV's convertTo(CV_8UC1, a, b) and 8-bit COLOR_HSV2BGR are restated from OpenCV 4.x (third party, not
+ * in /root/reference) and pinned against cv2 4.13 by tests/golden/make_draw.py. */
+void orc_hsv2bgr_8u(uint8_t h, uint8_t s, uint8_t v, uint8_t bgr[3]);
+uint8_t orc_convert_8u(float v, float a, float b);
+void orc_visualize(int kind, const float* src, const float* aux, int n, uint8_t* bgr);
+
 #ifdef __cplusplus
 }
 #endif

@@ -271,6 +271,25 @@ class Oracle:
         self.lib.orc_regularize(_p(depth), _p(sigma), C.c_int(w), C.c_int(h), _p(out))
         return out
 
+    VIS = {"gray": 0, "depth": 1, "depth_sigma": 2, "depth_raw": 3, "sigma": 4, "gradient": 5, "age": 6}
+
+    def visualize(self, kind, src, aux=None):
+        """Draw::visualize* (draw.cpp:7-100): float image -> (h, w, 3) BGR bytes."""
+        src = _f32(src); out = np.empty(src.shape + (3,), np.uint8)
+        aux = _f32(aux) if aux is not None else None
+        self.lib.orc_visualize(C.c_int(self.VIS[kind]), _p(src), _p(aux) if aux is not None else None, C.c_int(src.size),
+                               out.ctypes.data_as(C.c_void_p))
+        return out
+
+    def hsv2bgr(self, h, s, v):
+        out = (C.c_uint8 * 3)()
+        self.lib.orc_hsv2bgr_8u(C.c_uint8(h), C.c_uint8(s), C.c_uint8(v), out)
+        return tuple(out)
+
+    def convert_8u(self, v, a, b):
+        self.lib.orc_convert_8u.restype = C.c_uint8
+        return int(self.lib.orc_convert_8u(C.c_float(v), C.c_float(a), C.c_float(b)))
+
     def mapper_update(self, depth, sigma, age, obj_gray, born_gray, born_gx, born_gy, hist_xi, obj_xi, rel_xi, K,
                       params=None, rng=None):
         """In-place on copies; returns (depth, sigma, age, mask, valid_update, rc)."""

@@ -6,6 +6,7 @@
 //   in.bin : int32 n, w, h; float K[9]; n gray frames [h][w]; depth0 [h][w]; sigma0 [h][w];
 //            prior depth [h/4][w/4]; prior sigma [h/4][w/4]
 //   out.bin: sequence of (int32 count, float[count]) records, in the order written below
+#include "dvo/core/draw.hpp"
 #include "dvo/core/transform.hpp"
 #include "dvo/map/implement.hpp"
 #include "dvo/map/mapper.hpp"
@@ -111,6 +112,22 @@ int main(int argc, char** argv)
         System::VisualOdometry vo2(K);
         put(vo2.odometrizeUsingDepth(gray[0], depth0, sigma0));
         put(vo2.odometrizeUsingDepth(gray[1], depth0, sigma0));
+        // 10. headless outputs: Draw::visualize* of the keyframe of step 8, Convert::inversePose, trajectory file, PNG
+        auto put_img = [](const Draw::Image& im) {
+            std::vector<float> f(im.data.begin(), im.data.end());
+            put(f.data(), (int)f.size());
+        };
+        const System::Scene& top = *kf->top();
+        put_img(Draw::visualizeGray(top)); put_img(Draw::visualizeDepth(top)); put_img(Draw::visualizeDepthSigma(top));
+        put_img(Draw::visualizeSigma(top)); put_img(Draw::visualizeGradientX(top)); put_img(Draw::visualizeAge(top));
+        Draw::Image both = Draw::merge(Draw::visualizeDepthRaw(top), Draw::visualizeGradientY(top));
+        put((float)both.rows);
+        const std::string base = std::string(argv[2]);
+        both.writePng(base + ".png");
+        dvo::TrajectoryWriter traj(base + ".csv");
+        Mat1f Tlast = math::se3::exp(kf->m_xi);
+        traj.push(Convert::inversePose(Tlast)); traj.push(Tlast);
+        put(Convert::inversePose(Tlast));
     } catch (const std::exception& e) {
         fprintf(stderr, "dropin_main: %s\n", e.what());
         return 1;

@@ -156,3 +156,21 @@ def test_dropin_matches_oracle(orc, seq160, tmp_path):
     o1 = orc.frame_create(g[1], K, 4, 1, d[0], sigma0)
     x1, _ = orc.track(o1, ref)
     assert np.abs(next(rec).reshape(4, 4) - orc.se3_exp(x1)).max() <= 1e-4
+    # 10. headless outputs: Draw::visualize* of step 8's keyframe = the oracle's colour maps of the same images
+    kd, ks, ka = (m.reshape(h // 4, w // 4) for m in maps7)
+    vis = {k: next(rec) for k in ("gray", "depth", "depth_sigma", "sigma", "gradx", "age")}
+    as_u8 = lambda a: a.astype(np.uint8).reshape(h // 4, w // 4, 3)
+    assert as_u8(vis["depth"]).tobytes() == orc.visualize("depth", kd).tobytes()
+    assert as_u8(vis["depth_sigma"]).tobytes() == orc.visualize("depth_sigma", kd, ks).tobytes()
+    assert as_u8(vis["sigma"]).tobytes() == orc.visualize("sigma", ks).tobytes()
+    assert as_u8(vis["age"]).tobytes() == orc.visualize("age", ka).tobytes()
+    gv = as_u8(vis["gray"])
+    assert (gv[..., 1] == gv[..., 2]).all() and gv[..., 1].std() > 5          # a gray image (invalid pixels only differ in blue)
+    assert int(next(rec)[0]) == 2 * (h // 4)                                      # Draw::merge(img1, img2): vconcat
+    assert open(str(outp) + ".png", "rb").read(8) == b"\x89PNG\r\n\x1a\n"
+    inv = next(rec).reshape(4, 4)
+    rows = np.loadtxt(str(outp) + ".csv", delimiter=",")
+    assert rows.shape == (2, 17) and rows[:, 0].tolist() == [0, 1]
+    assert np.array_equal(rows[0, 1:].astype(np.float32).reshape(4, 4), inv)
+    Tl = rows[1, 1:].astype(np.float32).reshape(4, 4)
+    assert np.array_equal(inv[:3, :3], Tl[:3, :3].T) and np.array_equal(inv[:3, 3], -Tl[:3, 3]) and not inv[3].any()
