@@ -280,10 +280,10 @@ def ncu_traffic(kernel):
         try:
             k = json.load(open(path))["kernels"].get(kernel)
             if k:
-                return k["dram_bytes"], os.path.basename(path)
+                return k["dram_bytes"], os.path.basename(path), k
         except Exception:
             continue
-    return None, None
+    return None, None, None
 
 
 def run_other_configs(lib):
@@ -557,7 +557,15 @@ def run_gpu_arm(args, rank, world, local_rank, dist):
         table.append(dict(kernel=name, launches=kn, avg_launch_us=1e3 * kms / kn if kn else None, share=kms / tot_ms,
                           algorithmic_bytes_per_launch=b / kn if kn else None, achieved_gbs=gbs, frac=gbs / peak, bytes_model=what))
     top = table[0]
-    traffic, traffic_src = ncu_traffic(top["kernel"])
+    traffic, traffic_src, cap = ncu_traffic(top["kernel"])
+    # the levels below HBM, from the same ncu capture (one launch early in a sequence, cold cache): what the kernel is bound by when
+    # it is not DRAM - L2 traffic, and ncu's percent-of-peak for L2, L1/TEX and the SM
+    hierarchy = None
+    if cap and "lts_bytes" in cap:
+        hierarchy = dict(source=traffic_src, capture_launch_us=cap["duration_us"], l2_bytes=cap["lts_bytes"],
+                         l2_gbs=cap["lts_bytes"] / (cap["duration_us"] * 1e-6) / 1e9, l2_pct_of_peak=cap.get("lts_pct_of_peak"),
+                         l2_hit_pct=cap.get("l2_hit_pct"), l1tex_pct_of_peak=cap.get("l1tex_pct_of_peak"), l1_hit_pct=cap.get("l1_hit_pct"),
+                         sm_pct_of_peak=cap.get("sm_pct_of_peak"), dram_pct_of_measured_peak=100.0 * cap["dram_bytes"] / (cap["duration_us"] * 1e-6) / 1e9 / peak)
     res = dict(
         value=world * S * K_ / (ms * 1e-3), ms_per_step=ms / K_,
         e2e=dict(value=world * S * E / e2e_s, unit="frames/s", h2d_bytes_per_step=h2d_bytes, d2h_bytes_per_step=S * 64, steps=E,
@@ -574,7 +582,7 @@ def run_gpu_arm(args, rank, world, local_rank, dist):
         roofline=dict(kernel=top["kernel"], bound="hbm", achieved=top["achieved_gbs"], peak=peak, unit="GB/s", frac=top["frac"],
                       traffic=traffic, traffic_source=traffic_src, peak_source=peak_src, launches=top["launches"], avg_launch_us=top["avg_launch_us"],
                       algorithmic_bytes_per_launch=top["algorithmic_bytes_per_launch"], share_of_step=top["share"],
-                      bytes_model=top["bytes_model"]),
+                      bytes_model=top["bytes_model"], hierarchy=hierarchy),
         kernels=table,
         gn_iters_per_s=world * gn_iters / (ms * 1e-3), gn_iters_per_frame=gn_iters / float(S * K_),
         frames_propagate=n_prop, frames_update=n_upd)

@@ -61,6 +61,14 @@ def traffic(path):
         rd = float(r[idx["dram__bytes_read.sum"]]) * scale[unit[idx["dram__bytes_read.sum"]]]
         wr = float(r[idx["dram__bytes_write.sum"]]) * scale[unit[idx["dram__bytes_write.sum"]]]
         res[k] = dict(dram_bytes=rd + wr, dram_read=rd, dram_write=wr, duration_us=float(r[idx["gpu__time_duration.sum"]]))
+        # the other levels of the hierarchy (BASELINE.json: "% HBM/L2 roofline"): L2 traffic (32 B sectors) and ncu's own
+        # percent-of-peak figures for L2, L1/TEX and the SM
+        for key, col, mul in (("lts_bytes", "lts__t_sectors.sum", 32.0), ("lts_pct_of_peak", "lts__throughput.avg.pct_of_peak_sustained_elapsed", 1.0),
+                              ("l1tex_pct_of_peak", "l1tex__throughput.avg.pct_of_peak_sustained_elapsed", 1.0),
+                              ("sm_pct_of_peak", "sm__throughput.avg.pct_of_peak_sustained_elapsed", 1.0),
+                              ("l2_hit_pct", "lts__t_sector_hit_rate.pct", 1.0), ("l1_hit_pct", "l1tex__t_sector_hit_rate.pct", 1.0)):
+            if col in idx and r[idx[col]] not in ("", "n/a"):
+                res[k][key] = float(r[idx[col]].replace(",", "")) * mul
     print(json.dumps(dict(source=path.split("/")[-1], how="ncu --set full --clock-control none, first captured launch of each kernel", kernels=res), indent=1))
 
 
