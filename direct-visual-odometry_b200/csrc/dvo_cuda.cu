@@ -643,6 +643,27 @@ extern "C" int dvo_visualize(dvo_ctx* ctx, int slot, int level, int kind, uint8_
     return DVO_OK;
 }
 
+// Draw::visualize*(image) on raw host images, any size: no context needed (temporary device buffers on `device`'s default stream)
+extern "C" int dvo_visualize_image(int kind, const float* src, const float* aux, int width, int height, uint8_t* bgr_out)
+{
+    if (!src || !bgr_out || width <= 0 || height <= 0 || kind < DVO_VIS_GRAY || kind > DVO_VIS_AGE) return DVO_ERR_ARG;
+    if (kind == DVO_VIS_DEPTH_SIGMA && !aux) return DVO_ERR_ARG;
+    const size_t n = (size_t)width * height;
+    float *d_src = nullptr, *d_aux = nullptr;
+    uint8_t* d_out = nullptr;
+    bool ok = cudaMalloc(&d_src, n * 4) == cudaSuccess && cudaMalloc(&d_out, n * 3) == cudaSuccess;
+    const bool use_aux = (kind == DVO_VIS_DEPTH_SIGMA);
+    if (ok && use_aux) ok = cudaMalloc(&d_aux, n * 4) == cudaSuccess;
+    if (ok) ok = cudaMemcpy(d_src, src, n * 4, cudaMemcpyHostToDevice) == cudaSuccess;
+    if (ok && use_aux) ok = cudaMemcpy(d_aux, aux, n * 4, cudaMemcpyHostToDevice) == cudaSuccess;
+    if (ok) {
+        k_visualize_image<<<(unsigned)((n + 255) / 256), 256>>>(kind, d_src, d_aux, n, d_out);
+        ok = cudaGetLastError() == cudaSuccess && cudaMemcpy(bgr_out, d_out, n * 3, cudaMemcpyDeviceToHost) == cudaSuccess;
+    }
+    cudaFree(d_src); cudaFree(d_aux); cudaFree(d_out);
+    return ok ? DVO_OK : DVO_ERR_CUDA;
+}
+
 // ---- headless outputs: host side ----------------------------------------------------------------
 extern "C" int dvo_inverse_pose(const float T[16], float out[16])
 {

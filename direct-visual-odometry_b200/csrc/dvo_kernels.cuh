@@ -297,7 +297,42 @@ __device__ __forceinline__ void cv_hsv2bgr_8u(uint8_t H, uint8_t S, uint8_t V, u
     }
 }
 
-// kind: dvo_vis_kind.  grid = (ceil(n_l/256), S); out: [S][n_l][3]
+// one pixel of Draw::visualize*: t = the image value the reference's function reads (gray, depth, sigma, a gradient, age),
+// sg = sigma for visualizeDepth(depth, sigma)
+__device__ __forceinline__ void vis_pixel(int kind, float t, float sg, uint8_t p[3])
+{
+    p[0] = p[1] = p[2] = 0;
+    switch (kind) {
+    case DVO_VIS_GRAY: // draw.cpp:7-19
+        p[0] = p[1] = p[2] = cv_convert_8u(t, 255.f, 0.f);
+        if (!is_valid(t)) p[0] = 255;
+        break;
+    case DVO_VIS_DEPTH: case DVO_VIS_DEPTH_SIGMA: { // draw.cpp:32-67
+        if (t < 1e-6f) break;
+        float hx = (t - 0.70f) * 70.0f;
+        hx = hx < 0.0f ? 0.0f : (180.0f < hx ? 180.0f : hx); // std::clamp
+        uint8_t vv = 255;
+        if (kind == DVO_VIS_DEPTH_SIGMA) vv = uchar_cast(-500 * (sg < 0.5f ? sg : 0.5f) + 255);
+        cv_hsv2bgr_8u(uchar_cast(hx), 255, vv, p);
+        break;
+    }
+    case DVO_VIS_DEPTH_RAW: { // draw.cpp:21-29
+        float q = t < 2.5f ? t : 2.5f;
+        q = q > 0.5f ? q : 0.5f;
+        p[0] = p[1] = p[2] = cv_convert_8u(q, 100.f, 0.f);
+        break;
+    }
+    case DVO_VIS_SIGMA: p[0] = p[1] = p[2] = cv_convert_8u(t, -500.f, 255.f); break; // draw.cpp:69-75
+    case DVO_VIS_GRADX: case DVO_VIS_GRADY: // draw.cpp:77-91
+        if (is_invalid(t)) { p[0] = 255; break; }
+        p[1] = uchar_cast(255 * (t > 0.0f ? t : 0.0f));
+        p[2] = uchar_cast(-255 * (t < 0.0f ? t : 0.0f));
+        break;
+    default: p[0] = p[1] = p[2] = cv_convert_8u(t, 10.f, 0.f); break; // draw.cpp:94-100
+    }
+}
+
+// one level of a frame slot.  kind: dvo_vis_kind.  grid = (ceil(n_l/256), S); out: [S][n_l][3]
 __global__ void __launch_bounds__(256) k_visualize(const __grid_constant__ Consts c, SlotDev slot, int l, int kind, uint8_t* __restrict__ out)
 {
     const int s = blockIdx.y;
@@ -308,47 +343,31 @@ __global__ void __launch_bounds__(256) k_visualize(const __grid_constant__ Const
     const int y = i / g.w, x = i - y * g.w;
     const size_t nt = (size_t)c.lv[c.L - 1].n;
     const size_t ti = (size_t)s * nt + top_index(v, x, y);
-    uint8_t p[3] = {0, 0, 0};
+    float t, sg = 0.f;
     switch (kind) {
-    case DVO_VIS_GRAY: { // draw.cpp:7-19
-        const float t = level_value(v, slot.gray[ti]);
-        p[0] = p[1] = p[2] = cv_convert_8u(t, 255.f, 0.f);
-        if (is_invalid(t) || t != t) p[0] = 255;
-        break;
+    case DVO_VIS_GRAY: t = level_value(v, slot.gray[ti]); break;
+    case DVO_VIS_DEPTH: case DVO_VIS_DEPTH_RAW: t = level_value(v, slot.ds[ti].x); break;
+    case DVO_VIS_DEPTH_SIGMA: { const float2 d = slot.ds[ti]; t = level_value(v, d.x); sg = level_value(v, d.y); break; }
+    case DVO_VIS_SIGMA: t = level_value(v, slot.ds[ti].y); break;
+    case DVO_VIS_GRADX: t = grad_x_at(slot.gray + (size_t)s * nt, v, x, y); break;
+    case DVO_VIS_GRADY: t = grad_y_at(slot.gray + (size_t)s * nt, v, x, y); break;
+    default: t = slot.age[ti]; break;
     }
-    case DVO_VIS_DEPTH: case DVO_VIS_DEPTH_SIGMA: { // draw.cpp:32-67
-        const float2 d = slot.ds[ti];
-        const float t = level_value(v, d.x);
-        if (t < 1e-6f) break;
-        float hx = (t - 0.70f) * 70.0f;
-        hx = hx < 0.0f ? 0.0f : (180.0f < hx ? 180.0f : hx); // std::clamp
-        uint8_t vv = 255;
-        if (kind == DVO_VIS_DEPTH_SIGMA) {
-            const float sg = level_value(v, d.y);
-            vv = uchar_cast(-500 * (sg < 0.5f ? sg : 0.5f) + 255);
-        }
-        cv_hsv2bgr_8u(uchar_cast(hx), 255, vv, p);
-        break;
-    }
-    case DVO_VIS_DEPTH_RAW: { // draw.cpp:21-29
-        const float t = level_value(v, slot.ds[ti].x);
-        float q = t < 2.5f ? t : 2.5f;
-        q = q > 0.5f ? q : 0.5f;
-        p[0] = p[1] = p[2] = cv_convert_8u(q, 100.f, 0.f);
-        break;
-    }
-    case DVO_VIS_SIGMA: p[0] = p[1] = p[2] = cv_convert_8u(level_value(v, slot.ds[ti].y), -500.f, 255.f); break; // draw.cpp:69-75
-    case DVO_VIS_GRADX: case DVO_VIS_GRADY: { // draw.cpp:77-91
-        const float t = kind == DVO_VIS_GRADX ? grad_x_at(slot.gray + (size_t)s * nt, v, x, y) : grad_y_at(slot.gray + (size_t)s * nt, v, x, y);
-        if (is_invalid(t)) { p[0] = 255; break; }
-        p[1] = uchar_cast(255 * (t > 0.0f ? t : 0.0f));
-        p[2] = uchar_cast(-255 * (t < 0.0f ? t : 0.0f));
-        break;
-    }
-    default: p[0] = p[1] = p[2] = cv_convert_8u(slot.age[ti], 10.f, 0.f); break; // draw.cpp:94-100
-    }
+    uint8_t p[3];
+    vis_pixel(kind, t, sg, p);
     uint8_t* o = out + ((size_t)s * g.n + i) * 3;
     o[0] = p[0]; o[1] = p[1]; o[2] = p[2];
+}
+
+// a raw image, as the reference's callers pass it (Draw::visualizeGray(obj_gray), test/update.cpp:19).  aux = sigma or nullptr
+__global__ void __launch_bounds__(256) k_visualize_image(int kind, const float* __restrict__ src, const float* __restrict__ aux, size_t n,
+                                                         uint8_t* __restrict__ out)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint8_t p[3];
+    vis_pixel(kind, src[i], aux ? aux[i] : 0.f, p);
+    out[3 * i] = p[0]; out[3 * i + 1] = p[1]; out[3 * i + 2] = p[2];
 }
 
 // =============================================================================================

@@ -46,7 +46,7 @@ class DvoIterLog(C.Structure):
 EXPORTS = [
     "dvo_device_count", "dvo_set_device", "dvo_params_default", "dvo_create", "dvo_destroy", "dvo_last_error", "dvo_sync", "dvo_level_size", "dvo_level_K",
     "dvo_host_alloc", "dvo_host_free", "dvo_frame_create", "dvo_frame_create_dev", "dvo_frame_release",
-    "dvo_frame_set_depth", "dvo_frame_download", "dvo_visualize", "dvo_inverse_pose", "dvo_write_trajectory_csv", "dvo_write_png", "dvo_frame_set_xi", "dvo_frame_get_xi", "dvo_warp_image",
+    "dvo_frame_set_depth", "dvo_frame_download", "dvo_visualize", "dvo_visualize_image", "dvo_inverse_pose", "dvo_write_trajectory_csv", "dvo_write_png", "dvo_frame_set_xi", "dvo_frame_get_xi", "dvo_warp_image",
     "dvo_gn_step", "dvo_track", "dvo_map_propagate", "dvo_map_update", "dvo_map_regularize", "dvo_rng_position",
     "dvo_mask_compact", "dvo_vo_reset", "dvo_vo_reserve", "dvo_vo_force_pose", "dvo_vo_push", "dvo_vo_push_dev", "dvo_vo_state", "dvo_vo_ref_slot",
     "dvo_vo_last_slot", "dvo_vo_last_log", "dvo_vo_counters", "dvo_vo_error", "dvo_synth_render_dev", "dvo_dev_alloc", "dvo_dev_free",
@@ -85,6 +85,7 @@ def load_library(path=None):
     lib.dvo_frame_set_depth.argtypes = [C.c_void_p, C.c_int, F32P, F32P, F32P, C.c_int]
     lib.dvo_frame_download.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, F32P]
     lib.dvo_visualize.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
+    lib.dvo_visualize_image.argtypes = [C.c_int, F32P, F32P, C.c_int, C.c_int, C.c_void_p]
     lib.dvo_inverse_pose.argtypes = [F32P, F32P]
     lib.dvo_write_trajectory_csv.argtypes = [C.c_char_p, F32P, C.c_int, C.c_int, C.c_int]
     lib.dvo_write_png.argtypes = [C.c_char_p, C.c_void_p, C.c_int, C.c_int]
@@ -320,6 +321,13 @@ class Dvo:
         w, h = self.level_size(level)
         out = np.empty((self.S, h, w, 3), np.uint8)
         self._ck(self.lib.dvo_visualize(self.ctx, slot, level, VIS[kind], out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def visualize_image(self, kind, src, aux=None):
+        """Draw::visualize*(image) on a raw host image: (h, w, 3) BGR bytes."""
+        src = _f32(src); aux = _f32(aux) if aux is not None else None
+        out = np.empty(src.shape + (3,), np.uint8)
+        self._ck(self.lib.dvo_visualize_image(VIS[kind], _p(src), _p(aux), src.shape[1], src.shape[0], out.ctypes.data_as(C.c_void_p)))
         return out
 
     def inverse_pose(self, T):

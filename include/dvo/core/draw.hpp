@@ -1,8 +1,9 @@
 // dvo/core/draw.hpp — Draw::visualize* (include/core/draw.hpp:9-23, src/core/draw.cpp:7-100) and Convert::inversePose
 // (src/core/convert.cpp:31-39) over the C ABI, headless: the reference hands the 8-bit BGR image to cv::imshow and the inverted
 // poses to its GLFW drawer (main.cpp:50-53,76-86); here the same bytes come back as a Draw::Image (optionally written as a PNG)
-// and the poses go to a CSV file.  The colour mapping runs on the device from the frame's slot, so the overloads take the
-// System::Scene (one pyramid level of a Frame) whose image the reference would have passed.
+// and the poses go to a CSV file.  The colour mapping runs on the device: either from a raw image, with the reference's own
+// signatures (visualizeGray(const Mat1f&), visualizeDepth(depth, sigma), ...), or straight from a frame's slot through the
+// overloads that take the System::Scene (one pyramid level of a Frame) whose image the reference would have passed.
 #pragma once
 #include "../system/frame.hpp"
 
@@ -39,6 +40,27 @@ inline Image visualizeSigma(const System::Scene& s) { return visualize(s, DVO_VI
 inline Image visualizeGradientX(const System::Scene& s) { return visualize(s, DVO_VIS_GRADX); }          // visualizeGradient(gradX), draw.cpp:77-91
 inline Image visualizeGradientY(const System::Scene& s) { return visualize(s, DVO_VIS_GRADY); }
 inline Image visualizeAge(const System::Scene& s) { return visualize(s, DVO_VIS_AGE); }                  // finest level only, draw.cpp:94-100
+
+// The reference's own signatures: a raw image (test/update.cpp:19-27, src/map/mapper.cpp:37-42)
+inline Image visualize(const dvo::Mat1f& image, dvo_vis_kind kind, const dvo::Mat1f* sigma = nullptr)
+{
+    dvo::require(!image.empty(), "visualize: empty image");
+    dvo::require(sigma == nullptr || (sigma->rows == image.rows && sigma->cols == image.cols), "visualize: depth/sigma size mismatch");
+    Image out;
+    out.rows = image.rows; out.cols = image.cols;
+    out.data.resize((size_t)3 * image.rows * image.cols);
+    dvo::Mat1f k0, k1;
+    const int rc = dvo_visualize_image(kind, dvo::pixels(image, k0), sigma ? dvo::pixels(*sigma, k1) : nullptr, image.cols, image.rows, out.data.data());
+    if (rc) throw dvo::Error(rc, "dvo_visualize_image failed");
+    return out;
+}
+inline Image visualizeGray(const dvo::Mat1f& m) { return visualize(m, DVO_VIS_GRAY); }
+inline Image visualizeDepth(const dvo::Mat1f& m) { return visualize(m, DVO_VIS_DEPTH); }
+inline Image visualizeDepth(const dvo::Mat1f& depth, const dvo::Mat1f& sigma) { return visualize(depth, DVO_VIS_DEPTH_SIGMA, &sigma); }
+inline Image visualizeDepthRaw(const dvo::Mat1f& m) { return visualize(m, DVO_VIS_DEPTH_RAW); }
+inline Image visualizeSigma(const dvo::Mat1f& m) { return visualize(m, DVO_VIS_SIGMA); }
+inline Image visualizeGradient(const dvo::Mat1f& m) { return visualize(m, DVO_VIS_GRADX); }
+inline Image visualizeAge(const dvo::Mat1f& m) { return visualize(m, DVO_VIS_AGE); }
 
 // Draw::merge(img1, img2) (draw.hpp:33-39): vconcat
 inline Image merge(const Image& a, const Image& b)

@@ -139,6 +139,10 @@ typedef enum dvo_vis_kind {
     DVO_VIS_AGE = 7          /* visualizeAge(age), finest level draw.cpp:94-100 */
 } dvo_vis_kind;
 int dvo_visualize(dvo_ctx* ctx, int slot, int level, int kind, uint8_t* bgr_out);
+/* The same functions with the reference's own argument: a raw float image on the host (test/update.cpp:19-27,
+ * src/map/mapper.cpp:37-42 pass frame->gray(), frame->depth(), ...).  src / aux: [height][width]; aux = sigma, only for
+ * DVO_VIS_DEPTH_SIGMA; for DVO_VIS_GRADX / GRADY src is the gradient image itself.  Needs no context; DVO_ERR_CUDA without a device. */
+int dvo_visualize_image(int kind, const float* src, const float* aux, int width, int height, uint8_t* bgr_out);
 /* Convert::inversePose (src/core/convert.cpp:31-39): R^T and -t (not -R^T t) in a 4x4 whose last row stays ZERO, as the reference
  * builds it; main.cpp:50-51 pushes that matrix on the trajectory it draws.  Host arithmetic (16 floats). */
 int dvo_inverse_pose(const float T[16], float out[16]);

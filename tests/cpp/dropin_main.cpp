@@ -128,6 +128,9 @@ int main(int argc, char** argv)
         Mat1f Tlast = math::se3::exp(kf->m_xi);
         traj.push(Convert::inversePose(Tlast)); traj.push(Tlast);
         put(Convert::inversePose(Tlast));
+        // the reference's own call forms (src/map/mapper.cpp:37-42): raw images
+        put_img(Draw::visualizeGray(kf->gray())); put_img(Draw::visualizeDepth(kf->depth(), kf->sigma()));
+        put_img(Draw::visualizeDepth(kf->depth())); put_img(Draw::visualizeAge(kf->age())); put_img(Draw::visualizeGradient(kf->gradX()));
     } catch (const std::exception& e) {
         fprintf(stderr, "dropin_main: %s\n", e.what());
         return 1;

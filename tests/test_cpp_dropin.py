@@ -174,3 +174,6 @@ def test_dropin_matches_oracle(orc, seq160, tmp_path):
     assert np.array_equal(rows[0, 1:].astype(np.float32).reshape(4, 4), inv)
     Tl = rows[1, 1:].astype(np.float32).reshape(4, 4)
     assert np.array_equal(inv[:3, :3], Tl[:3, :3].T) and np.array_equal(inv[:3, 3], -Tl[:3, 3]) and not inv[3].any()
+    raw = [next(rec) for _ in range(5)]
+    assert raw[0].tobytes() == vis["gray"].tobytes() and raw[1].tobytes() == vis["depth_sigma"].tobytes()
+    assert raw[2].tobytes() == vis["depth"].tobytes() and raw[3].tobytes() == vis["age"].tobytes() and raw[4].tobytes() == vis["gradx"].tobytes()

@@ -135,6 +135,7 @@ def test_gpu_visualize_matches_oracle(orc, tmp_path):
             got = dv.visualize(slot, lv, kind)[0]
             want = orc.visualize(okind, src, aux)
             assert got.shape == want.shape and np.array_equal(got, want), (lv, kind, int((got != want).any(-1).sum()))
+            assert np.array_equal(dv.visualize_image(kind, src, aux), want), (lv, kind, "raw image form")
             seen += 1
     assert seen == 22
     vis = dv.visualize(slot, 2, "depth_sigma")[0]
