@@ -468,6 +468,7 @@ def run_gpu_arm(args, rank, world, local_rank, dist):
     for _ in range(W_):
         dv.vo_push_dev(fptr(f)); f += 1
     c0 = dv.vo_counters()
+    m0 = dv.vo_matched()
     # --- timed: K steps, inputs resident in HBM, CUDA events on the library's stream
     barrier()
     l0 = dv.launch_count()
@@ -480,6 +481,7 @@ def run_gpu_arm(args, rank, world, local_rank, dist):
     clocks = sampler.stop() if rank == 0 else None
     ms = maxrank(ms)
     c1 = dv.vo_counters()
+    matched = int((dv.vo_matched() - m0).sum())
     if dv.vo_error() != 0:
         raise SystemExit("bench.py: device-side VO error")
     gn_iters = int((c1["gn_iters"] - c0["gn_iters"]).sum())
@@ -585,6 +587,7 @@ def run_gpu_arm(args, rank, world, local_rank, dist):
                       bytes_model=top["bytes_model"], hierarchy=hierarchy),
         kernels=table,
         gn_iters_per_s=world * gn_iters / (ms * 1e-3), gn_iters_per_frame=gn_iters / float(S * K_),
+        matched_pixels_per_s=world * matched / (ms * 1e-3),  # pixels the epipolar search matched and Mapper::update fused (rank 0's count x ranks)
         frames_propagate=n_prop, frames_update=n_upd)
     return res
 

@@ -1211,7 +1211,7 @@ __global__ void k_vo_reset(Consts c, VoState* vo, MapState* mst)
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= c.S) return;
     vo[s].kf_slot = -1; vo[s].kf_frame_id = -1; vo[s].n_kf = 0; vo[s].need_new = 0; vo[s].was_keyframe = 0; vo[s].n_iters = 0; vo[s].cur_slot = c.vo_base;
-    vo[s].gn_iters = 0; vo[s].gn_pixels = 0; vo[s].n_propagate = 0; vo[s].n_update = 0;
+    vo[s].gn_iters = 0; vo[s].gn_pixels = 0; vo[s].n_propagate = 0; vo[s].n_update = 0; vo[s].map_matched = 0;
     mst[s].rng_pos = 0; mst[s].err = 0; mst[s].valid_update = 0; mst[s].ticket = 0;
 }
 
@@ -1460,6 +1460,19 @@ extern "C" int dvo_vo_counters(dvo_ctx* ctx, uint64_t* gn_iters, uint64_t* gn_pi
         if (n_propagate) n_propagate[s] = hv[s].n_propagate;
         if (n_update) n_update[s] = hv[s].n_update;
     }
+    return DVO_OK;
+}
+
+extern "C" int dvo_vo_matched(dvo_ctx* ctx, uint64_t* matched)
+{
+    const Consts& c = ctx->c;
+    ARG(matched, "bad argument");
+    std::vector<VoState> hv(c.S);
+    std::vector<MapState> hm(c.S);
+    CK(cudaMemcpyAsync(hv.data(), ctx->d_vo, sizeof(VoState) * (size_t)c.S, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(hm.data(), ctx->d_ms, sizeof(MapState) * (size_t)c.S, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (int s = 0; s < c.S; s++) matched[s] = hv[s].map_matched + (uint64_t)(unsigned int)hm[s].valid_update;
     return DVO_OK;
 }
 

@@ -102,6 +102,7 @@ struct VoState {
     unsigned long long gn_iters;  // Gauss-Newton iterations since dvo_vo_reset
     unsigned long long gn_pixels; // pixels swept by those iterations
     unsigned long long n_propagate, n_update; // frames mapped by propagate / update
+    unsigned long long map_matched;           // pixels Mapper::update matched and fused (valid_update, mapper.cpp:122-128), frames before the last
 };
 
 struct PoseTab { // per (stream, age): exp(-r_xi) and -r_xi[0:3] (src/map/mapper.cpp:107, implement.cpp:56-58,193)

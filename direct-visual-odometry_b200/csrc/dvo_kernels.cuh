@@ -722,6 +722,7 @@ __device__ __noinline__ void vo_decide(const Consts& c, const TrackArgs& a, cons
     const int cur_slot = vo_cur_slot(c, v->n_kf);
     v->cur_slot = cur_slot;
     const SlotDev cur = a.slots[cur_slot];
+    v->map_matched += (unsigned long long)(unsigned int)m->valid_update; // the previous frame's update, before its count is cleared
     m->valid_update = 0; m->n_reject = 0; m->ticket = 0;
     if (v->kf_slot < 0) { // first frame: m_history.setRefFrame(frame); return identity (system.hpp:49-54)
         for (int q = 0; q < 6; q++) { cur.xi[6 * s + q] = 0.f; cur.rel_xi[6 * s + q] = 0.f; }

@@ -49,7 +49,7 @@ EXPORTS = [
     "dvo_frame_set_depth", "dvo_frame_download", "dvo_visualize", "dvo_visualize_image", "dvo_inverse_pose", "dvo_write_trajectory_csv", "dvo_write_png", "dvo_frame_set_xi", "dvo_frame_get_xi", "dvo_warp_image",
     "dvo_gn_step", "dvo_track", "dvo_map_propagate", "dvo_map_update", "dvo_map_regularize", "dvo_rng_position",
     "dvo_mask_compact", "dvo_vo_reset", "dvo_vo_reserve", "dvo_vo_force_pose", "dvo_vo_push", "dvo_vo_push_dev", "dvo_vo_state", "dvo_vo_ref_slot",
-    "dvo_vo_last_slot", "dvo_vo_last_log", "dvo_vo_counters", "dvo_vo_error", "dvo_synth_render_dev", "dvo_dev_alloc", "dvo_dev_free",
+    "dvo_vo_last_slot", "dvo_vo_last_log", "dvo_vo_counters", "dvo_vo_matched", "dvo_vo_error", "dvo_synth_render_dev", "dvo_dev_alloc", "dvo_dev_free",
     "dvo_copy_to_host", "dvo_copy_to_dev", "dvo_timer_start", "dvo_timer_stop", "dvo_launch_count", "dvo_gn_timing", "dvo_kernel_timing",
     "dvo_map_update_points", "dvo_se3_exp", "dvo_se3_log", "dvo_se3_concatenate", "dvo_vo_submit", "dvo_vo_collect",
     "dvo_frame_create_gray8", "dvo_vo_push_gray8", "dvo_vo_submit_gray8",
@@ -111,6 +111,7 @@ def load_library(path=None):
     lib.dvo_vo_error.argtypes = [C.c_void_p]
     U64P = C.POINTER(C.c_uint64)
     lib.dvo_vo_counters.argtypes = [C.c_void_p, U64P, U64P, U64P, U64P]
+    lib.dvo_vo_matched.argtypes = [C.c_void_p, U64P]
     lib.dvo_vo_last_log.argtypes = [C.c_void_p, C.POINTER(DvoIterLog), C.c_int, I32P]
     lib.dvo_synth_render_dev.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_uint64, C.c_float, C.c_float]
     lib.dvo_dev_alloc.restype = C.c_void_p
@@ -513,6 +514,12 @@ class Dvo:
         arrs = [np.zeros(self.S, np.uint64) for _ in range(4)]
         self._ck(self.lib.dvo_vo_counters(self.ctx, *[a.ctypes.data_as(C.POINTER(C.c_uint64)) for a in arrs]))
         return dict(gn_iters=arrs[0], gn_pixels=arrs[1], n_propagate=arrs[2], n_update=arrs[3])
+
+    def vo_matched(self):
+        """Pixels matched and fused by Mapper::update since vo_reset, per stream (sum of valid_update)."""
+        a = np.zeros(self.S, np.uint64)
+        self._ck(self.lib.dvo_vo_matched(self.ctx, a.ctypes.data_as(C.POINTER(C.c_uint64))))
+        return a
 
     def vo_error(self):
         return self.lib.dvo_vo_error(self.ctx)

@@ -267,6 +267,9 @@ int dvo_vo_state(dvo_ctx* ctx, float* xi /*[S][6]*/, float* rel_xi /*[S][6]*/, i
  * Gauss-Newton iterations, pixels swept by them (sum of level sizes), frames mapped by
  * Mapper::propagate and by Mapper::update. */
 int dvo_vo_counters(dvo_ctx* ctx, uint64_t* gn_iters, uint64_t* gn_pixels, uint64_t* n_propagate, uint64_t* n_update);
+/* pixels matched and fused by Mapper::update since dvo_vo_reset, per stream: the sum of its `valid_update` counts
+ * (src/map/mapper.cpp:122-128,135) - the epipolar search's own unit of work (matched pixels / s). */
+int dvo_vo_matched(dvo_ctx* ctx, uint64_t* matched /*[n_streams]*/);
 /* Gauss-Newton iteration records of the last pushed frame's tracking (what Tracker::track prints,
  * src/track/tracker.cpp:56-61).  log: [n_streams][log_cap]; n_iters: [n_streams]. */
 int dvo_vo_last_log(dvo_ctx* ctx, dvo_iter_log* log, int log_cap, int* n_iters);

@@ -42,6 +42,7 @@ def _run_pair(orc, g, K, d0, s0, levels=3, culls=2, n_streams=1, forced=True, up
     vo = orc.vo_create(K, levels, culls, orc.params(**params))
     top = levels - 1
     n_kf = 0; n_upd = 0; agreed = 0; n_ulp = [0]
+    matched = np.zeros(n_streams, np.uint64)  # running sum of Mapper::update's valid_update counts
     bc = lambda a: np.broadcast_to(a, (n_streams,) + a.shape)
     for i in range(n):
         T_o = vo.odometrize(g[i], d0 if i == 0 else None, s0 if i == 0 else None)
@@ -78,6 +79,9 @@ def _run_pair(orc, g, K, d0, s0, levels=3, culls=2, n_streams=1, forced=True, up
             break
         agreed += 1
         assert int(dv.rng_position()[0]) == vo.rng_draws()
+        if i and not vo.last_was_keyframe():
+            matched += np.asarray(st["valid_updates"], np.uint64)
+        assert np.array_equal(dv.vo_matched(), matched), "frame %d: cumulative matched-pixel counter" % i
         n_kf += vo.last_was_keyframe(); n_upd += (not vo.last_was_keyframe())
         kf = vo.ref_frame()
         for s in range(n_streams):
