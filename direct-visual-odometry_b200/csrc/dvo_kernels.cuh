@@ -1122,7 +1122,13 @@ __device__ __forceinline__ float search_ssd(float s0, float s1, float s2, float 
     // implement.cpp:122-139: a tap that is invalid ends the accumulation with ssd = 2.0 * 3
     if (is_invalid(s0) || is_invalid(s1) || is_invalid(s2)) return 2.0f * 3;
     const float d0 = s0 - og, d1 = s1 - og, d2 = s2 - og;
-    float ssd = (float)__dadd_rn(0.0, __dmul_rn(1.0 * 1 / 3, (double)(d0 * d0))); // :134
+    // first term: (float)(0.0 + (double)(1/3) * (double)a), a = d0 * d0 >= 0, equals the correctly rounded float quotient a / 3 for
+    // EVERY non-negative finite float (a / 3 is never within 2^-27 relative of a float rounding boundary, the double product is within
+    // 2^-52 of it; checked exhaustively over all 2^31 bit patterns, tests/test_oracle_known_answers.py samples it).  a / 3 itself =
+    // Markstein's two-FMA correction of a * RN(1/3): three fp32 instructions instead of two conversions and two fp64 operations.
+    const float a0 = d0 * d0;
+    const float q0 = __fmul_rn(a0, 0.3333333432674407958984375f);
+    float ssd = __fmaf_rn(__fmaf_rn(-3.0f, q0, a0), 0.3333333432674407958984375f, q0); // :134
     ssd = (float)__dadd_rn((double)ssd, __dmul_rn(1.0 * 2 / 3, (double)(d1 * d1)));
     // third term: weight 3/3 = 1.0, i.e. (float)((double)ssd + (double)(d2 * d2)).  For two non-negative floats that equals the
     // float sum: the double sum is exact unless the exponents are > 29 bits apart, and then both roundings return ssd itself.

@@ -120,3 +120,16 @@ def test_mt19937_stream_and_distribution(orc):
     key = "dist" if "dist" in gold else [k for k in gold if k != "raw"][0]
     dist = np.array(gold[key], np.float32)
     assert np.array_equal(orc.dist_from_u32(raw[:len(dist)]), dist)
+
+
+def test_ssd_first_term_identity(tmp_path):
+    """search_ssd (csrc/dvo_kernels.cuh) evaluates implement.cpp:134's first term, (float)(0.0 + (1.0 * 1 / 3) * (double)(d * d)), as the
+    correctly rounded float quotient (d * d) / 3 through two FMAs.  tests/cpp/ssd_third.c compares the two forms bit for bit; here over
+    every 61st non-negative finite float bit pattern (stride 1 = all of them: 0 mismatches, ~20 s)."""
+    import subprocess
+    exe = str(tmp_path / "ssd_third")
+    src = os.path.join(os.path.dirname(os.path.abspath(__file__)), "cpp", "ssd_third.c")
+    subprocess.check_call(["gcc", "-O2", "-mfma", "-ffp-contract=off", "-o", exe, src, "-lm"])
+    out = subprocess.run([exe, "61"], capture_output=True, text=True, timeout=120)
+    n, bad = map(int, out.stdout.split())
+    assert out.returncode == 0 and bad == 0 and n > 30_000_000, out.stdout
