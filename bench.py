@@ -611,6 +611,15 @@ def main():
     ap.add_argument("--no-other-configs", action="store_true", help="skip the single-stream 1080p / 4K configurations (N = 1 only)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else max(args.warmup, 1)
+    # stdout carries exactly ONE line, the JSON: whatever native libraries print on file descriptor 1 meanwhile (NCCL's "NCCL version ..."
+    # banner ignores NCCL_DEBUG_FILE) is sent to stderr, and the line is written to the saved descriptor at the end
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(line):
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     config = dict(workload="C5/configs[1]: %d independent synthetic 640x480 sequences per GPU, full VO loop (track + propagate|update + "
@@ -627,7 +636,7 @@ def main():
         info["value"] = fps
         line = dict(base, impl="reference", value=fps, ms_per_step=ms_step, cpu_baseline=info, gpu_launches=0,
                     e2e=dict(value=fps, unit="frames/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
-        print(json.dumps(line), flush=True)
+        emit(line)
         return
 
     dist = None
@@ -659,7 +668,7 @@ def main():
         line = dict(base, impl="b200", **res)
         line["other_configs"] = other
         line["cpu_baseline"] = cpu
-        print(json.dumps(line), flush=True)
+        emit(line)
 
 
 if __name__ == "__main__":
