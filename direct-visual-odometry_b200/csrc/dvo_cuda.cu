@@ -57,6 +57,14 @@ struct dvo_ctx {
     uint16_t* d_kin_depth = nullptr; // [S][in_h][in_w]
     float* d_tmp = nullptr;
     uint32_t* d_rng = nullptr;
+    uint64_t rng_bound = 0;        // upper bound of any stream's replay position (grows by roi.n per Mapper::update; tightened on read-back)
+    ReadyQ* d_rq = nullptr;        // tracking -> Mapper::update hand-over of one frame
+    int* d_status = nullptr;       // first device-side error of any stream
+    int* h_status = nullptr;       // pinned: [0], [1] = status read back with pipeline buffer k's poses; [2] = synchronous pushes
+    bool overlap = true;           // k_map_update as a programmatic dependent of k_track (DVO_OVERLAP=0 disables)
+    bool fuse_prop = true;         // Implement::propagate in k_track's epilogue (DVO_FUSE_PROP=0: the two wide kernels)
+    bool fold_commit = false;      // Frame::updateDepth by k_regularize's last CTA (DVO_FOLD_COMMIT=1; measured slower than k_regularize_commit)
+    int status_pending[2] = {0, 0};
     float* d_stage_in = nullptr;   // [S][in_h][in_w]
     float* d_stage[3] = {nullptr, nullptr, nullptr}; // depth/sigma/age uploads, download staging
     float* d_small = nullptr;      // [S][64] small vectors (xi, poses)
@@ -72,6 +80,7 @@ struct dvo_ctx {
     std::vector<cudaEvent_t> k_ev;
     std::vector<int> k_ev_id;
     size_t k_ev_used = 0;
+    std::vector<cudaEvent_t> user_ev; // dvo_event_record / dvo_event_elapsed
     bool rows_only_staged = false; // d_stage_in holds only the sampled input rows (host path)
     // pipelined submission (dvo_vo_submit / dvo_vo_collect)
     cudaStream_t copy_stream = nullptr;
@@ -142,7 +151,12 @@ extern "C" void dvo_params_default(dvo_params* p)
 static int alloc_slot(dvo_ctx* ctx, int idx)
 {
     SlotHost& sh = ctx->slots[idx];
-    if (sh.base) return DVO_OK;
+    if (sh.base) {
+        // A recycled slot must not hand its previous occupant's depth / sigma / age / pose to the new Frame: the reference's
+        // Frame ctor starts from m_age = zeros and a fresh prior (frame.hpp:108-117).  Same state as a first allocation: all zero.
+        CK(cudaMemsetAsync(sh.base, 0, ctx->slot_bytes, ctx->stream));
+        return DVO_OK;
+    }
     CK(cudaMalloc(&sh.base, ctx->slot_bytes));
     CK(cudaMemsetAsync(sh.base, 0, ctx->slot_bytes, ctx->stream));
     char* p = (char*)sh.base;
@@ -191,6 +205,7 @@ extern "C" int dvo_create(dvo_ctx** out, const dvo_params* p)
         g.fx = Kb[0]; g.fy = Kb[1]; g.cx = Kb[2]; g.cy = Kb[3];
     }
     c.max_kf = p->max_keyframes;
+    c.kf_stride = (p->max_keyframes + 31) & ~31;
     c.vo_base = p->max_frames;
     c.max_iter = p->max_iterations;
     c.roi_level = p->roi_level; c.roi_x0 = p->roi_x0; c.roi_x1 = p->roi_x1; c.roi_y0 = p->roi_y0; c.roi_y1 = p->roi_y1;
@@ -201,6 +216,8 @@ extern "C" int dvo_create(dvo_ctx** out, const dvo_params* p)
     }
     c.sigma_lo = p->sigma_lo; c.sigma_hi = p->sigma_hi;
     c.step_default = p->step_default; c.step_level1 = p->step_level1; c.step_level2 = p->step_level2;
+    c.huber_delta = p->huber_delta > 0.0f ? p->huber_delta : 0.0f;
+    c.min_grad2 = p->min_gradient > 0.0f ? p->min_gradient * p->min_gradient : 0.0f;
     c.map_x0 = p->map_roi_x0; c.map_x1 = p->map_roi_x1; c.map_y0 = p->map_roi_y0; c.map_y1 = p->map_roi_y1;
     c.min_movement = p->min_movement; c.max_forward = p->max_forward;
     c.acc_d_lo = p->accept_depth_lo; c.acc_d_hi = p->accept_depth_hi; c.acc_s_hi = p->accept_sigma_hi;
@@ -225,8 +242,22 @@ extern "C" int dvo_create(dvo_ctx** out, const dvo_params* p)
     CK(cudaMalloc(&ctx->d_ms, sizeof(MapState) * S));
     CK(cudaMemset(ctx->d_ms, 0, sizeof(MapState) * S));
     CK(cudaMalloc(&ctx->d_vo, sizeof(VoState) * S));
-    CK(cudaMalloc(&ctx->d_hist, sizeof(int) * (size_t)S * c.max_kf));
-    CK(cudaMalloc(&ctx->d_tab, sizeof(PoseTab) * (size_t)S * c.max_kf));
+    CK(cudaMalloc(&ctx->d_hist, sizeof(int) * (size_t)S * c.kf_stride));
+    CK(cudaMalloc(&ctx->d_tab, sizeof(PoseTab) * (size_t)S * c.kf_stride));
+    CK(cudaMalloc(&ctx->d_rq, sizeof(ReadyQ) + sizeof(int) * (size_t)S));
+    CK(cudaMemset(ctx->d_rq, 0, sizeof(ReadyQ) + sizeof(int) * (size_t)S));
+    CK(cudaMalloc(&ctx->d_status, sizeof(int)));
+    CK(cudaMemset(ctx->d_status, 0, sizeof(int)));
+    CK(cudaMallocHost(&ctx->h_status, sizeof(int) * 4));
+    memset(ctx->h_status, 0, sizeof(int) * 4);
+    if (const char* e = getenv("DVO_OVERLAP")) ctx->overlap = atoi(e) != 0;
+    if (const char* e = getenv("DVO_FUSE_PROP")) ctx->fuse_prop = atoi(e) != 0;
+    if (const char* e = getenv("DVO_FOLD_COMMIT")) ctx->fold_commit = atoi(e) != 0;
+    for (int k = 0; k < 2; k++) { // pipeline events exist from the start: buffer 0 is d_stage_in, which the plain entry points use too
+        CK(cudaEventCreateWithFlags(&ctx->ev_copied[k], cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&ctx->ev_consumed[k], cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&ctx->ev_done[k], cudaEventDisableTiming));
+    }
     // Tracking launch shape: one CTA per stream when the streams alone fill the GPU; otherwise a
     // stream's pixels are split over B co-resident CTAs (cooperative launch, global barrier).
     {
@@ -303,14 +334,17 @@ extern "C" void dvo_destroy(dvo_ctx* ctx)
     cudaFree(ctx->d_blockcnt); cudaFree(ctx->d_winner); cudaFree(ctx->d_remap);
     cudaFree(ctx->d_kin_cidx); cudaFree(ctx->d_kin_didx); cudaFree(ctx->d_kin_color); cudaFree(ctx->d_kin_depth); cudaFree(ctx->d_tmp); cudaFree(ctx->d_rng); cudaFree(ctx->d_stage_in);
     for (int k = 0; k < 3; k++) cudaFree(ctx->d_stage[k]);
-    cudaFree(ctx->d_small); cudaFree(ctx->d_ismall); cudaFree(ctx->d_forced);
+    cudaFree(ctx->d_small); cudaFree(ctx->d_ismall); cudaFree(ctx->d_forced); cudaFree(ctx->d_rq); cudaFree(ctx->d_status);
     if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
+    if (ctx->h_status) cudaFreeHost(ctx->h_status);
     if (ctx->copy_stream) {
         cudaStreamSynchronize(ctx->copy_stream);
         cudaFree(ctx->d_stage_pp[1]);
-        for (int k = 0; k < 2; k++) { cudaEventDestroy(ctx->ev_copied[k]); cudaEventDestroy(ctx->ev_consumed[k]); cudaEventDestroy(ctx->ev_done[k]); }
         cudaStreamDestroy(ctx->copy_stream);
     }
+    for (int k = 0; k < 2; k++)
+        if (ctx->ev_copied[k]) { cudaEventDestroy(ctx->ev_copied[k]); cudaEventDestroy(ctx->ev_consumed[k]); cudaEventDestroy(ctx->ev_done[k]); }
+    for (auto e : ctx->user_ev) if (e) cudaEventDestroy(e);
     for (auto e : ctx->k_ev) cudaEventDestroy(e);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -401,15 +435,21 @@ static int build_frame(dvo_ctx* ctx, int slot, const float* gray_dev, bool rows_
     const VoState* vo = slot < 0 ? ctx->d_vo : nullptr;
     const LevelGeom& gt = c.lv[c.L - 1];
     dim3 grid(cdiv(gt.n, 1024), c.S);
-    KTimer t(ctx, K_CULL);
-    if (kind == 2)
-        k_cull_bgr8<<<dim3(cdiv(gt.n, 256), c.S), 256, 0, ctx->stream>>>(c, (const uint8_t*)gray_dev, aux, ctx->d_remap, ctx->d_slots, slot, vo);
-    else if (kind == 1)
-        k_cull_gray8<<<grid, 256, 0, ctx->stream>>>(c, (const uint8_t*)gray_dev, rows_only ? gt.h : c.in_h, rows_only ? 0 : c.culls,
-                                                    aux, ctx->d_slots, slot, vo);
-    else
-        k_cull_gray<<<grid, 256, 0, ctx->stream>>>(c, gray_dev, rows_only ? gt.h : c.in_h, rows_only ? 0 : c.culls, ctx->d_slots, slot, vo);
-    KCHECK();
+    ReadyQ* rq = vo ? ctx->d_rq : nullptr; // the VO frame's first kernel clears the tracking -> mapping hand-over queue
+    {
+        KTimer t(ctx, K_CULL);
+        if (kind == 2)
+            k_cull_bgr8<<<dim3(cdiv(gt.n, 256), c.S), 256, 0, ctx->stream>>>(c, (const uint8_t*)gray_dev, aux, ctx->d_remap, ctx->d_slots, slot, vo, rq);
+        else if (kind == 1)
+            k_cull_gray8<<<grid, 256, 0, ctx->stream>>>(c, (const uint8_t*)gray_dev, rows_only ? gt.h : c.in_h, rows_only ? 0 : c.culls,
+                                                        aux, ctx->d_slots, slot, vo, rq);
+        else
+            k_cull_gray<<<grid, 256, 0, ctx->stream>>>(c, gray_dev, rows_only ? gt.h : c.in_h, rows_only ? 0 : c.culls, ctx->d_slots, slot, vo, rq);
+        KCHECK();
+    }
+    // d_stage_in doubles as pipeline buffer 0: whoever filled it (dvo_frame_create*, dvo_vo_push*), a later dvo_vo_submit must not
+    // overwrite it on the copy stream before this kernel has read it
+    if ((const void*)gray_dev == (const void*)ctx->d_stage_in) CK(cudaEventRecord(ctx->ev_consumed[0], ctx->stream));
     return DVO_OK;
 }
 
@@ -664,6 +704,110 @@ extern "C" int dvo_visualize_image(int kind, const float* src, const float* aux,
     return ok ? DVO_OK : DVO_ERR_CUDA;
 }
 
+// ---- scalar geometry and the depth filter of the reference's boundary, host arithmetic ---------------------------------------
+// Compiled here once (x86-64 baseline: no FMA contraction) so that callers' own compiler flags cannot change the rounding.
+extern "C" int dvo_transform_point(const float T[16], const float x[3], float out[3])
+{   // Transform::transform, transform.cpp:7-12: R x + t, fp32 left to right
+    if (!T || !x || !out) return DVO_ERR_ARG;
+    const volatile float X = x[0], Y = x[1], Z = x[2];
+    for (int r = 0; r < 3; r++) {
+        volatile float a = T[r * 4 + 0] * X; volatile float b = T[r * 4 + 1] * Y; volatile float c2 = T[r * 4 + 2] * Z;
+        volatile float s = a + b; s = s + c2;
+        out[r] = s + T[r * 4 + 3];
+    }
+    return DVO_OK;
+}
+extern "C" int dvo_project_point(const float K[9], const float p[3], float out[2])
+{   // Transform::project, transform.cpp:20-23
+    if (!K || !p || !out) return DVO_ERR_ARG;
+    volatile float a = p[0] * K[0]; a = a / p[2]; out[0] = a + K[2];
+    volatile float b = p[1] * K[4]; b = b / p[2]; out[1] = b + K[5];
+    return DVO_OK;
+}
+extern "C" int dvo_back_project_point(const float K[9], const float xy[2], float depth, float out[3])
+{   // Transform::backProject, transform.cpp:25-28
+    if (!K || !xy || !out) return DVO_ERR_ARG;
+    volatile float a = xy[0] - K[2]; a = depth * a; out[0] = a / K[0];
+    volatile float b = xy[1] - K[5]; b = depth * b; out[1] = b / K[4];
+    out[2] = depth;
+    return DVO_OK;
+}
+namespace {
+std::mt19937 g_gauss_engine; // the file-scope engine of src/math/gaussian.cpp:8 for the host-side math::Gaussian
+bool gaussian_gate(float depth, float sigma, float d, float s, float& v1, float& v2, float& v)
+{
+    volatile float a = sigma * sigma, b = s * s;
+    v1 = a; v2 = b;
+    volatile float sum = a + b;
+    v = sum;
+    const float diff = std::fabs(d - depth);
+    const float m = d < diff ? d : diff;
+    volatile float q = m / 0.8f; q = q * 0.5f;
+    const float gain = ((double)m < 0.8) ? 0.5f + q : 1.0f;
+    const float mx = sigma < s ? s : sigma;
+    volatile float lim = gain * mx;
+    return !(diff > lim);
+}
+void gaussian_merge(float& depth, float& sigma, float d, float v1, float v2, float v)
+{
+    volatile float a = v2 * depth, b = v1 * d;
+    volatile float num = a + b;
+    depth = num / v;
+    volatile float p = v1 * v2; p = p / v;
+    sigma = std::sqrt(p);
+}
+} // namespace
+extern "C" int dvo_gaussian_fuse(float* depth, float* sigma, float d, float s)
+{   // Gaussian::operator(), gaussian.cpp:33-50: 1 = fused, 0 = refused (state untouched)
+    if (!depth || !sigma) return DVO_ERR_ARG;
+    float v1, v2, v;
+    if (!gaussian_gate(*depth, *sigma, d, s, v1, v2, v)) return 0;
+    gaussian_merge(*depth, *sigma, d, v1, v2, v);
+    return 1;
+}
+extern "C" int dvo_gaussian_update(float* depth, float* sigma, float d, float s)
+{   // Gaussian::update, gaussian.cpp:12-31: a refused observation resets the hypothesis from the process-wide mt19937
+    if (!depth || !sigma) return DVO_ERR_ARG;
+    float v1, v2, v;
+    if (!gaussian_gate(*depth, *sigma, d, s, v1, v2, v)) {
+        // libstdc++ uniform_real_distribution<float>(2.0, 0.5): one 32-bit draw, (raw * 2^-32) * (0.5 - 2.0) + 2.0
+        volatile float u = (float)(uint32_t)g_gauss_engine() / 4294967296.0f;
+        if (u >= 1.0f) u = 0.99999994f;
+        volatile float r = u * (0.5f - 2.0f); r = r + 2.0f;
+        *depth = 4.0f < r ? 4.0f : r;
+        *sigma = 0.5f;
+        return 0;
+    }
+    gaussian_merge(*depth, *sigma, d, v1, v2, v);
+    return 1;
+}
+extern "C" void dvo_gaussian_reseed(void) { g_gauss_engine = std::mt19937(); }
+
+// Transform::mapDepthtoGray on raw host images (no context: temporary device buffers)
+extern "C" int dvo_map_depth_to_gray(const float* depth, int w, int h, const float* gray, int gw, int gh, const float rgb_K[9],
+                                     const float depth_K[9], const float invT[16], float* mapped, float* sigma)
+{
+    if (!depth || !gray || !rgb_K || !depth_K || !invT || !mapped || !sigma || w <= 0 || h <= 0 || gw <= 0 || gh <= 0) return DVO_ERR_ARG;
+    MapD2G P;
+    P.w = w; P.h = h; P.gw = gw; P.gh = gh;
+    P.dfx = depth_K[0]; P.dfy = depth_K[4]; P.dcx = depth_K[2]; P.dcy = depth_K[5];
+    P.fx = rgb_K[0]; P.fy = rgb_K[4]; P.cx = rgb_K[2]; P.cy = rgb_K[5];
+    for (int r = 0; r < 3; r++)
+        for (int q = 0; q < 4; q++) P.T[r * 4 + q] = invT[r * 4 + q];
+    const size_t n = (size_t)w * h, gn = (size_t)gw * gh;
+    float *d_d = nullptr, *d_g = nullptr, *d_m = nullptr, *d_s = nullptr;
+    bool ok = cudaMalloc(&d_d, n * 4) == cudaSuccess && cudaMalloc(&d_g, gn * 4) == cudaSuccess && cudaMalloc(&d_m, n * 4) == cudaSuccess &&
+              cudaMalloc(&d_s, n * 4) == cudaSuccess;
+    if (ok) ok = cudaMemcpy(d_d, depth, n * 4, cudaMemcpyHostToDevice) == cudaSuccess && cudaMemcpy(d_g, gray, gn * 4, cudaMemcpyHostToDevice) == cudaSuccess;
+    if (ok) {
+        k_map_depth_to_gray<<<(unsigned)((n + 255) / 256), 256>>>(P, d_d, d_g, d_m, d_s);
+        ok = cudaGetLastError() == cudaSuccess && cudaMemcpy(mapped, d_m, n * 4, cudaMemcpyDeviceToHost) == cudaSuccess &&
+             cudaMemcpy(sigma, d_s, n * 4, cudaMemcpyDeviceToHost) == cudaSuccess;
+    }
+    cudaFree(d_d); cudaFree(d_g); cudaFree(d_m); cudaFree(d_s);
+    return ok ? DVO_OK : DVO_ERR_CUDA;
+}
+
 // ---- headless outputs: host side ----------------------------------------------------------------
 extern "C" int dvo_inverse_pose(const float T[16], float out[16])
 {
@@ -807,6 +951,7 @@ static int launch_track(dvo_ctx* ctx, TrackArgs a)
     a.st = ctx->d_ts; a.partials = ctx->d_partials; a.B = ctx->trk_B;
     a.log = ctx->d_log; a.log_cap = ctx->log_cap;
     a.slots = ctx->d_slots;
+    a.status = ctx->d_status;
     dim3 grid(ctx->trk_B, c.S);
     KTimer t(ctx, K_TRACK);
     if (ctx->trk_B > 1) { // CTAs of a stream meet at a global barrier: they must be co-resident
@@ -916,7 +1061,7 @@ extern "C" int dvo_gn_step(dvo_ctx* ctx, int obj_slot, int ref_slot, int level, 
 }
 
 static int enqueue_track(dvo_ctx* ctx, int obj_slot, int ref_slot, bool use_vo, double stop_update, float stop_residual, int frame_id,
-                         const float* forced_rel)
+                         const float* forced_rel, float* T_out_dev = nullptr, bool overlapped = false, bool fused_propagate = false)
 {
     if (stop_update < 0) stop_update = (double)ctx->P.min_update; // cv::norm(...) < MINIMUM_UPDATE: float promoted
     if (stop_residual < 0) stop_residual = ctx->P.min_residual;
@@ -926,6 +1071,9 @@ static int enqueue_track(dvo_ctx* ctx, int obj_slot, int ref_slot, bool use_vo, 
     if (use_vo) {
         a.vo = ctx->d_vo; a.ms = ctx->d_ms; a.hist = ctx->d_hist; a.tab = ctx->d_tab;
         a.frame_id = frame_id; a.forced_rel = forced_rel;
+        a.T_out = T_out_dev;
+        a.rq = overlapped ? ctx->d_rq : nullptr;
+        a.winner = fused_propagate ? ctx->d_winner : nullptr;
     }
     return launch_track(ctx, a);
 }
@@ -967,8 +1115,14 @@ __global__ void k_map_config(Consts c, MapState* mst, int ref_slot, int obj_slot
 __global__ void k_hist_fill(Consts c, int* hist, const int* list, int n)
 {
     const int s = blockIdx.x;
-    for (int k = threadIdx.x; k < n; k += blockDim.x) hist[(size_t)s * c.max_kf + k] = list[k];
+    for (int k = threadIdx.x; k < n; k += blockDim.x) hist[(size_t)s * c.kf_stride + k] = list[k];
 }
+
+// Levels up to this many pixels take the fused forms: Implement::propagate in k_track's epilogue (one CTA per stream) and
+// Frame::updateDepth in k_regularize's last CTA (one CTA copies the stream's whole level).  Larger levels (1080p, 4K single
+// streams) keep the wide two-kernel forms.
+static const int FUSE_MAX_PIXELS = 64 * 1024;
+static bool small_level(const dvo_ctx* ctx) { return ctx->c.lv[ctx->c.L - 1].n <= FUSE_MAX_PIXELS; }
 
 static int enqueue_propagate(dvo_ctx* ctx)
 {
@@ -987,9 +1141,38 @@ static int enqueue_propagate(dvo_ctx* ctx)
     }
     return DVO_OK;
 }
+
+// mt19937 replay table (src/math/gaussian.cpp:8-9): the reference's engine is unbounded, so the table grows on demand.  Every
+// Mapper::update can consume at most roi.n draws per stream; `rng_bound` bounds every stream's position from above.
+static int rng_reserve(dvo_ctx* ctx)
+{
+    Consts& c = ctx->c;
+    const uint64_t need = ctx->rng_bound + (uint64_t)(ctx->roi.n > 0 ? ctx->roi.n : 0);
+    ctx->rng_bound = need;
+    if (need <= (uint64_t)c.rng_table) return DVO_OK;
+    uint64_t len = (uint64_t)c.rng_table * 2;
+    while (len < need) len *= 2;
+    if (len > 0xffffffffull) {
+        ctx->err = "mt19937 replay table would exceed 2^32 draws";
+        return DVO_ERR_RNG;
+    }
+    std::vector<uint32_t> tail((size_t)(len - c.rng_table));
+    for (auto& v : tail) v = (uint32_t)ctx->engine(); // the host engine continues where the table ends
+    uint32_t* d_new = nullptr;
+    CK(cudaMalloc(&d_new, sizeof(uint32_t) * (size_t)len));
+    CK(cudaStreamSynchronize(ctx->stream)); // kernels in flight still read the old table
+    CK(cudaMemcpy(d_new, ctx->d_rng, sizeof(uint32_t) * (size_t)c.rng_table, cudaMemcpyDeviceToDevice));
+    CK(cudaMemcpy(d_new + c.rng_table, tail.data(), sizeof(uint32_t) * tail.size(), cudaMemcpyHostToDevice));
+    cudaFree(ctx->d_rng);
+    ctx->d_rng = d_new;
+    c.rng_table = (unsigned int)len;
+    return DVO_OK;
+}
+
 // tables: the granular entry point computes Mapper::update's pose table here; in the VO loop the
-// tracking kernel's epilogue already did.
-static int enqueue_update(dvo_ctx* ctx, bool tables)
+// tracking kernel's epilogue already did.  overlapped: launched as a programmatic dependent of the k_track launch right before
+// it, so that its CTAs start on whatever the tracking kernel leaves free and serve streams in tracking-completion order.
+static int enqueue_update(dvo_ctx* ctx, bool tables, bool overlapped)
 {
     const Consts& c = ctx->c;
     if (tables) {
@@ -1001,13 +1184,24 @@ static int enqueue_update(dvo_ctx* ctx, bool tables)
     dim3 grid(ctx->roi.nblk, c.S);
     {
         KTimer t(ctx, K_MAP_UPDATE);
-        k_map_update<<<grid, MAPU_THREADS, 0, ctx->stream>>>(c, ctx->roi, ctx->d_slots, ctx->d_ms, ctx->d_hist, ctx->d_tab, ctx->d_flags, ctx->d_blockcnt);
-        KCHECK();
+        if (overlapped) {
+            cudaLaunchConfig_t cfg{};
+            cfg.gridDim = grid; cfg.blockDim = dim3(MAPU_THREADS); cfg.dynamicSmemBytes = 0; cfg.stream = ctx->stream;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            at[0].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = at; cfg.numAttrs = 1;
+            CK(cudaLaunchKernelEx(&cfg, k_map_update, c, ctx->roi, (const SlotDev*)ctx->d_slots, ctx->d_ms, (const int*)ctx->d_hist,
+                                  (const PoseTab*)ctx->d_tab, ctx->d_flags, ctx->d_blockcnt, ctx->d_rq, ctx->d_status));
+            ctx->launches++;
+        } else {
+            k_map_update<<<grid, MAPU_THREADS, 0, ctx->stream>>>(c, ctx->roi, ctx->d_slots, ctx->d_ms, ctx->d_hist, ctx->d_tab, ctx->d_flags,
+                                                                ctx->d_blockcnt, nullptr, ctx->d_status);
+            KCHECK();
+        }
     }
     {
         KTimer t(ctx, K_MAP_APPLY);
-        k_map_scan<<<c.S, 256, 0, ctx->stream>>>(c, ctx->roi, ctx->d_ms, ctx->d_blockcnt);
-        KCHECK();
         dim3 agrid(cdiv(ctx->roi.nblk, APPLY_SUB), c.S);
         k_map_update_apply<<<agrid, MAPU_THREADS * APPLY_SUB, 0, ctx->stream>>>(c, ctx->roi, ctx->d_slots, ctx->d_ms, ctx->d_flags,
                                                                                  ctx->d_blockcnt, ctx->d_rng);
@@ -1019,12 +1213,13 @@ static int enqueue_regularize(dvo_ctx* ctx)
 {
     const Consts& c = ctx->c;
     const int ntop = c.lv[c.L - 1].n;
+    const bool fold = ctx->fold_commit && small_level(ctx);
     {
         KTimer t(ctx, K_REGULARIZE);
-        k_regularize<<<dim3(cdiv(ntop, 256), c.S), 256, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ms, ctx->d_tmp);
+        k_regularize<<<dim3(cdiv(ntop, 256), c.S), 256, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ms, ctx->d_tmp, fold ? 1 : 0);
         KCHECK();
     }
-    {
+    if (!fold) {
         KTimer t(ctx, K_REG_COMMIT);
         k_regularize_commit<<<dim3(cdiv(ntop, 512), c.S), 256, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ms, ctx->d_tmp);
         KCHECK();
@@ -1039,6 +1234,11 @@ static int map_error(dvo_ctx* ctx)
     if (sizeof(MapState) * (size_t)c.S > ctx->h_pinned_bytes) return DVO_OK;
     CK(cudaMemcpyAsync(hm, ctx->d_ms, sizeof(MapState) * (size_t)c.S, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    {   // nothing is in flight: the replay-table bound becomes the furthest actual position
+        uint64_t mx = 0;
+        for (int s = 0; s < c.S; s++) mx = hm[s].rng_pos > mx ? hm[s].rng_pos : mx;
+        ctx->rng_bound = mx;
+    }
     for (int s = 0; s < c.S; s++)
         if (hm[s].err) {
             ctx->err = hm[s].err == DVO_ERR_HISTORY ? "age >= history size (FrameHistory::operator[] would throw)" : "mt19937 replay table exhausted";
@@ -1090,7 +1290,9 @@ extern "C" int dvo_map_update(dvo_ctx* ctx, int obj_slot, int ref_slot, const in
     KCHECK();
     k_map_prepare<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_ms, ctx->slots[obj_slot].dev.rel_xi);
     KCHECK();
-    rc = enqueue_update(ctx, true); // ref->updateDepthSigma (mapper.cpp:135) is implicit: coarser levels are views
+    rc = rng_reserve(ctx);
+    if (rc) return rc;
+    rc = enqueue_update(ctx, true, false); // ref->updateDepthSigma (mapper.cpp:135) is implicit: coarser levels are views
     if (rc) return rc;
     const int ntop = c.lv[c.L - 1].n;
     if (mask) CK(cudaMemcpyAsync(mask, ctx->d_flags, (size_t)c.S * ntop, cudaMemcpyDeviceToHost, ctx->stream));
@@ -1181,27 +1383,57 @@ extern "C" int dvo_se3_log(dvo_ctx* ctx, const float* T, float* xi, int n) { ret
 extern "C" int dvo_se3_concatenate(dvo_ctx* ctx, const float* a, const float* b, float* out, int n) { return se3_op(ctx, 2, a, 6, b, out, 6, n); }
 
 // ---- mask compaction ------------------------------------------------------------------------
+// mask [S][n] on the device -> idx [S][n], count [S]; scratch from the context (d_blockcnt is sized for roi.nblk CTAs of 64, so the
+// compaction keeps its own)
+static int compact_device(dvo_ctx* ctx, const uint8_t* d_mask, int S, int n, int32_t* d_idx, int* d_total)
+{
+    const int nb = cdiv(n, 256);
+    DevScratch sc;
+    CK(cudaMalloc(&sc.p, sizeof(unsigned) * (size_t)S * nb));
+    unsigned int* d_c = (unsigned int*)sc.p;
+    k_compact_count<<<dim3(nb, S), 256, 0, ctx->stream>>>(d_mask, n, d_c);
+    KCHECK();
+    k_compact_scan<<<S, 256, 0, ctx->stream>>>(nb, d_c, d_total);
+    KCHECK();
+    k_compact_scatter<<<dim3(nb, S), 256, 0, ctx->stream>>>(d_mask, n, d_c, d_idx);
+    KCHECK();
+    CK(cudaStreamSynchronize(ctx->stream));
+    return DVO_OK;
+}
+
 extern "C" int dvo_mask_compact(dvo_ctx* ctx, const uint8_t* mask, int n, int32_t* idx, int* count)
 {
     ARG(mask && idx && count && n > 0, "bad argument");
-    uint8_t* d_m = nullptr;
-    int32_t* d_i = nullptr;
-    unsigned int* d_c = nullptr;
-    const int nb = cdiv(n, 256);
-    CK(cudaMalloc(&d_m, n));
-    CK(cudaMalloc(&d_i, sizeof(int32_t) * (size_t)n));
-    CK(cudaMalloc(&d_c, sizeof(unsigned) * (size_t)(nb + 1)));
-    CK(cudaMemcpyAsync(d_m, mask, n, cudaMemcpyHostToDevice, ctx->stream));
-    k_compact_count<<<nb, 256, 0, ctx->stream>>>(d_m, n, d_c);
+    DevScratch m, i, t;
+    CK(cudaMalloc(&m.p, n));
+    CK(cudaMalloc(&i.p, sizeof(int32_t) * (size_t)n));
+    CK(cudaMalloc(&t.p, sizeof(int)));
+    CK(cudaMemcpyAsync(m.p, mask, n, cudaMemcpyHostToDevice, ctx->stream));
+    int rc = compact_device(ctx, (const uint8_t*)m.p, 1, n, (int32_t*)i.p, (int*)t.p);
+    if (rc) return rc;
+    int total = 0;
+    CK(cudaMemcpy(&total, t.p, sizeof(int), cudaMemcpyDeviceToHost));
+    if (total) CK(cudaMemcpy(idx, i.p, sizeof(int32_t) * (size_t)total, cudaMemcpyDeviceToHost));
+    *count = total;
+    return DVO_OK;
+}
+
+extern "C" int dvo_select_pixels(dvo_ctx* ctx, int slot, int level, float min_gradient, int32_t* idx, int* count)
+{
+    int rc = check_slot(ctx, slot);
+    if (rc) return rc;
+    const Consts& c = ctx->c;
+    ARG(level >= 0 && level < c.L && idx && count && min_gradient >= 0.0f, "bad argument");
+    const LevelGeom& g = c.lv[level];
+    DevScratch i, t;
+    CK(cudaMalloc(&i.p, sizeof(int32_t) * (size_t)c.S * g.n));
+    CK(cudaMalloc(&t.p, sizeof(int) * (size_t)c.S));
+    k_select_mask<<<dim3(cdiv(g.n, 256), c.S), 256, 0, ctx->stream>>>(c, ctx->slots[slot].dev, level, min_gradient * min_gradient, ctx->d_mask);
     KCHECK();
-    k_compact_scatter<<<nb, 256, 0, ctx->stream>>>(d_m, n, d_c, d_i, d_c + nb);
-    KCHECK();
-    unsigned int total = 0;
-    CK(cudaMemcpyAsync(&total, d_c + nb, sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaStreamSynchronize(ctx->stream));
-    if (total) CK(cudaMemcpy(idx, d_i, sizeof(int32_t) * (size_t)total, cudaMemcpyDeviceToHost));
-    *count = (int)total;
-    cudaFree(d_m); cudaFree(d_i); cudaFree(d_c);
+    rc = compact_device(ctx, ctx->d_mask, c.S, g.n, (int32_t*)i.p, (int*)t.p);
+    if (rc) return rc;
+    CK(cudaMemcpy(count, t.p, sizeof(int) * (size_t)c.S, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(idx, i.p, sizeof(int32_t) * (size_t)c.S * g.n, cudaMemcpyDeviceToHost));
     return DVO_OK;
 }
 
@@ -1212,15 +1444,21 @@ __global__ void k_vo_reset(Consts c, VoState* vo, MapState* mst)
     if (s >= c.S) return;
     vo[s].kf_slot = -1; vo[s].kf_frame_id = -1; vo[s].n_kf = 0; vo[s].need_new = 0; vo[s].was_keyframe = 0; vo[s].n_iters = 0; vo[s].cur_slot = c.vo_base;
     vo[s].gn_iters = 0; vo[s].gn_pixels = 0; vo[s].n_propagate = 0; vo[s].n_update = 0; vo[s].map_matched = 0;
-    mst[s].rng_pos = 0; mst[s].err = 0; mst[s].valid_update = 0; mst[s].ticket = 0;
+    mst[s].rng_pos = 0; mst[s].err = 0; mst[s].valid_update = 0; mst[s].ticket = 0; mst[s].ticket_a = 0; mst[s].ticket_r = 0;
 }
 
 extern "C" int dvo_vo_reset(dvo_ctx* ctx)
 {
     const Consts& c = ctx->c;
     for (auto& s : ctx->slots) s.in_use = false;
+    // a new sequence starts from fresh frames: no map, age or pose of the previous run may survive in the keyframe pool
+    for (size_t k = (size_t)c.vo_base; k < ctx->slots.size(); k++)
+        if (ctx->slots[k].base) CK(cudaMemsetAsync(ctx->slots[k].base, 0, ctx->slot_bytes, ctx->stream));
     ctx->vo_frame_id = -1;
     ctx->forced_pending = false;
+    ctx->rng_bound = 0;
+    CK(cudaMemsetAsync(ctx->d_status, 0, sizeof(int), ctx->stream));
+    memset(ctx->h_status, 0, sizeof(int) * 4);
     k_vo_reset<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_vo, ctx->d_ms);
     KCHECK();
     return DVO_OK;
@@ -1255,8 +1493,16 @@ extern "C" int dvo_vo_force_pose(dvo_ctx* ctx, const float* rel_xi)
 
 // One odometrize for every stream, enqueued on the context's stream.  after_cull (nullable) is recorded
 // once the staging buffer has been consumed; sync_out = false leaves the pose read-back asynchronous.
+static int status_error(dvo_ctx* ctx, int code)
+{
+    ctx->err = code == DVO_ERR_HISTORY ? "a stream ran out of keyframe capacity (dvo_params.max_keyframes) or met an age >= history size: "
+                                         "it is tracked but no longer mapped"
+                                       : "device-side error";
+    return code;
+}
+
 static int vo_push_impl(dvo_ctx* ctx, const float* gray_dev, const float* init_depth, const float* init_sigma, float* T_out,
-                        cudaEvent_t after_cull, bool sync_out, int kind = 0, int aux = -1)
+                        cudaEvent_t after_cull, bool sync_out, int kind = 0, int aux = -1, int status_slot = 2)
 {
     const Consts& c = ctx->c;
     ARG(gray_dev, "null gray");
@@ -1275,6 +1521,13 @@ static int vo_push_impl(dvo_ctx* ctx, const float* gray_dev, const float* init_d
             sh.in_use = true;
         }
     }
+    if (frame_id == 0 && !init_depth) {
+        // Scene's ctor draws the first keyframe's depth from cv::randn and sets sigma = 0.5 (frame.hpp:18-21); that prior is an INPUT
+        // here.  Without it every pixel fails optimize's depth gate and tracking would silently return identities.
+        ctx->vo_frame_id = -1;
+        ctx->err = "the first frame of a sequence needs init_depth (use dvo_vo_push* for frame 0; dvo_vo_submit* carries no prior)";
+        return DVO_ERR_STATE;
+    }
     int rc = build_frame(ctx, -1, gray_dev, ctx->rows_only_staged, kind, aux); // make_shared<Frame>(gray, K, 3, 2), system.hpp:47
     ctx->rows_only_staged = false;
     if (rc) return rc;
@@ -1283,25 +1536,37 @@ static int vo_push_impl(dvo_ctx* ctx, const float* gray_dev, const float* init_d
         rc = set_depth_impl(ctx, -1, init_depth, init_sigma, nullptr, 0);
         if (rc) return rc;
     }
+    const bool fused = ctx->fuse_prop && small_level(ctx) && ctx->trk_B == 1;   // propagate in the tracking kernel's epilogue
+    const bool overlapped = ctx->overlap && ctx->trk_B == 1 && !ctx->ktiming;   // per-kernel timing needs the launches apart
+    if (frame_id > 0) {
+        rc = rng_reserve(ctx); // before the launches: Mapper::update must follow the tracking kernel back to back
+        if (rc) return rc;
+    }
     // Tracking (system.hpp:57) against each stream's current keyframe (no-op on the first frame), then
-    // Frame::updateXi + Mapper::needNewFrame + setRefFrame in the same kernel's epilogue
-    rc = enqueue_track(ctx, -1, -1, true, -1.0, -1.0f, frame_id, ctx->forced_pending ? ctx->d_forced : nullptr);
+    // Frame::updateXi + Mapper::needNewFrame + setRefFrame (+ propagate, + odometrize's return value) in the same kernel's epilogue
+    rc = enqueue_track(ctx, -1, -1, true, -1.0, -1.0f, frame_id, ctx->forced_pending ? ctx->d_forced : nullptr, T_out ? ctx->d_small : nullptr,
+                       overlapped && frame_id > 0, fused);
     if (rc) return rc;
     ctx->forced_pending = false;
     // Mapping (system.hpp:67, mapper.cpp:16-33): per stream either propagate or update, then regularize
     if (frame_id > 0) {
-        rc = enqueue_propagate(ctx);
+        rc = enqueue_update(ctx, false, overlapped);
         if (rc) return rc;
-        rc = enqueue_update(ctx, false);
-        if (rc) return rc;
+        if (!fused) {
+            rc = enqueue_propagate(ctx); // update and propagate touch disjoint streams: their order is free
+            if (rc) return rc;
+        }
         rc = enqueue_regularize(ctx);
         if (rc) return rc;
     }
     if (T_out) {
-        k_pose_out<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_vo, ctx->d_small);
-        KCHECK();
+        // device-side errors (history overflow) come back with the poses: checked here when synchronous, in dvo_vo_collect otherwise
+        CK(cudaMemcpyAsync(ctx->h_status + status_slot, ctx->d_status, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
         CK(cudaMemcpyAsync(T_out, ctx->d_small, sizeof(float) * 16 * (size_t)c.S, cudaMemcpyDeviceToHost, ctx->stream));
-        if (sync_out) CK(cudaStreamSynchronize(ctx->stream));
+        if (sync_out) {
+            CK(cudaStreamSynchronize(ctx->stream));
+            if (ctx->h_status[status_slot]) return status_error(ctx, ctx->h_status[status_slot]);
+        }
     }
     return DVO_OK;
 }
@@ -1311,6 +1576,13 @@ extern "C" int dvo_vo_push_dev(dvo_ctx* ctx, const float* gray_dev, const float*
     return vo_push_impl(ctx, gray_dev, init_depth, init_sigma, T_out, nullptr, true);
 }
 
+extern "C" int dvo_vo_push_gray8_dev(dvo_ctx* ctx, const uint8_t* gray8_dev, int invalid_code, const float* init_depth,
+                                     const float* init_sigma, float* T_out)
+{
+    ARG(gray8_dev && invalid_code >= -1 && invalid_code <= 255, "bad argument");
+    return vo_push_impl(ctx, (const float*)gray8_dev, init_depth, init_sigma, T_out, nullptr, true, 1, invalid_code);
+}
+
 extern "C" int dvo_vo_push(dvo_ctx* ctx, const float* gray, const float* init_depth, const float* init_sigma, float* T_out)
 {
     ARG(gray, "null gray");
@@ -1318,8 +1590,7 @@ extern "C" int dvo_vo_push(dvo_ctx* ctx, const float* gray, const float* init_de
     int rc = stage_gray(ctx, gray, &rows_only);
     if (rc) return rc;
     ctx->rows_only_staged = rows_only;
-    // d_stage_in doubles as pipeline buffer 0: tell a later dvo_vo_submit when this frame has consumed it
-    return vo_push_impl(ctx, ctx->d_stage_in, init_depth, init_sigma, T_out, ctx->copy_stream ? ctx->ev_consumed[0] : nullptr, true);
+    return vo_push_impl(ctx, ctx->d_stage_in, init_depth, init_sigma, T_out, nullptr, true);
 }
 
 extern "C" int dvo_vo_push_gray8(dvo_ctx* ctx, const uint8_t* gray8, int invalid_code, const float* init_depth, const float* init_sigma,
@@ -1330,8 +1601,7 @@ extern "C" int dvo_vo_push_gray8(dvo_ctx* ctx, const uint8_t* gray8, int invalid
     int rc = stage_gray_to(ctx, ctx->d_stage_in, ctx->stream, gray8, &rows_only, 1);
     if (rc) return rc;
     ctx->rows_only_staged = rows_only;
-    return vo_push_impl(ctx, ctx->d_stage_in, init_depth, init_sigma, T_out, ctx->copy_stream ? ctx->ev_consumed[0] : nullptr, true, 1,
-                        invalid_code);
+    return vo_push_impl(ctx, ctx->d_stage_in, init_depth, init_sigma, T_out, nullptr, true, 1, invalid_code);
 }
 
 extern "C" int dvo_vo_push_bgr8(dvo_ctx* ctx, const uint8_t* bgr8, int channels, const float* init_depth, const float* init_sigma,
@@ -1340,8 +1610,7 @@ extern "C" int dvo_vo_push_bgr8(dvo_ctx* ctx, const uint8_t* bgr8, int channels,
     int rc = stage_bgr(ctx, ctx->d_stage_in, ctx->stream, bgr8, channels);
     if (rc) return rc;
     ctx->rows_only_staged = false;
-    return vo_push_impl(ctx, ctx->d_stage_in, init_depth, init_sigma, T_out, ctx->copy_stream ? ctx->ev_consumed[0] : nullptr, true, 2,
-                        channels);
+    return vo_push_impl(ctx, ctx->d_stage_in, init_depth, init_sigma, T_out, nullptr, true, 2, channels);
 }
 
 // Pipelined submission: two staging buffers filled on a copy stream, so frame n+1 crosses PCIe while
@@ -1357,11 +1626,6 @@ static int pipe_init(dvo_ctx* ctx)
     }
     ctx->d_stage_pp[0] = ctx->d_stage_in;
     CK(cudaMalloc(&ctx->d_stage_pp[1], sizeof(float) * (size_t)c.S * c.in_w * c.in_h));
-    for (int k = 0; k < 2; k++) {
-        CK(cudaEventCreateWithFlags(&ctx->ev_copied[k], cudaEventDisableTiming));
-        CK(cudaEventCreateWithFlags(&ctx->ev_consumed[k], cudaEventDisableTiming));
-        CK(cudaEventCreateWithFlags(&ctx->ev_done[k], cudaEventDisableTiming));
-    }
     return DVO_OK;
 }
 
@@ -1392,7 +1656,7 @@ static int vo_submit_impl(dvo_ctx* ctx, const void* gray, float* T_out, int kind
     CK(cudaEventRecord(ctx->ev_copied[k], ctx->copy_stream));
     CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_copied[k], 0));
     ctx->rows_only_staged = rows_only;
-    rc = vo_push_impl(ctx, ctx->d_stage_pp[k], nullptr, nullptr, T_out, ctx->ev_consumed[k], false, kind, aux);
+    rc = vo_push_impl(ctx, ctx->d_stage_pp[k], nullptr, nullptr, T_out, k == 0 ? nullptr : ctx->ev_consumed[k], false, kind, aux, k);
     if (rc) return rc;
     CK(cudaEventRecord(ctx->ev_done[k], ctx->stream));
     ctx->pp_head++;
@@ -1421,6 +1685,7 @@ extern "C" int dvo_vo_collect(dvo_ctx* ctx)
     const int k = (int)((ctx->pp_head - ctx->pp_in_flight) & 1);
     CK(cudaEventSynchronize(ctx->ev_done[k]));
     ctx->pp_in_flight--;
+    if (ctx->h_status[k]) return status_error(ctx, ctx->h_status[k]); // read back with this frame's poses (0 when T_out was NULL)
     return DVO_OK;
 }
 
@@ -1515,19 +1780,56 @@ extern "C" int dvo_vo_last_slot(dvo_ctx* ctx, int stream, int* slot)
 extern "C" int dvo_vo_error(dvo_ctx* ctx) { return map_error(ctx); }
 
 // ---- synthetic inputs -----------------------------------------------------------------------
-extern "C" int dvo_synth_render_dev(dvo_ctx* ctx, float* gray_dev, float* depth_dev, int frame, uint64_t seed0, float trans_step,
-                                    float rot_step_deg)
+static int synth_render(dvo_ctx* ctx, float* gray_dev, float* depth_dev, uint8_t* gray8_dev, int frame, uint64_t seed0, uint64_t seed_stride,
+                        float trans_step, float rot_step_deg)
 {
-    ARG(gray_dev && frame >= 0, "bad argument");
+    ARG((gray_dev || gray8_dev) && frame >= 0, "bad argument");
     const Consts& c = ctx->c;
     SynthParams P;
     P.w = c.in_w; P.h = c.in_h;
     P.fx = ctx->P.K[0]; P.fy = ctx->P.K[4]; P.cx = ctx->P.K[2]; P.cy = ctx->P.K[5];
-    P.seed0 = seed0; P.trans_step = trans_step; P.rot_step = rot_step_deg * 0.017453292519943295f; P.frame = frame;
+    P.seed0 = seed0; P.seed_stride = seed_stride; P.trans_step = trans_step; P.rot_step = rot_step_deg * 0.017453292519943295f; P.frame = frame;
     dim3 grid(cdiv(P.w * P.h, 256), c.S);
-    k_synth_render<<<grid, 256, 0, ctx->stream>>>(P, gray_dev, depth_dev);
+    k_synth_render<<<grid, 256, 0, ctx->stream>>>(P, gray_dev, depth_dev, gray8_dev);
     KCHECK();
     return DVO_OK;
+}
+extern "C" int dvo_synth_render_dev(dvo_ctx* ctx, float* gray_dev, float* depth_dev, int frame, uint64_t seed0, float trans_step,
+                                    float rot_step_deg)
+{
+    return synth_render(ctx, gray_dev, depth_dev, nullptr, frame, seed0, 1, trans_step, rot_step_deg);
+}
+extern "C" int dvo_synth_render_gray8_dev(dvo_ctx* ctx, uint8_t* gray8_dev, float* depth_dev, int frame, uint64_t seed0, uint64_t seed_stride,
+                                          float trans_step, float rot_step_deg)
+{
+    return synth_render(ctx, nullptr, depth_dev, gray8_dev, frame, seed0, seed_stride, trans_step, rot_step_deg);
+}
+static int synth_info(dvo_ctx* ctx, int frame, uint64_t seed, float trans_step, float rot_step_deg, float* host, int first, int count)
+{
+    float* d = ctx->d_small; // [S][64] floats: room for SY_INFO_FLOATS when S >= 3; otherwise a scratch allocation
+    DevScratch sc;
+    if ((size_t)ctx->c.S * 64 < (size_t)SY_INFO_FLOATS) {
+        CK(cudaMalloc(&sc.p, sizeof(float) * SY_INFO_FLOATS));
+        d = (float*)sc.p;
+    }
+    k_synth_info<<<1, 64, 0, ctx->stream>>>((unsigned long long)seed, frame, trans_step, rot_step_deg * 0.017453292519943295f, d);
+    KCHECK();
+    CK(cudaMemcpyAsync(host, d + first, sizeof(float) * count, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return DVO_OK;
+}
+extern "C" int dvo_synth_pose(dvo_ctx* ctx, int frame, uint64_t seed, float trans_step, float rot_step_deg, float* T_wc)
+{
+    ARG(T_wc && frame >= 0, "bad argument");
+    int rc = synth_info(ctx, frame, seed, trans_step, rot_step_deg, T_wc, 0, 12);
+    if (rc) return rc;
+    T_wc[12] = T_wc[13] = T_wc[14] = 0.f; T_wc[15] = 1.f;
+    return DVO_OK;
+}
+extern "C" int dvo_synth_scene(dvo_ctx* ctx, uint64_t seed, float* out, int cap)
+{
+    ARG(out && cap >= SY_INFO_FLOATS - 12, "bad argument");
+    return synth_info(ctx, 0, seed, 0.f, 0.f, out, 12, SY_INFO_FLOATS - 12);
 }
 extern "C" void* dvo_dev_alloc(size_t bytes)
 {
@@ -1560,6 +1862,23 @@ extern "C" int dvo_timer_stop(dvo_ctx* ctx, float* ms)
     CK(cudaEventRecord(ctx->ev1, ctx->stream));
     CK(cudaEventSynchronize(ctx->ev1));
     CK(cudaEventElapsedTime(ms, ctx->ev0, ctx->ev1));
+    return DVO_OK;
+}
+
+extern "C" int dvo_event_record(dvo_ctx* ctx, int id)
+{
+    ARG(id >= 0 && id < 65536, "bad event id");
+    if ((size_t)id >= ctx->user_ev.size()) ctx->user_ev.resize((size_t)id + 1, nullptr);
+    if (!ctx->user_ev[id]) CK(cudaEventCreate(&ctx->user_ev[id]));
+    CK(cudaEventRecord(ctx->user_ev[id], ctx->stream));
+    return DVO_OK;
+}
+extern "C" int dvo_event_elapsed(dvo_ctx* ctx, int id0, int id1, float* ms)
+{
+    ARG(ms && id0 >= 0 && id1 >= 0 && (size_t)id0 < ctx->user_ev.size() && (size_t)id1 < ctx->user_ev.size() && ctx->user_ev[id0] &&
+        ctx->user_ev[id1], "bad event id");
+    CK(cudaEventSynchronize(ctx->user_ev[id1]));
+    CK(cudaEventElapsedTime(ms, ctx->user_ev[id0], ctx->user_ev[id1]));
     return DVO_OK;
 }
 

@@ -121,6 +121,23 @@ __device__ __forceinline__ float subpixel_dense_nb(const float* __restrict__ img
     return bilerp(g0, g1, g2, g3, hh, v);
 }
 
+// Fully predicated form: no branch at all.  Out-of-image positions read texel (0, 0) and the result is replaced by INVALID with
+// one select, so the compiler is free to interleave the address arithmetic and loads of neighbouring taps (the search loop's
+// stall samples were 14 % branch resolution with three BSSY regions per step, profiles/r1g_full issue summary).
+__device__ __forceinline__ float subpixel_dense_bf(const float* __restrict__ img, int w, int h, float wf, float hf, float px, float py)
+{
+    const bool in = (px > -1.0f && px < wf && py > -1.0f && py < hf);
+    const float qx = in ? px : 0.0f, qy = in ? py : 0.0f;
+    const int x0 = __float2int_rz(qx), y0 = __float2int_rz(qy);
+    const float hh = qx - (float)x0, v = qy - (float)y0;
+    const float* __restrict__ p = img + (y0 * w + x0);
+    const int ox = (x0 + 1 < w) ? 1 : 0, oy = (y0 + 1 < h) ? w : 0;
+    const float g0 = __ldg(p), g1 = __ldg(p + ox), g2 = __ldg(p + oy), g3r = __ldg(p + oy + ox);
+    const float g3 = (ox != 0 && oy != 0) ? g3r : g0;
+    const float r = bilerp(g0, g1, g2, g3, hh, v);
+    return in ? r : DVO_INV;
+}
+
 // The same, split into position, loads and arithmetic, so that a caller can put several samples' loads in
 // flight before consuming any of them, or take the four texels from elsewhere when (x0, y0) coincide.
 struct TapPos {

@@ -27,6 +27,8 @@ struct Consts {
     int in_w, in_h, culls;
     LevelGeom lv[MAXL];
     int max_kf;
+    int kf_stride; // row pitch of the per-stream history / pose tables: max_kf rounded up to 32 entries, so that no 128-byte line
+                   // holds entries of two streams (Mapper::update may run while OTHER streams' tables are still being written)
     int vo_base; // first slot id of the VO keyframe pool (= dvo_params.max_frames)
     // tracking
     int max_iter;
@@ -34,6 +36,7 @@ struct Consts {
     float min_depth_f;  // smallest float >= (double)min_depth: (double)d < min_depth <=> d < min_depth_f
     float sigma_lo, sigma_hi;
     float step_default, step_level1, step_level2;
+    float huber_delta, min_grad2; // extras (dvo_params.huber_delta, min_gradient^2); 0 = off = the reference
     // mapping
     int map_x0, map_x1, map_y0, map_y1;
     float min_movement;
@@ -86,10 +89,24 @@ struct MapState {
     float rel_z;      // rel_xi[2]
     int valid_update;
     unsigned int n_reject;      // rejects of this update
-    unsigned int ticket;
+    unsigned int ticket;        // phase-B CTAs that have finished (the last one advances rng_pos)
     unsigned long long rng_pos; // draws consumed so far
     int err;
+    unsigned int ticket_a;      // phase-A CTAs that have finished (the last one turns the per-CTA reject counts into offsets)
+    unsigned int ticket_r;      // regularize CTAs that have finished (the last one copies the result back, Frame::updateDepth)
+    int pad[3];
+};
+
+// Hand-over from the tracking kernel to Mapper::update inside one frame (DESIGN.md §4 "overlap").  Streams are independent, so a
+// stream whose tracking has finished can be mapped while slower streams still iterate: the tracking CTA appends its stream to
+// `list` (completion order) when Mapper::needNewFrame chose update, and every finished stream counts in n_finished.  k_map_update
+// CTAs take a ticket and serve (list position, tile) = (ticket / nblk, ticket % nblk).  Reset by the frame's ingest kernel.
+struct ReadyQ {
+    int n_reserved;        // list entries handed out
+    int n_finished;        // streams whose tracking epilogue is complete (updating or not)
+    unsigned int ticket;   // k_map_update CTAs started
     int pad;
+    int list[1];           // [S] stream ids in completion order, -1 = not yet written
 };
 
 // Per-stream VO state (System::VisualOdometry + FrameHistory).

@@ -20,6 +20,24 @@ __device__ __forceinline__ size_t top_index(const LevelView& v, int x, int y) { 
 __device__ __forceinline__ float level_value(const LevelView& v, float raw) { return v.t ? get_pixel_value(raw) : raw; }
 
 // =============================================================================================
+// Programmatic dependent launch (sm_90+): a kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may start
+// while its predecessor in the stream still runs; pdl_wait() blocks until the predecessor has completed and its memory is
+// visible, pdl_launch() lets the successor's CTAs be scheduled.  Both are no-ops for a kernel launched the ordinary way.
+// =============================================================================================
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ int ld_volatile_i32(const int* p) { return *(const volatile int*)p; }
+
+// the frame's first kernel clears the tracking -> mapping hand-over queue (dvo_internal.cuh)
+__device__ __forceinline__ void ready_reset(ReadyQ* rq, int S)
+{
+    if (rq && blockIdx.x == 0 && blockIdx.y == 0) {
+        for (int k = threadIdx.x; k < S; k += blockDim.x) rq->list[k] = -1;
+        if (threadIdx.x == 0) { rq->n_reserved = 0; rq->n_finished = 0; rq->ticket = 0; }
+    }
+}
+
+// =============================================================================================
 // Frame construction: Frame ctor = Convert::cullImage(gray, culls) (frame.hpp:108-117,
 // convert.cpp:7-20).  One thread per 4 finest-level pixels; the input row is read with a stride of
 // 2^culls elements.  row_shift = culls when `in` holds every input row, 0 when the host staged only
@@ -27,8 +45,9 @@ __device__ __forceinline__ float level_value(const LevelView& v, float raw) { re
 // =============================================================================================
 __global__ void __launch_bounds__(256) k_cull_gray(const __grid_constant__ Consts c, const float* __restrict__ in, int in_rows,
                                                    int row_shift, const SlotDev* __restrict__ slots, int fixed,
-                                                   const VoState* __restrict__ vo)
+                                                   const VoState* __restrict__ vo, ReadyQ* rq)
 {
+    ready_reset(rq, c.S);
     const int s = blockIdx.y;
     const SlotDev& slot = slots[vo ? vo_cur_slot(c, vo[s].n_kf) : fixed];
     const LevelGeom g = c.lv[c.L - 1];
@@ -58,8 +77,9 @@ __global__ void __launch_bounds__(256) k_cull_gray(const __grid_constant__ Const
 // 32 << culls contiguous bytes of one input row.
 __global__ void __launch_bounds__(256) k_cull_gray8(const __grid_constant__ Consts c, const uint8_t* __restrict__ in, int in_rows,
                                                     int row_shift, int invalid_code, const SlotDev* __restrict__ slots, int fixed,
-                                                    const VoState* __restrict__ vo)
+                                                    const VoState* __restrict__ vo, ReadyQ* rq)
 {
+    ready_reset(rq, c.S);
     const int s = blockIdx.y;
     const SlotDev& slot = slots[vo ? vo_cur_slot(c, vo[s].n_kf) : fixed];
     const LevelGeom g = c.lv[c.L - 1];
@@ -107,8 +127,9 @@ __global__ void __launch_bounds__(256) k_build_remap(const __grid_constant__ Con
 // OpenCV's 15-bit fixed point, convertTo(1/255) as one fp32 multiply, INVALID outside the source image.  grid = (ceil(n_top/256), S)
 __global__ void __launch_bounds__(256) k_cull_bgr8(const __grid_constant__ Consts c, const uint8_t* __restrict__ in, int channels,
                                                    const int* __restrict__ idx, const SlotDev* __restrict__ slots, int fixed,
-                                                   const VoState* __restrict__ vo)
+                                                   const VoState* __restrict__ vo, ReadyQ* rq)
 {
+    ready_reset(rq, c.S);
     const int s = blockIdx.y;
     const SlotDev& slot = slots[vo ? vo_cur_slot(c, vo[s].n_kf) : fixed];
     const LevelGeom g = c.lv[c.L - 1];
@@ -196,6 +217,46 @@ __global__ void __launch_bounds__(256) k_kinect_frame(const __grid_constant__ Co
     slot.gray[(size_t)s * g.n + i] = culled ? get_pixel_value(gray) : gray;
     slot.ds[(size_t)s * g.n + i] = make_float2(culled ? get_pixel_value(depth) : depth, sigma);
     slot.age[(size_t)s * g.n + i] = 0.f;
+}
+
+// Transform::mapDepthtoGray (src/core/transform.cpp:53-78) on raw float images, the class-level form the reference's callers use
+// (KinectLoader::getMappedImages, loader.cpp:116-119): per depth pixel backProject(depth_K) -> transform(invT) -> project(rgb_K) ->
+// Convert::getSubpixel(gray); sigma 0.1 where mapped, 1.0 elsewhere.  grid = ceil(w h / 256)
+struct MapD2G {
+    int w, h, gw, gh;
+    float dfx, dfy, dcx, dcy, fx, fy, cx, cy;
+    float T[12];
+};
+__global__ void __launch_bounds__(256) k_map_depth_to_gray(const MapD2G P, const float* __restrict__ depth, const float* __restrict__ gray,
+                                                           float* __restrict__ mapped, float* __restrict__ sigma)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P.w * P.h) return;
+    const int y = i / P.w, x = i - y * P.w;
+    const float d = depth[i];
+    float g = DVO_INV, sg = 1.0f; // transform.cpp:60-61
+    if (!(fabsf(d) < DVO_EPS)) {  // math::isEpsilon :67
+        const float Xc = d * ((float)x - P.dcx) / P.dfx, Yc = d * ((float)y - P.dcy) / P.dfy;
+        const float tx = (P.T[0] * Xc + P.T[1] * Yc + P.T[2] * d) + P.T[3];
+        const float ty = (P.T[4] * Xc + P.T[5] * Yc + P.T[6] * d) + P.T[7];
+        const float tz = (P.T[8] * Xc + P.T[9] * Yc + P.T[10] * d) + P.T[11];
+        const float px = tx * P.fx / tz + P.cx, py = ty * P.fy / tz + P.cy;
+        const int x0 = trunc_x86(px), y0 = trunc_x86(py);
+        if (in_range(x0, y0, P.gw, P.gh)) { // Convert::getSubpixel, convert.cpp:127-177
+            const float hh = px - (float)x0, v = py - (float)y0;
+            const float* p = gray + (size_t)y0 * P.gw + x0;
+            float t[4];
+            t[0] = t[1] = t[2] = t[3] = __ldg(p);
+            const bool xin = x0 + 1 < P.gw, yin = y0 + 1 < P.gh;
+            if (xin) t[1] = __ldg(p + 1);
+            if (yin) t[2] = __ldg(p + P.gw);
+            if (xin && yin) t[3] = __ldg(p + P.gw + 1);
+            if (repair_taps(t)) g = bilerp(t[0], t[1], t[2], t[3], hh, v);
+        }
+        sg = 0.1f; // :73
+    }
+    mapped[i] = g;
+    sigma[i] = sg;
 }
 
 // depth / sigma / age upload (Frame 6-arg ctor frame.hpp:91-106, updateDepthSigmaAge frame.cpp:47-54).
@@ -606,6 +667,10 @@ struct TrackArgs {
     PoseTab* tab;
     int frame_id;
     const float* forced_rel;
+    float* T_out;         // optional [S][16]: se3::exp(frame->m_xi), odometrize's return value (system.hpp:73)
+    int* status;          // first device-side error of any stream (dvo_status), read back with the poses
+    ReadyQ* rq;           // tracking -> Mapper::update hand-over (nullptr: k_map_update runs after this kernel has completed)
+    int* winner;          // [S][n_top] scatter scratch of Implement::propagate, all -1 between uses (nullptr: separate kernels)
 };
 
 struct TrackCtl { // per-CTA copy of the stream's iteration state
@@ -701,13 +766,13 @@ __device__ __noinline__ void gn_tail(const Consts& c, const TrackArgs& a, TrackS
 __device__ inline void pose_table_entry(const Consts& c, const SlotDev* __restrict__ slots, const MapState* m, const int* __restrict__ hist,
                                         PoseTab* __restrict__ tab, int s, int age)
 {
-    const int born_slot = hist[(size_t)s * c.max_kf + (m->n_hist - 1 - age)]; // FrameHistory::operator[] frame.hpp:176
+    const int born_slot = hist[(size_t)s * c.kf_stride + (m->n_hist - 1 - age)]; // FrameHistory::operator[] frame.hpp:176
     const float* oxi = slots[m->obj_slot].xi + 6 * s;
     const float* bxi = slots[born_slot].xi + 6 * s;
     float a6[6], nb[6], r[6];
     for (int q = 0; q < 6; q++) { a6[q] = oxi[q]; nb[q] = -bxi[q]; }
     se3_concatenate(a6, nb, r);
-    PoseTab* t = tab + (size_t)s * c.max_kf + age;
+    PoseTab* t = tab + (size_t)s * c.kf_stride + age;
     se3_exp_neg12(r, t->T);
     t->t[0] = -r[0]; t->t[1] = -r[1]; t->t[2] = -r[2];
 }
@@ -728,7 +793,7 @@ __device__ __noinline__ void vo_decide(const Consts& c, const TrackArgs& a, cons
         for (int q = 0; q < 6; q++) { cur.xi[6 * s + q] = 0.f; cur.rel_xi[6 * s + q] = 0.f; }
         m->do_propagate = 0; m->do_update = 0; m->do_regularize = 0;
         v->need_new = 1; v->was_keyframe = 1; v->n_iters = 0;
-        a.hist[(size_t)s * c.max_kf] = cur_slot;
+        a.hist[(size_t)s * c.kf_stride] = cur_slot;
         v->n_kf = 1; v->kf_slot = cur_slot; v->kf_frame_id = a.frame_id;
         m->reg_slot = cur_slot;
         return;
@@ -762,14 +827,27 @@ __device__ __noinline__ void vo_decide(const Consts& c, const TrackArgs& a, cons
         if (v->n_kf >= c.max_kf) {
             atomicCAS(&m->err, 0, (int)DVO_ERR_HISTORY);
         } else {
-            a.hist[(size_t)s * c.max_kf + v->n_kf] = cur_slot;
+            a.hist[(size_t)s * c.kf_stride + v->n_kf] = cur_slot;
             v->n_kf += 1;
             v->kf_slot = cur_slot;
             v->kf_frame_id = a.frame_id;
         }
     }
     m->reg_slot = v->kf_slot;
+    // a stream that has failed (history overflow) keeps tracking against its last good keyframe but is no longer mapped: its
+    // maps would silently stop matching the reference (the reference itself would have thrown, frame.hpp:176)
+    if (m->err) {
+        m->do_propagate = 0; m->do_update = 0; m->do_regularize = 0;
+        if (a.status) atomicCAS(a.status, 0, m->err);
+    }
 }
+
+// Implement::propagate (implement.cpp:217-256) + Frame::updateDepthSigmaAge for ONE stream by ONE CTA, in the tracking kernel's
+// epilogue: the streams that take a new keyframe are a third of all, their scatter + gather is 2 x 19 200 pixels, and doing it
+// here overlaps it with the streams that still iterate instead of two more launches that every stream's CTAs attend.  Same
+// arithmetic as k_propagate_scatter / k_propagate_gather (atomicMax of the source index: the LAST source in row-major order wins).
+__device__ __forceinline__ void propagate_stream(const Consts& c, const SlotDev* __restrict__ slots, const MapState* m, int* __restrict__ winner,
+                                                 int s, int tid, int nthreads);
 
 __device__ __forceinline__ unsigned int ld_volatile_u32(const unsigned int* p) { return *(const volatile unsigned int*)p; }
 
@@ -789,6 +867,11 @@ __global__ void __launch_bounds__(TRK_THREADS, TRK_MINB) k_track(const __grid_co
     __shared__ const float* s_ref;
     __shared__ const float2* s_ds;
     __shared__ unsigned int s_gen0;
+
+    // the ingest kernel before this one has completed (a no-op unless launched as a programmatic dependent); from here on
+    // k_map_update's CTAs may be scheduled onto whatever this kernel leaves free (they wait per stream, see ReadyQ)
+    pdl_wait();
+    pdl_launch();
 
     // ---- prologue: Tracker::track's xi = 0, level 0 (tracker.cpp:28-40); every CTA of the stream
     // derives the same initial state, the leader also publishes it for the host.
@@ -905,6 +988,7 @@ __global__ void __launch_bounds__(TRK_THREADS, TRK_MINB) k_track(const __grid_co
                     // I_2 valid (optimize.cpp:46); warped point inside the image (:52-56); gradients valid (:61)
                     ok = sm.in && !is_invalid(sm.I) && !(wx < 0 || wy < 0 || (float)g.w <= wx || (float)g.h <= wy)
                          && !(is_invalid(sm.gx) || is_invalid(sm.gy));
+                    if (ok && c.min_grad2 > 0.0f) ok = !(sm.gx * sm.gx + sm.gy * sm.gy < c.min_grad2); // semi-dense selection (extra, default off)
                     if (ok) {
                         const float fgx = g.fx * sm.gx, fgy = g.fy * sm.gy; // optimize.cpp:67-77
                         const float xz = X / Z, yz = Y / Z;
@@ -919,6 +1003,14 @@ __global__ void __launch_bounds__(TRK_THREADS, TRK_MINB) k_track(const __grid_co
                         const float sg = (sg0 < c.sigma_lo) ? c.sigma_lo : (c.sigma_hi < sg0) ? c.sigma_hi : sg0; // std::clamp :83
                         bw = r * (step / sg);
                         rr = r;
+                        if (c.huber_delta > 0.0f) { // variance-normalised Huber weight (extra, default off): row and entry scaled by sqrt(w)
+                            const float t = fabsf(r) / sg;
+                            const float wh = (t <= c.huber_delta) ? 1.0f : c.huber_delta / t;
+                            const float sw = sqrtf(wh);
+#pragma unroll
+                            for (int q = 0; q < 6; q++) J[q] = J[q] * sw;
+                            bw = bw * sw;
+                        }
                         nvalid++;
                     }
                 }
@@ -1026,11 +1118,35 @@ __global__ void __launch_bounds__(TRK_THREADS, TRK_MINB) k_track(const __grid_co
 
     // ---- VO epilogue (leader CTA of each stream) ----
     if (a.vo && leader) {
-        if (tid == 0) vo_decide(c, a, st, s);
+        if (tid == 0) {
+            vo_decide(c, a, st, s);
+            if (a.T_out) { // se3::exp(frame->m_xi), system.hpp:73 (identity on the first frame)
+                float xi[6], T[16];
+                const float* cx = a.slots[a.vo[s].cur_slot].xi + 6 * s;
+                for (int q = 0; q < 6; q++) xi[q] = cx[q];
+                se3_exp(xi, T);
+                for (int q = 0; q < 16; q++) a.T_out[16 * s + q] = T[q];
+            }
+        }
         __syncthreads();
         const MapState* m = a.ms + s;
-        if (m->do_update)
+        const int do_update = m->do_update, do_propagate = m->do_propagate;
+        if (do_update)
             for (int age = tid; age < m->n_hist; age += TRK_THREADS) pose_table_entry(c, a.slots, m, a.hist, a.tab, s, age);
+        if (a.rq) {
+            // publish: everything Mapper::update reads of this stream (MapState, history, pose table, frame poses) is written
+            __threadfence();
+            __syncthreads();
+            if (tid == 0) {
+                if (do_update) {
+                    const int pos = atomicAdd(&a.rq->n_reserved, 1);
+                    *(volatile int*)&a.rq->list[pos] = s;
+                    __threadfence();
+                }
+                atomicAdd(&a.rq->n_finished, 1);
+            }
+        }
+        if (a.winner && do_propagate) propagate_stream(c, a.slots, m, a.winner + (size_t)s * c.lv[c.L - 1].n, s, tid, TRK_THREADS);
     }
 }
 
@@ -1117,10 +1233,22 @@ struct SearchSmem { // per warp
     unsigned long long best[32];
 };
 
+#ifndef DVO_SEARCH_BF
+#define DVO_SEARCH_BF 0
+#endif
+#if DVO_SEARCH_BF
+#define SEARCH_TAP subpixel_dense_bf
+#else
+#define SEARCH_TAP subpixel_dense_nb
+#endif
 __device__ __forceinline__ float search_ssd(float s0, float s1, float s2, float og)
 {
     // implement.cpp:122-139: a tap that is invalid ends the accumulation with ssd = 2.0 * 3
+#if DVO_SEARCH_BF
+    const bool bad = is_invalid(s0) || is_invalid(s1) || is_invalid(s2); // selected at the end: no branch in the search loop
+#else
     if (is_invalid(s0) || is_invalid(s1) || is_invalid(s2)) return 2.0f * 3;
+#endif
     const float d0 = s0 - og, d1 = s1 - og, d2 = s2 - og;
     // first term: (float)(0.0 + (double)(1/3) * (double)a), a = d0 * d0 >= 0, equals the correctly rounded float quotient a / 3 for
     // EVERY non-negative finite float (a / 3 is never within 2^-27 relative of a float rounding boundary, the double product is within
@@ -1133,7 +1261,11 @@ __device__ __forceinline__ float search_ssd(float s0, float s1, float s2, float 
     // third term: weight 3/3 = 1.0, i.e. (float)((double)ssd + (double)(d2 * d2)).  For two non-negative floats that equals the
     // float sum: the double sum is exact unless the exponents are > 29 bits apart, and then both roundings return ssd itself.
     ssd = __fadd_rn(ssd, d2 * d2);
+#if DVO_SEARCH_BF
+    return bad ? 2.0f * 3 : ssd;
+#else
     return ssd;
+#endif
 }
 
 // All 32 lanes of the warp must call this (active = false for lanes without a segment).  w, h are warp-uniform.
@@ -1216,14 +1348,14 @@ __device__ __forceinline__ void warp_search(SearchSmem& sm, bool active, const f
             // tap per step instead of three, results bit-identical.
             float prevx = ptx, prevy = pty;                    // pt of the previous step (the checkpoint itself for k = 1)
             const float wf = (float)w, hf = (float)h;
-            float c_prev = subpixel_dense_nb(img, w, h, wf, hf, ptx, pty); // tap at prev
+            float c_prev = SEARCH_TAP(img, w, h, wf, hf, ptx, pty); // tap at prev
             ptx += dx;
             pty += dy;
-            float c_cur = subpixel_dense_nb(img, w, h, wf, hf, ptx + dx * 0.0f, pty + dy * 0.0f); // tap at pt (k = 1)
+            float c_cur = SEARCH_TAP(img, w, h, wf, hf, ptx + dx * 0.0f, pty + dy * 0.0f); // tap at pt (k = 1)
             unsigned long long kbest = ~0ull;
 #pragma unroll(SEARCH_UNROLL)
             for (int k = 1; k <= cnt; k++) {
-                const float s2 = subpixel_dense_nb(img, w, h, wf, hf, ptx + dx * 1.0f, pty + dy * 1.0f);
+                const float s2 = SEARCH_TAP(img, w, h, wf, hf, ptx + dx * 1.0f, pty + dy * 1.0f);
                 const float bx = ptx + dx * -1.0f, by = pty + dy * -1.0f;
                 const float s0 = (bx == prevx && by == prevy) ? c_prev : subpixel_dense_nb(img, w, h, wf, hf, bx, by);
                 const unsigned long long key = ((unsigned long long)__float_as_uint(search_ssd(s0, c_cur, s2, ogp)) << 32) | (unsigned)(b0 + k);
@@ -1376,14 +1508,50 @@ struct MapRoi {
 __global__ void __launch_bounds__(MAPU_THREADS, DVO_MAPU_MINB) k_map_update(const __grid_constant__ Consts c, const MapRoi roi, const SlotDev* __restrict__ slots,
                                                        MapState* __restrict__ mst, const int* __restrict__ hist,
                                                        const PoseTab* __restrict__ tab, uint8_t* __restrict__ flags,
-                                                       unsigned int* __restrict__ blockcnt)
+                                                       unsigned int* __restrict__ blockcnt, ReadyQ* rq, int* status)
 {
-    const int s = blockIdx.y;
-    MapState* m = mst + s;
-    if (!m->do_update) return;
-    const LevelGeom g = c.lv[c.L - 1];
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
     __shared__ SearchSmem s_search[MAPU_THREADS / 32];
+    __shared__ int s_sel[2];
+    // Which (stream, tile) this CTA serves.  Ordinary launch: (blockIdx.y, blockIdx.x) of streams that update.  Overlapped with
+    // the tracking kernel (rq != nullptr, programmatic dependent launch): the CTA takes a ticket and serves tile (ticket % nblk)
+    // of the (ticket / nblk)-th stream to FINISH tracking with an update to do, waiting for that list entry if tracking has not
+    // got that far - tickets are handed out in start order and streams are listed in completion order, so a CTA only ever waits
+    // when every tile of every finished stream is already taken, i.e. when its SM slot would have idled anyway.
+    int s = blockIdx.y, tile = blockIdx.x;
+    if (rq) {
+        if (threadIdx.x == 0) {
+            const unsigned int t = atomicAdd(&rq->ticket, 1u);
+            const int q = (int)(t / (unsigned int)roi.nblk);
+            int v;
+            unsigned long long t0 = 0;
+            for (;;) {
+                v = ld_volatile_i32(&rq->list[q]);
+                if (v >= 0) break;
+                // The producers (k_track's CTAs) are all resident before this kernel may start, so the wait is bounded by one
+                // tracking run (< 1 ms).  Should that ever not hold (a tool serialising the two launches the wrong way round),
+                // give up after 2 s with an error instead of hanging the GPU.
+                unsigned long long now;
+                asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+                if (t0 == 0) t0 = now;
+                else if (now - t0 > 2000000000ull) { if (status) atomicCAS(status, 0, (int)DVO_ERR_STATE); v = -1; break; }
+                if (ld_volatile_i32(&rq->n_finished) >= c.S) { // every stream has decided: the list is final
+                    __threadfence();
+                    v = ld_volatile_i32(&rq->list[q]);
+                    break;
+                }
+                __nanosleep(200);
+            }
+            __threadfence(); // acquire: the stream's MapState / history / pose table were written before its list entry
+            s_sel[0] = v; s_sel[1] = (int)(t - (unsigned int)q * (unsigned int)roi.nblk);
+        }
+        __syncthreads();
+        s = s_sel[0]; tile = s_sel[1];
+        if (s < 0) return;
+    }
+    MapState* m = mst + s;
+    if (!rq && !m->do_update) return;
+    const LevelGeom g = c.lv[c.L - 1];
+    const int j = tile * blockDim.x + threadIdx.x;
     uint8_t fl = 0;
     bool reject = false;
     // --- per pixel: candidate gate, keyframe lookup, epipolar segment (mapper.cpp:90-107, implement.cpp:23-47)
@@ -1398,23 +1566,29 @@ __global__ void __launch_bounds__(MAPU_THREADS, DVO_MAPU_MINB) k_map_update(cons
         const int ry = j / roi.w;
         const int x = roi.x0 + (j - ry * roi.w), y = roi.y0 + ry;
         i = y * g.w + x;
-        const SlotDev ref = slots[m->ref_slot];
+        const int n_hist = __ldcg(&m->n_hist);
+        const SlotDev ref = slots[__ldcg(&m->ref_slot)];
         ds = ref.ds + (size_t)s * g.n;
         const float2 dsv = ds[i];
         const float d = dsv.x;
         float wx, wy;
-        warp_point(m->Trel, g, (float)x, (float)y, d, wx, wy);
+        {
+            float Trel[12];
+#pragma unroll
+            for (int q = 0; q < 12; q++) Trel[q] = __ldcg(&m->Trel[q]);
+            warp_point(Trel, g, (float)x, (float)y, d, wx, wy);
+        }
         px = round_x86(wx); py = round_x86(wy); // Point2f -> Point2i :94
         if (in_range(px, py, g.w, g.h)) {
             const int age = trunc_x86(ref.age[(size_t)s * g.n + i]); // :99
-            if (age < 0 || age >= m->n_hist) {
+            if (age < 0 || age >= n_hist) {
                 atomicCAS(&m->err, 0, (int)DVO_ERR_HISTORY); // m_history.at() would throw
             } else {
-                const int born_slot = hist[(size_t)s * c.max_kf + (m->n_hist - 1 - age)];
-                pt = tab + (size_t)s * c.max_kf + age;
-                prior_d = d - m->rel_z; // :104
+                const int born_slot = __ldcg(hist + (size_t)s * c.kf_stride + (n_hist - 1 - age));
+                pt = tab + (size_t)s * c.kf_stride + age;
+                prior_d = d - __ldcg(&m->rel_z); // :104
                 prior_s = dsv.y;
-                og = __ldg(slots[m->obj_slot].gray + (size_t)s * g.n + (size_t)py * g.w + px);
+                og = __ldg(slots[__ldcg(&m->obj_slot)].gray + (size_t)s * g.n + (size_t)py * g.w + px);
                 born_gray = slots[born_slot].gray + (size_t)s * g.n;
                 seg = make_segment(g, pt->T, px, py, prior_d, prior_s);
                 cand = true;
@@ -1446,41 +1620,38 @@ __global__ void __launch_bounds__(MAPU_THREADS, DVO_MAPU_MINB) k_map_update(cons
     if (j < roi.n) flags[(size_t)s * g.n + i] = fl;
     const int nrej = __syncthreads_count(reject);
     const int nval = __syncthreads_count((fl & 4) != 0);
-    if (threadIdx.x == 0) {
-        blockcnt[(size_t)s * roi.nblk + blockIdx.x] = (unsigned)nrej;
-        if (nval) atomicAdd(&m->valid_update, nval);
-    }
-}
-
-// Between the phases: per stream, the per-CTA reject counts become exclusive offsets (the row-major rank base of phase B) and
-// their total.  grid = S, 256 threads.  (Summing the preceding counts inside every phase-B CTA is quadratic in the CTA count:
-// fine for 196 CTAs at 160x120, hopeless for 129 600 at 3840x2160.)
-__global__ void __launch_bounds__(256) k_map_scan(const __grid_constant__ Consts c, const MapRoi roi, MapState* __restrict__ mst,
-                                                  unsigned int* __restrict__ blockcnt)
-{
-    const int s = blockIdx.x;
-    MapState* m = mst + s;
-    if (!m->do_update) return;
-    __shared__ unsigned int s_sum[256];
+    // The stream's LAST phase-A CTA turns the per-CTA reject counts into exclusive offsets (the row-major rank base of phase B)
+    // and their total - no separate scan launch, and nothing quadratic in the CTA count (129 600 CTAs at 3840x2160).
     unsigned int* bc = blockcnt + (size_t)s * roi.nblk;
-    const int per = (roi.nblk + 255) / 256;
+    __shared__ unsigned int s_last;
+    if (threadIdx.x == 0) {
+        bc[tile] = (unsigned)nrej;
+        if (nval) atomicAdd(&m->valid_update, nval);
+        __threadfence();
+        s_last = (atomicAdd(&m->ticket_a, 1u) == (unsigned int)(roi.nblk - 1)) ? 1u : 0u;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    unsigned int* s_sum = reinterpret_cast<unsigned int*>(s_search); // the search scratch is free now
+    const int per = (roi.nblk + MAPU_THREADS - 1) / MAPU_THREADS;
     const int b0 = threadIdx.x * per, b1 = min(roi.nblk, b0 + per);
     unsigned int sum = 0;
-    for (int b = b0; b < b1; b++) sum += bc[b];
+    for (int b = b0; b < b1; b++) sum += __ldcg(bc + b);
     s_sum[threadIdx.x] = sum;
     __syncthreads();
     unsigned int off = 0;
     for (int k = 0; k < (int)threadIdx.x; k++) off += s_sum[k];
     for (int b = b0; b < b1; b++) {
-        const unsigned int v = bc[b];
+        const unsigned int v = __ldcg(bc + b);
         bc[b] = off;
         off += v;
     }
-    if (threadIdx.x == 255) m->n_reject = off;
+    if (threadIdx.x == MAPU_THREADS - 1) { m->n_reject = off; m->ticket_a = 0; }
 }
 
 // Mapper::update phase B: replay of the mt19937 stream for the rejected pixels in row-major order.
-// rank = (rejects in the preceding phase-A CTAs, k_map_scan) + (rejects before this thread in its phase-A CTA).
+// rank = (rejects in the preceding phase-A CTAs, scanned by the stream's last phase-A CTA) + (rejects before this thread in its phase-A CTA).
 // One CTA covers APPLY_SUB phase-A CTAs.   grid = (ceil(roi.nblk / APPLY_SUB), S)
 constexpr int APPLY_SUB = 256 / MAPU_THREADS;
 __global__ void __launch_bounds__(MAPU_THREADS * APPLY_SUB) k_map_update_apply(const __grid_constant__ Consts c, const MapRoi roi,
@@ -1527,6 +1698,78 @@ __global__ void __launch_bounds__(MAPU_THREADS * APPLY_SUB) k_map_update_apply(c
         if (t == gridDim.x - 1) {
             m->rng_pos += m->n_reject;
             m->ticket = 0;
+        }
+    }
+}
+
+// Implement::propagate for one stream by one CTA (declared above; called from the tracking kernel's epilogue).  winner: the
+// stream's [n_top] scratch, all -1 on entry and on exit.
+__device__ __forceinline__ void propagate_stream(const Consts& c, const SlotDev* __restrict__ slots, const MapState* m, int* __restrict__ winner,
+                                                 int s, int tid, int nthreads)
+{
+    const LevelGeom g = c.lv[c.L - 1];
+    const SlotDev ref = slots[m->ref_slot];
+    const SlotDev dst = slots[m->new_slot];
+    const float2* __restrict__ rds = ref.ds + (size_t)s * g.n;
+    const float* __restrict__ rage = ref.age + (size_t)s * g.n;
+    float T[12];
+#pragma unroll
+    for (int q = 0; q < 12; q++) T[q] = m->Trel[q];
+    const float rel_z = m->rel_z;
+    // One CTA walks the whole level, so the loop is latency-bound: four independent pixels per thread and round, loads first.
+    constexpr int U = 4;
+    for (int i0 = tid; i0 < g.n; i0 += U * nthreads) {
+        float rd[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const int i = i0 + u * nthreads;
+            rd[u] = i < g.n ? rds[i].x : 0.f;
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const int i = i0 + u * nthreads;
+            if (i >= g.n || fabsf(rd[u]) < DVO_EPS) continue; // :236
+            const int y = i / g.w, x = i - y * g.w;
+            float wx, wy;
+            warp_point(T, g, (float)x, (float)y, rd[u], wx, wy); // :239
+            const int px = round_x86(wx), py = round_x86(wy);
+            if (!in_range(px, py, g.w, g.h)) continue; // :240
+            atomicMax(winner + (size_t)py * g.w + px, i);
+        }
+    }
+    __syncthreads(); // every scatter of this stream is at L2 before the first gather reads it (ld.cg below)
+    for (int i0 = tid; i0 < g.n; i0 += U * nthreads) {
+        int src[U];
+        float2 v[U];
+        float ag[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const int i = i0 + u * nthreads;
+            src[u] = i < g.n ? __ldcg(winner + i) : -1;
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            v[u] = make_float2(0.f, 0.f); ag[u] = 0.f;
+            if (src[u] >= 0) { v[u] = rds[src[u]]; ag[u] = rage[src[u]]; }
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const int i = i0 + u * nthreads;
+            if (i >= g.n) continue;
+            float2 out = make_float2(1.0f, 1.0f); // :229-231
+            float age = 0.f;
+            if (src[u] >= 0) {
+                winner[i] = -1;
+                const float d0 = v[u].x < 0.01f ? 0.01f : v[u].x; // :244
+                const float d1 = d0 + rel_z;
+                const float q = d1 / d0;
+                const float q4 = q * (q * (q * q)); // math::pow(., 4)
+                const float sg = sqrtf(q4 * (v[u].y * v[u].y) + (0.06f * 0.06f)); // :247
+                out = make_float2(d1 < 0.0f ? 0.0f : d1, sg);
+                age = ag[u] + 1; // :252
+            }
+            dst.ds[(size_t)s * g.n + i] = out;
+            dst.age[(size_t)s * g.n + i] = age;
         }
     }
 }
@@ -1586,24 +1829,40 @@ __global__ void __launch_bounds__(256) k_propagate_gather(const __grid_constant_
 
 // Implement::regularize (implement.cpp:156-180): 4-neighbour Gaussian fusion read from the input
 // maps; result -> tmp (depth only).  Slot = mst[s].reg_slot.
+// fold_commit != 0: the stream's LAST CTA to finish also performs Frame::updateDepth (frame.cpp:56-61), i.e. copies tmp back
+// into the depth plane once every CTA of the stream has read its neighbours - no second launch.  (One CTA copies the whole
+// finest level, so the host selects this for small levels only; large ones keep k_regularize_commit.)
 __global__ void __launch_bounds__(256) k_regularize(const __grid_constant__ Consts c, const SlotDev* __restrict__ slots,
-                                                    const MapState* __restrict__ mst, float* __restrict__ tmp)
+                                                    MapState* __restrict__ mst, float* __restrict__ tmp, int fold_commit)
 {
     const int s = blockIdx.y;
-    const MapState* m = mst + s;
+    MapState* m = mst + s;
     if (!m->do_regularize) return;
     const LevelGeom g = c.lv[c.L - 1];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= g.n) return;
-    const int y = i / g.w, x = i - y * g.w;
-    const float2* ds = slots[m->reg_slot].ds + (size_t)s * g.n;
-    float2 v = ds[i];
-    float gd = v.x, gs = v.y;
-    if (x - 1 >= 0) { const float2 n = __ldg(ds + i - 1); gaussian_fuse(gd, gs, n.x, n.y); }      // {0,-1}
-    if (x + 1 < g.w) { const float2 n = __ldg(ds + i + 1); gaussian_fuse(gd, gs, n.x, n.y); }     // {0, 1}
-    if (y + 1 < g.h) { const float2 n = __ldg(ds + i + g.w); gaussian_fuse(gd, gs, n.x, n.y); }   // {1, 0}
-    if (y - 1 >= 0) { const float2 n = __ldg(ds + i - g.w); gaussian_fuse(gd, gs, n.x, n.y); }    // {-1,0}
-    tmp[(size_t)s * g.n + i] = gd < 6.0f ? gd : 6.0f; // cv::min(new_depth, 6.0) :178
+    float2* ds = slots[m->reg_slot].ds + (size_t)s * g.n;
+    if (i < g.n) {
+        const int y = i / g.w, x = i - y * g.w;
+        float2 v = ds[i];
+        float gd = v.x, gs = v.y;
+        if (x - 1 >= 0) { const float2 n = __ldg(ds + i - 1); gaussian_fuse(gd, gs, n.x, n.y); }      // {0,-1}
+        if (x + 1 < g.w) { const float2 n = __ldg(ds + i + 1); gaussian_fuse(gd, gs, n.x, n.y); }     // {0, 1}
+        if (y + 1 < g.h) { const float2 n = __ldg(ds + i + g.w); gaussian_fuse(gd, gs, n.x, n.y); }   // {1, 0}
+        if (y - 1 >= 0) { const float2 n = __ldg(ds + i - g.w); gaussian_fuse(gd, gs, n.x, n.y); }    // {-1,0}
+        tmp[(size_t)s * g.n + i] = gd < 6.0f ? gd : 6.0f; // cv::min(new_depth, 6.0) :178
+    }
+    if (!fold_commit) return;
+    __shared__ unsigned int s_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = (atomicAdd(&m->ticket_r, 1u) == gridDim.x - 1) ? 1u : 0u;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    const float* t = tmp + (size_t)s * g.n;
+#pragma unroll 4
+    for (int k = threadIdx.x; k < g.n; k += blockDim.x) ds[k].x = __ldcg(t + k);
+    if (threadIdx.x == 0) m->ticket_r = 0;
 }
 
 // Frame::updateDepth (frame.cpp:56-61): depth <- tmp; sigma stays.  Two pixels per thread so that
@@ -1629,17 +1888,6 @@ __global__ void __launch_bounds__(256) k_regularize_commit(const __grid_constant
         ds[i].x = t[i];
         if (i + 1 < g.n) ds[i + 1].x = t[i + 1];
     }
-}
-
-// se3::exp(frame->m_xi) for odometrize's return value (system.hpp:73)
-__global__ void k_pose_out(const __grid_constant__ Consts c, const SlotDev* __restrict__ slots, const VoState* __restrict__ vo,
-                           float* __restrict__ T_out)
-{
-    const int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= c.S) return;
-    float T[16];
-    se3_exp(slots[vo[s].cur_slot].xi + 6 * s, T);
-    for (int q = 0; q < 16; q++) T_out[16 * s + q] = T[q];
 }
 
 // xi / rel_xi of every stream's current frame, gathered for dvo_vo_state.  out: [S][12]
@@ -1713,45 +1961,71 @@ __global__ void __launch_bounds__(64) k_update_points(const __grid_constant__ Co
 }
 
 // =============================================================================================
-// Row-major mask compaction (decoupled 2-pass: block counts, then offsets + scatter).
+// Row-major mask compaction, batched over streams: per-CTA counts -> one scan CTA per stream (exclusive offsets + total) ->
+// scatter.  Linear in the CTA count (the first version summed all preceding counts in every CTA).  mask: [S][n] bytes,
+// idx: [S][n], blockcnt: [S][nblk], total: [S].
 // =============================================================================================
 __global__ void __launch_bounds__(256) k_compact_count(const uint8_t* __restrict__ mask, int n, unsigned int* __restrict__ blockcnt)
 {
+    const int s = blockIdx.y;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool on = (i < n) && mask[i];
+    const bool on = (i < n) && mask[(size_t)s * n + i];
     const int cnt = __syncthreads_count(on);
-    if (threadIdx.x == 0) blockcnt[blockIdx.x] = cnt;
+    if (threadIdx.x == 0) blockcnt[(size_t)s * gridDim.x + blockIdx.x] = cnt;
+}
+__global__ void __launch_bounds__(256) k_compact_scan(int nblk, unsigned int* __restrict__ blockcnt, int* __restrict__ total)
+{
+    const int s = blockIdx.x;
+    __shared__ unsigned int s_sum[256];
+    unsigned int* bc = blockcnt + (size_t)s * nblk;
+    const int per = (nblk + 255) / 256;
+    const int b0 = threadIdx.x * per, b1 = min(nblk, b0 + per);
+    unsigned int sum = 0;
+    for (int b = b0; b < b1; b++) sum += bc[b];
+    s_sum[threadIdx.x] = sum;
+    __syncthreads();
+    unsigned int off = 0;
+    for (int k = 0; k < (int)threadIdx.x; k++) off += s_sum[k];
+    for (int b = b0; b < b1; b++) {
+        const unsigned int v = bc[b];
+        bc[b] = off;
+        off += v;
+    }
+    if (threadIdx.x == 255) total[s] = (int)off;
 }
 __global__ void __launch_bounds__(256) k_compact_scatter(const uint8_t* __restrict__ mask, int n, const unsigned int* __restrict__ blockcnt,
-                                                         int32_t* __restrict__ idx, unsigned int* __restrict__ total)
+                                                         int32_t* __restrict__ idx)
 {
+    const int s = blockIdx.y;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    __shared__ unsigned int s_warp[8], s_part[8], s_base;
-    unsigned int part = 0;
-    for (int b = threadIdx.x; b < (int)blockIdx.x; b += blockDim.x) part += blockcnt[b];
-    for (int off = 16; off > 0; off >>= 1) part += __shfl_down_sync(0xffffffffu, part, off);
+    __shared__ unsigned int s_warp[8];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (lane == 0) s_part[warp] = part;
-    const bool on = (i < n) && mask[i];
+    const bool on = (i < n) && mask[(size_t)s * n + i];
     const unsigned int bal = __ballot_sync(0xffffffffu, on);
     if (lane == 0) s_warp[warp] = __popc(bal);
     __syncthreads();
-    if (threadIdx.x == 0) {
-        unsigned int t = 0;
-        for (int k = 0; k < 8; k++) t += s_part[k];
-        s_base = t;
-        if (blockIdx.x == gridDim.x - 1) {
-            unsigned int bt = 0;
-            for (int k = 0; k < 8; k++) bt += s_warp[k];
-            *total = t + bt;
-        }
-    }
-    __syncthreads();
     if (on) {
-        unsigned int rank = s_base + __popc(bal & ((1u << lane) - 1u));
+        unsigned int rank = blockcnt[(size_t)s * gridDim.x + blockIdx.x] + __popc(bal & ((1u << lane) - 1u));
         for (int k = 0; k < warp; k++) rank += s_warp[k];
-        idx[rank] = i;
+        idx[(size_t)s * n + rank] = i;
     }
+}
+
+// Semi-dense pixel selection by gradient threshold (north_star; no reference counterpart): mask of the level pixels whose gray and
+// both Convert::gradiate values are valid and gx^2 + gy^2 >= thr2.  grid = (ceil(n_l/256), S)
+__global__ void __launch_bounds__(256) k_select_mask(const __grid_constant__ Consts c, SlotDev slot, int l, float thr2, uint8_t* __restrict__ mask)
+{
+    const int s = blockIdx.y;
+    const LevelGeom g = c.lv[l];
+    const LevelView v = level_view(c, l);
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= g.n) return;
+    const int y = i / g.w, x = i - y * g.w;
+    const size_t nt = (size_t)c.lv[c.L - 1].n;
+    const float* gray = slot.gray + (size_t)s * nt;
+    const float I = level_value(v, gray[top_index(v, x, y)]);
+    const float gx = grad_x_at(gray, v, x, y), gy = grad_y_at(gray, v, x, y);
+    mask[(size_t)s * g.n + i] = (!is_invalid(I) && !is_invalid(gx) && !is_invalid(gy) && !(gx * gx + gy * gy < thr2)) ? 1 : 0;
 }
 
 } // namespace dvo

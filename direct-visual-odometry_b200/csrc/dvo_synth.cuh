@@ -11,7 +11,8 @@ namespace dvo {
 struct SynthParams {
     int w, h;
     float fx, fy, cx, cy;
-    unsigned long long seed0; // stream s renders the scene / trajectory of seed0 + s
+    unsigned long long seed0; // stream s renders the scene / trajectory of seed0 + s * seed_stride
+    unsigned long long seed_stride;
     float trans_step, rot_step; // per-frame motion scale [m], [rad]
     int frame;
 };
@@ -61,11 +62,13 @@ __device__ inline void sy_pose(unsigned long long seed, int i, float trans_step,
 }
 
 // grid = (ceil(w*h/256), S).  gray: [S][h][w]; depth (optional): z in the camera frame.
-__global__ void __launch_bounds__(256) k_synth_render(const SynthParams P, float* __restrict__ gray, float* __restrict__ depth)
+// gray8 (optional): the same image as 8-bit codes, round-half-even of 255 g - what a camera / cv::imread + cvtColor delivers
+__global__ void __launch_bounds__(256) k_synth_render(const SynthParams P, float* __restrict__ gray, float* __restrict__ depth,
+                                                      uint8_t* __restrict__ gray8)
 {
     __shared__ SynthScene sc;
     const int s = blockIdx.y;
-    const unsigned long long seed = P.seed0 + (unsigned long long)s;
+    const unsigned long long seed = P.seed0 + (unsigned long long)s * P.seed_stride;
     for (int k = threadIdx.x; k < SY_PLANES * SY_WAVES; k += blockDim.x) {
         const int p = k / SY_WAVES, wv = k % SY_WAVES;
         const float sgu = sy_u01(seed, 4 * k + 0) < 0.5f ? -1.f : 1.f, sgv = sy_u01(seed, 4 * k + 1) < 0.5f ? -1.f : 1.f;
@@ -112,8 +115,33 @@ __global__ void __launch_bounds__(256) k_synth_render(const SynthParams P, float
         g = fminf(fmaxf(g, 0.02f), 0.98f);
         d = best; // the camera-frame ray has unit z, so lambda == z
     }
-    gray[(size_t)s * P.w * P.h + i] = g;
+    if (gray) gray[(size_t)s * P.w * P.h + i] = g;
+    if (gray8) gray8[(size_t)s * P.w * P.h + i] = (uint8_t)__float2int_rn(fminf(fmaxf(g * 255.0f, 0.0f), 255.0f));
     if (depth) depth[(size_t)s * P.w * P.h + i] = d;
+}
+
+// ground truth of the renderer for tests and error reporting: out[0..11] = camera-to-world [R | t] rows of frame `frame`,
+// out[12 ..] = the scene of `seed`: fu, fv, ph, amp as [SY_PLANES][SY_WAVES] each, then chk[SY_PLANES]
+constexpr int SY_INFO_FLOATS = 12 + 4 * SY_PLANES * SY_WAVES + SY_PLANES;
+__global__ void k_synth_info(unsigned long long seed, int frame, float trans_step, float rot_step, float* __restrict__ out)
+{
+    if (threadIdx.x == 0) {
+        float R[9], t[3];
+        sy_pose(seed, frame, trans_step, rot_step, R, t);
+        for (int r = 0; r < 3; r++) {
+            for (int q = 0; q < 3; q++) out[r * 4 + q] = R[r * 3 + q];
+            out[r * 4 + 3] = t[r];
+        }
+    }
+    const int NW = SY_PLANES * SY_WAVES;
+    for (int k = threadIdx.x; k < NW; k += blockDim.x) {
+        const float sgu = sy_u01(seed, 4 * k + 0) < 0.5f ? -1.f : 1.f, sgv = sy_u01(seed, 4 * k + 1) < 0.5f ? -1.f : 1.f;
+        out[12 + k] = sgu * (1.5f + 7.5f * sy_u01(seed, 4 * k + 2));
+        out[12 + NW + k] = sgv * (1.5f + 7.5f * sy_u01(seed, 4 * k + 3));
+        out[12 + 2 * NW + k] = 6.2831853f * sy_u01(seed, 500 + k);
+        out[12 + 3 * NW + k] = 0.3f + 0.7f * sy_u01(seed, 600 + k);
+    }
+    if (threadIdx.x < SY_PLANES) out[12 + 4 * NW + threadIdx.x] = 0.8f + 1.2f * sy_u01(seed, 700 + threadIdx.x);
 }
 
 } // namespace dvo

@@ -30,7 +30,7 @@ class DvoParams(C.Structure):
         ("map_roi_x0", C.c_int), ("map_roi_x1", C.c_int), ("map_roi_y0", C.c_int), ("map_roi_y1", C.c_int),
         ("min_movement", C.c_float), ("max_forward", C.c_int),
         ("accept_depth_lo", C.c_float), ("accept_depth_hi", C.c_float), ("accept_sigma_hi", C.c_float),
-        ("rng_table", C.c_int),
+        ("rng_table", C.c_int), ("huber_delta", C.c_float), ("min_gradient", C.c_float),
     ]
 
 
@@ -55,6 +55,10 @@ EXPORTS = [
     "dvo_frame_create_gray8", "dvo_vo_push_gray8", "dvo_vo_submit_gray8",
     "dvo_set_undistort_map", "dvo_frame_create_bgr8", "dvo_vo_push_bgr8", "dvo_vo_submit_bgr8",
     "dvo_kinect_configure", "dvo_frame_create_kinect",
+    "dvo_vo_push_gray8_dev", "dvo_synth_pose", "dvo_synth_scene", "dvo_event_record", "dvo_event_elapsed",
+    "dvo_synth_render_gray8_dev",
+    "dvo_transform_point", "dvo_project_point", "dvo_back_project_point", "dvo_gaussian_fuse", "dvo_gaussian_update", "dvo_gaussian_reseed",
+    "dvo_map_depth_to_gray", "dvo_select_pixels",
 ]
 
 
@@ -138,6 +142,20 @@ def load_library(path=None):
     lib.dvo_kinect_configure.argtypes = [C.c_void_p, C.POINTER(DvoKinectParams), F32P, F32P, F32P, F32P]
     lib.dvo_frame_create_kinect.argtypes = [C.c_void_p, I32P, C.c_void_p, C.c_void_p]
     lib.dvo_frame_create_bgr8.argtypes = [C.c_void_p, I32P, C.c_void_p, C.c_int]
+    lib.dvo_vo_push_gray8_dev.argtypes = [C.c_void_p, C.c_void_p, C.c_int, F32P, F32P, F32P]
+    lib.dvo_synth_pose.argtypes = [C.c_void_p, C.c_int, C.c_uint64, C.c_float, C.c_float, F32P]
+    lib.dvo_synth_scene.argtypes = [C.c_void_p, C.c_uint64, F32P, C.c_int]
+    lib.dvo_synth_render_gray8_dev.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_uint64, C.c_uint64, C.c_float, C.c_float]
+    lib.dvo_transform_point.argtypes = [F32P, F32P, F32P]
+    lib.dvo_project_point.argtypes = [F32P, F32P, F32P]
+    lib.dvo_back_project_point.argtypes = [F32P, F32P, C.c_float, F32P]
+    lib.dvo_gaussian_fuse.argtypes = [F32P, F32P, C.c_float, C.c_float]
+    lib.dvo_gaussian_update.argtypes = [F32P, F32P, C.c_float, C.c_float]
+    lib.dvo_gaussian_reseed.restype = None
+    lib.dvo_map_depth_to_gray.argtypes = [F32P, C.c_int, C.c_int, F32P, C.c_int, C.c_int, F32P, F32P, F32P, F32P, F32P]
+    lib.dvo_select_pixels.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_float, I32P, I32P]
+    lib.dvo_event_record.argtypes = [C.c_void_p, C.c_int]
+    lib.dvo_event_elapsed.argtypes = [C.c_void_p, C.c_int, C.c_int, F32P]
     lib.dvo_vo_push_bgr8.argtypes = [C.c_void_p, C.c_void_p, C.c_int, F32P, F32P, F32P]
     lib.dvo_vo_submit_bgr8.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
     return lib
@@ -448,6 +466,13 @@ class Dvo:
         self._ck(self.lib.dvo_mask_compact(self.ctx, m.ctypes.data_as(U8P), m.size, idx.ctypes.data_as(I32P), C.byref(cnt)))
         return idx[:cnt.value].copy()
 
+    def select_pixels(self, slot, level, min_gradient):
+        """Semi-dense selection by gradient threshold, compacted on the device: list of index arrays, one per stream."""
+        w, h = self.level_size(level)
+        idx = np.empty((self.S, w * h), np.int32); cnt = np.empty(self.S, np.int32)
+        self._ck(self.lib.dvo_select_pixels(self.ctx, slot, level, float(min_gradient), idx.ctypes.data_as(I32P), cnt.ctypes.data_as(I32P)))
+        return [idx[s, :cnt[s]].copy() for s in range(self.S)]
+
     # ---- VO
     def vo_reset(self):
         self._ck(self.lib.dvo_vo_reset(self.ctx))
@@ -537,6 +562,9 @@ class Dvo:
     def synth_render_dev(self, gray_dev, depth_dev, frame, seed0=1, trans_step=0.004, rot_step_deg=0.15):
         self._ck(self.lib.dvo_synth_render_dev(self.ctx, gray_dev, depth_dev, frame, seed0, trans_step, rot_step_deg))
 
+    def synth_render_gray8_dev(self, gray8_dev, depth_dev, frame, seed0=1, seed_stride=1, trans_step=0.004, rot_step_deg=0.15):
+        self._ck(self.lib.dvo_synth_render_gray8_dev(self.ctx, gray8_dev, depth_dev, frame, seed0, seed_stride, trans_step, rot_step_deg))
+
     def copy_to_host(self, arr, dev_ptr):
         self._ck(self.lib.dvo_copy_to_host(self.ctx, arr.ctypes.data_as(C.c_void_p), dev_ptr, arr.nbytes))
         return arr
@@ -553,7 +581,36 @@ class Dvo:
         self._ck(self.lib.dvo_vo_push_dev(self.ctx, gray_dev, _p(d), _p(s), _p(T)))
         return T
 
+    def vo_push_gray8_dev(self, gray8_dev, invalid_code=-1, init_depth=None, init_sigma=None, want_pose=False):
+        w, h = self.level_size(self.L - 1)
+        d = self._stack(init_depth, h, w) if init_depth is not None else None
+        s = self._stack(init_sigma, h, w) if init_sigma is not None else None
+        T = np.empty((self.S, 4, 4), np.float32) if want_pose else None
+        self._ck(self.lib.dvo_vo_push_gray8_dev(self.ctx, gray8_dev, int(invalid_code), _p(d), _p(s), _p(T)))
+        return T
+
+    def synth_pose(self, frame, seed, trans_step=0.004, rot_step_deg=0.15):
+        """Ground-truth camera-to-world pose of `frame` of the synthetic sequence `seed` (4x4)."""
+        T = np.empty(16, np.float32)
+        self._ck(self.lib.dvo_synth_pose(self.ctx, int(frame), int(seed), trans_step, rot_step_deg, _p(T)))
+        return T.reshape(4, 4)
+
+    def synth_scene(self, seed):
+        """The renderer's scene of `seed`: dict of fu, fv, ph, amp [5][8] and chk [5]."""
+        out = np.empty(165, np.float32)
+        self._ck(self.lib.dvo_synth_scene(self.ctx, int(seed), _p(out), out.size))
+        a = out[:160].reshape(4, 5, 8)
+        return dict(fu=a[0], fv=a[1], ph=a[2], amp=a[3], chk=out[160:165])
+
     # ---- measurement
+    def event_record(self, idx):
+        self._ck(self.lib.dvo_event_record(self.ctx, int(idx)))
+
+    def event_elapsed(self, i0, i1):
+        ms = C.c_float(0)
+        self._ck(self.lib.dvo_event_elapsed(self.ctx, int(i0), int(i1), C.byref(ms)))
+        return ms.value
+
     def sync(self):
         self._ck(self.lib.dvo_sync(self.ctx))
 

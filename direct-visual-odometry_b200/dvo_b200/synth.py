@@ -97,6 +97,42 @@ def sequence(n, w=640, h=480, K=None, seed=1234, **kw):
     return g, d, np.stack(poses).astype(np.float32), np.asarray(K, np.float32)
 
 
+def render_device_scene(scene, K, T_wc, w, h):
+    """The DEVICE renderer's image formation (csrc/dvo_synth.cuh: k_synth_render) restated in float64 numpy from the scene
+    parameters dvo_synth_scene returns and a camera-to-world pose: (gray[h,w], depth[h,w]).  Used only to check the kernel."""
+    K = np.asarray(K, np.float64).reshape(3, 3)
+    R = np.asarray(T_wc, np.float64)[:3, :3]
+    t = np.asarray(T_wc, np.float64)[:3, 3]
+    zb, xw, yw = 2.6, 1.9, 1.4
+    xs, ys = np.meshgrid(np.arange(w, dtype=np.float64), np.arange(h, dtype=np.float64))
+    dc = np.stack([(xs - K[0, 2]) / K[0, 0], (ys - K[1, 2]) / K[1, 1], np.ones_like(xs)], -1)
+    dw = dc @ R.T
+    best = np.full((h, w), 1e30)
+    gray = np.zeros((h, w))
+    hit = np.zeros((h, w), bool)
+    for p, (axis, val) in enumerate([(2, zb), (0, xw), (0, -xw), (1, yw), (1, -yw)]):
+        with np.errstate(divide="ignore", invalid="ignore"):
+            lam = (val - t[axis]) / dw[..., axis]
+        P = t + lam[..., None] * dw
+        ok = (lam > 1e-6) & (lam < best)
+        ok &= ~((np.abs(P[..., 0]) > xw + 1e-4) | (np.abs(P[..., 1]) > yw + 1e-4) | (P[..., 2] > zb + 1e-4))
+        if axis == 2:
+            u, v = P[..., 0], P[..., 1]
+        elif axis == 0:
+            u, v = P[..., 2], P[..., 1]
+        else:
+            u, v = P[..., 0], P[..., 2]
+        tsum = np.zeros((h, w))
+        for k in range(scene["fu"].shape[1]):
+            tsum += scene["amp"][p, k] * np.sin(scene["fu"][p, k] * u + scene["fv"][p, k] * v + scene["ph"][p, k])
+        ck = np.sin(scene["chk"][p] * np.pi * u) * np.sin(scene["chk"][p] * np.pi * v)
+        g = np.clip(0.5 + 0.33 * (tsum / scene["amp"][p].sum()) + np.where(ck > 0, 0.10, -0.10), 0.02, 0.98)
+        gray = np.where(ok, g, gray)
+        best = np.where(ok, lam, best)
+        hit |= ok
+    return gray.astype(np.float32), np.where(hit, best, 0.0).astype(np.float32)
+
+
 def random_depth_prior(shape, seed=4321):
     """Stand-in for Scene's cv::randn(1.5, 0.5) clipped below at 0.5 and sigma = 0.5
     (include/system/frame.hpp:18-21): same distribution, NumPy PCG64 stream."""

@@ -70,6 +70,7 @@ inline dvo_params make_params(int w, int h, int levels, int culls, const Mat1f& 
     dvo_params_default(&p);
     p.n_streams = 1; p.width = w; p.height = h; p.levels = levels; p.culls = culls;
     p.max_frames = 1024;  // FrameHistory is never pruned (frame.hpp:179-185); slots are allocated on first use
+    p.max_keyframes = p.max_frames;  // Map::Mapper::update is handed the whole FrameHistory: as many keyframes as there can be frames
     for (int r = 0; r < 3; r++)
         for (int c = 0; c < 3; c++) p.K[r * 3 + c] = K(r, c);
     return p;

@@ -4,13 +4,13 @@
 #pragma once
 #include "../device.hpp"
 
+#include <array>
 #include <cmath>
+
+#include "util.hpp"
 
 namespace math
 {
-constexpr float INVALID = DVO_INVALID;  // include/math/util.hpp:7
-constexpr float EPSILON = 1e-6f;        // include/math/util.hpp:8
-
 namespace se3
 {
 using dvo::Mat1f;
@@ -22,6 +22,12 @@ inline Mat1f xi(std::initializer_list<float> v)
     Mat1f out(6, 1);
     int i = 0;
     for (float f : v) out(i++) = f;
+    return out;
+}
+inline Mat1f xi(const std::array<float, 6>& v)  // test/warp.cpp:40
+{
+    Mat1f out(6, 1);
+    for (int i = 0; i < 6; i++) out(i) = v[i];
     return out;
 }
 inline Mat1f T()  // 4x4 identity

@@ -34,7 +34,7 @@ typedef enum dvo_status {
     DVO_ERR_ARG = -2,      /* bad argument */
     DVO_ERR_SLOT = -3,     /* bad / exhausted frame slot */
     DVO_ERR_HISTORY = -4,  /* age >= history size: std::vector::at would throw (frame.hpp:176) */
-    DVO_ERR_RNG = -5,      /* mt19937 replay table exhausted */
+    DVO_ERR_RNG = -5,      /* mt19937 replay table cannot grow further (2^32 draws) */
     DVO_ERR_STATE = -6     /* call sequence error */
 } dvo_status;
 
@@ -62,8 +62,15 @@ typedef struct dvo_params {
     float min_movement; /* 0.02 */
     int max_forward;    /* 6 */
     float accept_depth_lo, accept_depth_hi, accept_sigma_hi; /* 0.2, 6.0, 0.5 */
-    /* mt19937 replay table length (draws) for Gaussian::update's reset (src/math/gaussian.cpp:8-9,22) */
+    /* INITIAL length (draws) of the mt19937 replay table for Gaussian::update's reset (src/math/gaussian.cpp:8-9,22); the table
+     * grows on demand (the reference's engine is unbounded) */
     int rng_table;      /* default 1<<22 */
+    /* Extras that north_star names and the REFERENCE DOES NOT HAVE: 0 = off = the reference's behaviour (default).
+     * min_gradient: semi-dense selection - a pixel enters Track::optimize only if gx^2 + gy^2 >= min_gradient^2 (the gradients
+     * sampled at its warped position, fp32).  huber_delta: variance-normalised Huber weight - its row of A and entry of B
+     * (optimize.cpp:87-89) are scaled by sqrt(w), w = 1 if |r| / sigma <= huber_delta else huber_delta / (|r| / sigma), sigma the
+     * clamped sigma of optimize.cpp:83.  The oracle implements the same definition (orc_params), so parity holds with them on. */
+    float huber_delta, min_gradient;
 } dvo_params;
 
 typedef struct dvo_ctx dvo_ctx;
@@ -219,10 +226,34 @@ int dvo_se3_exp(dvo_ctx* ctx, const float* xi, float* T, int n);                
 int dvo_se3_log(dvo_ctx* ctx, const float* T, float* xi, int n);                        /* se3::log   se3.cpp:102-124 */
 int dvo_se3_concatenate(dvo_ctx* ctx, const float* a, const float* b, float* out, int n); /* log(exp(a)*exp(b)) se3.cpp:127-131 */
 
+/* ---- scalar boundary helpers: Transform::{transform, project, backProject} (include/core/transform.hpp:8-16, src/core/transform.cpp:7-28)
+ * and math::Gaussian (include/math/gaussian.hpp:8-17, src/math/gaussian.cpp:12-50).  Host arithmetic in the reference's fp32 order,
+ * compiled inside the library so that a caller's -ffast-math / FMA contraction cannot change a rounding.  Transform::warp is their
+ * composition with se3::exp (include/dvo/core/transform.hpp). */
+int dvo_transform_point(const float T[16], const float x[3], float out[3]);   /* R x + t of a row-major 4x4 */
+int dvo_project_point(const float K[9], const float p[3], float out[2]);      /* (X fx / Z + cx, Y fy / Z + cy) */
+int dvo_back_project_point(const float K[9], const float xy[2], float depth, float out[3]);
+/* Gaussian::operator()(d, s): 1 = fused into (*depth, *sigma), 0 = refused (unchanged). */
+int dvo_gaussian_fuse(float* depth, float* sigma, float d, float s);
+/* Gaussian::update(d, s): like operator() but a refused observation RESETS the hypothesis to min(dist(engine), 4) / 0.5 from a
+ * process-wide default-seeded std::mt19937 (gaussian.cpp:8-9,21-25); dvo_gaussian_reseed() restarts that engine. */
+int dvo_gaussian_update(float* depth, float* sigma, float d, float s);
+void dvo_gaussian_reseed(void);
+/* Transform::mapDepthtoGray (include/core/transform.hpp:17-22, src/core/transform.cpp:53-78) on raw host images, computed on the
+ * device: depth [h][w] (the depth camera), gray [gh][gw] (the colour camera), invT row-major 4x4 (depth -> colour);
+ * mapped / sigma: [h][w].  Needs no context; DVO_ERR_CUDA without a device. */
+int dvo_map_depth_to_gray(const float* depth, int w, int h, const float* gray, int gw, int gh, const float rgb_K[9],
+                          const float depth_K[9], const float invT[16], float* mapped, float* sigma);
+
 /* ---- mask compaction ----------------------------------------------------------- */
 /* Row-major compaction of a byte mask on device: idx receives the linear indices of non-zero
  * entries in increasing order; returns their number in *count. */
 int dvo_mask_compact(dvo_ctx* ctx, const uint8_t* mask, int n, int32_t* idx, int* count);
+/* Semi-dense pixel selection of one pyramid level of a frame by gradient threshold (north_star; no reference counterpart), selected
+ * and compacted on the device: pixel (x, y) is kept iff its gray, Convert::gradiate x and y values are all valid and
+ * gx^2 + gy^2 >= min_gradient^2.  idx ([n_streams][w_l h_l], row-major linear indices in increasing order, the first count[s]
+ * entries of stream s are meaningful), count: [n_streams]. */
+int dvo_select_pixels(dvo_ctx* ctx, int slot, int level, float min_gradient, int32_t* idx, int* count);
 
 /* ---- full VO: System::VisualOdometry (include/system/system.hpp:12-104) --------------------- */
 int dvo_vo_reset(dvo_ctx* ctx);
@@ -232,8 +263,13 @@ int dvo_vo_reserve(dvo_ctx* ctx, int n_keyframes);
 /* VisualOdometry::odometrize(gray) (system.hpp:44-74) for every stream; the whole frame (pyramid,
  * <= levels*15 GN iterations, keyframe decision, propagate | update, regularize) is enqueued
  * without host synchronisation.  init_depth/init_sigma ([n_streams][h_top][w_top], nullable
- * after the first frame) replace the cv::randn prior of Scene's ctor (frame.hpp:18-21).
- * T_out ([n_streams][16], nullable) = se3::exp(frame->m_xi); passing NULL keeps the call async. */
+ * after the first frame) replace the cv::randn prior of Scene's ctor (frame.hpp:18-21); the FIRST frame of a sequence must
+ * bring init_depth (DVO_ERR_STATE otherwise: without a prior every pixel fails optimize's depth gate).
+ * T_out ([n_streams][16], nullable) = se3::exp(frame->m_xi); passing NULL keeps the call async.
+ * Per frame the library launches: ingest, k_track (all levels x iterations + keyframe decision + Implement::propagate + the pose),
+ * k_map_update (Mapper::update; as a programmatic dependent of k_track, so finished streams are mapped while others still
+ * iterate), its reset pass, k_regularize (+ Frame::updateDepth).  A device-side error of any stream (DVO_ERR_HISTORY: keyframe
+ * capacity exhausted) is returned by the call that reads the poses back; that stream is tracked but no longer mapped. */
 int dvo_vo_push(dvo_ctx* ctx, const float* gray, const float* init_depth, const float* init_sigma, float* T_out);
 int dvo_vo_push_dev(dvo_ctx* ctx, const float* gray_dev, const float* init_depth, const float* init_sigma, float* T_out);
 /* Pipelined form of dvo_vo_push for throughput: dvo_vo_submit stages `gray` (pinned host memory from
@@ -243,12 +279,15 @@ int dvo_vo_push_dev(dvo_ctx* ctx, const float* gray_dev, const float* init_depth
  * by the time the matching dvo_vo_collect returns.  At most 2 frames may be in flight; collect returns
  * them in submission order.  Results are identical to dvo_vo_push. */
 int dvo_vo_submit(dvo_ctx* ctx, const float* gray, float* T_out);
-int dvo_vo_collect(dvo_ctx* ctx);
+int dvo_vo_collect(dvo_ctx* ctx); /* also returns a device-side error flagged up to the collected frame (when it had a T_out) */
 /* dvo_vo_push / dvo_vo_submit from 8-bit gray frames (see dvo_frame_create_gray8): Loader::getNormalizedImages'
  * convertTo (loader.cpp:61) runs on the device.  Results are bit-identical to feeding the float frames
  * (float)code * (float)(1.0/255.0) to dvo_vo_push. */
 int dvo_vo_push_gray8(dvo_ctx* ctx, const uint8_t* gray8, int invalid_code, const float* init_depth, const float* init_sigma,
                       float* T_out);
+/* the same with the 8-bit frames already in device memory ([n_streams][height][width] uint8, e.g. from dvo_dev_alloc) */
+int dvo_vo_push_gray8_dev(dvo_ctx* ctx, const uint8_t* gray8_dev, int invalid_code, const float* init_depth, const float* init_sigma,
+                          float* T_out);
 int dvo_vo_submit_gray8(dvo_ctx* ctx, const uint8_t* gray8, int invalid_code, float* T_out);
 /* ... and from 8-bit BGR / BGRA frames through the undistortion map (see dvo_frame_create_bgr8).  The whole frame crosses PCIe
  * (3 or 4 bytes per input pixel), so this form is for hosts that cannot spare the cores for cvtColor + remap. */
@@ -285,6 +324,15 @@ int dvo_vo_error(dvo_ctx* ctx);
  * gray_dev: [n_streams][height][width] device floats in [0,1]; depth_dev (nullable): ground-truth z. */
 int dvo_synth_render_dev(dvo_ctx* ctx, float* gray_dev, float* depth_dev, int frame, uint64_t seed0, float trans_step,
                          float rot_step_deg);
+/* The same image as 8-bit codes (round-half-even of 255 g: what a camera / cv::imread + cvtColor hand the loader), stream s using
+ * seed0 + s * seed_stride (sharded sequence ids).  gray8_dev: [n_streams][height][width] device bytes. */
+int dvo_synth_render_gray8_dev(dvo_ctx* ctx, uint8_t* gray8_dev, float* depth_dev, int frame, uint64_t seed0, uint64_t seed_stride,
+                               float trans_step, float rot_step_deg);
+/* Ground truth of that renderer: the camera-to-world pose of `frame` of the sequence with seed `seed` (row-major 4x4), and the
+ * scene itself (out: fu, fv, phase, amplitude as [5 planes][8 waves] each, then the 5 checker frequencies = 165 floats), so that
+ * tests can re-render a frame independently and benchmarks can report the trajectory error against ground truth (C3). */
+int dvo_synth_pose(dvo_ctx* ctx, int frame, uint64_t seed, float trans_step, float rot_step_deg, float* T_wc /*[16]*/);
+int dvo_synth_scene(dvo_ctx* ctx, uint64_t seed, float* out, int cap);
 /* plain device memory for inputs that stay resident (benchmarks), and copies on the context's stream */
 void* dvo_dev_alloc(size_t bytes);
 void dvo_dev_free(void* p);
@@ -294,6 +342,9 @@ int dvo_copy_to_dev(dvo_ctx* ctx, void* dev, const void* host, size_t bytes);   
 /* ---- measurement helpers (CUDA events on the context's stream) -------------------------------- */
 int dvo_timer_start(dvo_ctx* ctx);
 int dvo_timer_stop(dvo_ctx* ctx, float* ms); /* synchronises */
+/* any number of marks on the context's stream (id 0..65535) and the device time between two of them */
+int dvo_event_record(dvo_ctx* ctx, int id);
+int dvo_event_elapsed(dvo_ctx* ctx, int id0, int id1, float* ms); /* synchronises on id1 */
 /* number of kernels this context has launched since creation */
 uint64_t dvo_launch_count(const dvo_ctx* ctx);
 /* Device time per kernel between kernel_timing(1, ...) and kernel_timing(0, out, cap, &n): CUDA events

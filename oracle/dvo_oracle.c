@@ -64,6 +64,7 @@ void orc_params_default(orc_params* p)
     p->min_movement = 0.02f;
     p->max_forward = 6;
     p->accept_depth_lo = 0.2f; p->accept_depth_hi = 6.0f; p->accept_sigma_hi = 0.5f;
+    p->huber_delta = 0.0f; p->min_gradient = 0.0f;
 }
 
 /* small cv::gemm: fp32 dot products evaluated left to right, no FMA. */
@@ -575,11 +576,29 @@ int orc_solve_svd(const float* A, const float* b, int m, int n, float* x)
 /* ------------------------------------------------------------------------------------------ */
 /* track — src/track/optimize.cpp:10-99                                                       */
 /* ------------------------------------------------------------------------------------------ */
+/* sys_A / sys_B (optional, caller-allocated w*h*6 / w*h floats): the stacked system cv::solve is handed, rows of valid pixels
+ * only, B already negated (optimize.cpp:87-97) - lets a test solve the very same system in fp64. */
+void orc_optimize_system(const float* obj_gray, const float* warped_gray, const float* ref_depth,
+                         const float* ref_sigma, const float* grad_x, const float* grad_y,
+                         const float K[9], const float xi[6], int w, int h, int level_index,
+                         const orc_params* P, float upd[6], float* residual_out, int* valid_out,
+                         uint8_t* mask, float* sys_A, float* sys_B);
+
 void orc_optimize(const float* obj_gray, const float* warped_gray, const float* ref_depth,
                   const float* ref_sigma, const float* grad_x, const float* grad_y,
                   const float K[9], const float xi[6], int w, int h, int level_index,
                   const orc_params* P, float upd[6], float* residual_out, int* valid_out,
                   uint8_t* mask)
+{
+    orc_optimize_system(obj_gray, warped_gray, ref_depth, ref_sigma, grad_x, grad_y, K, xi, w, h, level_index, P, upd, residual_out,
+                        valid_out, mask, NULL, NULL);
+}
+
+void orc_optimize_system(const float* obj_gray, const float* warped_gray, const float* ref_depth,
+                         const float* ref_sigma, const float* grad_x, const float* grad_y,
+                         const float K[9], const float xi[6], int w, int h, int level_index,
+                         const orc_params* P, float upd[6], float* residual_out, int* valid_out,
+                         uint8_t* mask, float* sys_A, float* sys_B)
 {
     float residual = 0;
     const float fx = K[0], fy = K[4];
@@ -616,6 +635,7 @@ void orc_optimize(const float* obj_gray, const float* warped_gray, const float* 
             float gx = orc_get_subpixel_dense(grad_x, w, h, wp[0], wp[1]);
             float gy = orc_get_subpixel_dense(grad_y, w, h, wp[0], wp[1]);
             if (orc_is_invalid(gx) || orc_is_invalid(gy)) continue; /* :61 */
+            if (P->min_gradient > 0.0f && gx * gx + gy * gy < P->min_gradient * P->min_gradient) continue; /* extra, default off */
 
             /* jacobian :67-77 */
             float X = depth * ((float)x - K[2]) / K[0];
@@ -637,11 +657,20 @@ void orc_optimize(const float* obj_gray, const float* warped_gray, const float* 
             float sigma = (s < P->sigma_lo) ? P->sigma_lo : (P->sigma_hi < s) ? P->sigma_hi : s;
             float weight = step / sigma;
             B[valid_pixels] = -(r * weight); /* cv::solve(A, -B, ...) :97 */
+            if (P->huber_delta > 0.0f) { /* extra, default off: variance-normalised Huber weight, rows scaled by sqrt(w) */
+                float t = fabsf(r) / sigma;
+                float wh = (t <= P->huber_delta) ? 1.0f : P->huber_delta / t;
+                float sw = sqrtf(wh);
+                for (int q = 0; q < 6; q++) J[q] = J[q] * sw;
+                B[valid_pixels] = B[valid_pixels] * sw;
+            }
             valid_pixels++;
             if (mask) mask[id] = 1;
         }
 
     *valid_out = valid_pixels;
+    if (sys_A) memcpy(sys_A, A, (size_t)valid_pixels * 6 * sizeof(float));
+    if (sys_B) memcpy(sys_B, B, (size_t)valid_pixels * sizeof(float));
     if (valid_pixels == 0) { /* :92-93 */
         for (int i = 0; i < 6; i++) upd[i] = 0;
         *residual_out = -1;

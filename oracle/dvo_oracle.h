@@ -41,6 +41,11 @@ typedef struct orc_params {
     float min_movement; /* 0.02 */
     int max_forward;    /* 6 */
     float accept_depth_lo, accept_depth_hi, accept_sigma_hi; /* 0.2, 6.0, 0.5 */
+    /* Extras north_star names that the REFERENCE DOES NOT HAVE; 0 = off = the reference's behaviour.  Same definition
+     * on the GPU (dvo_params.huber_delta / min_gradient): a pixel enters Track::optimize only if gx^2 + gy^2 >= min_gradient^2
+     * (sampled gradients, fp32), and its row of A and entry of B are scaled by sqrt(w), w = 1 if |r| / sigma <= huber_delta else
+     * huber_delta / (|r| / sigma), sigma the clamped sigma of optimize.cpp:83. */
+    float huber_delta, min_gradient;
 } orc_params;
 
 void orc_params_default(orc_params* p);
@@ -82,6 +87,11 @@ void orc_optimize(const float* obj_gray, const float* warped_gray, const float* 
                   const float K[9], const float xi[6], int w, int h, int level_index,
                   const orc_params* P, float upd[6], float* residual, int* valid_pixels,
                   uint8_t* mask);
+void orc_optimize_system(const float* obj_gray, const float* warped_gray, const float* ref_depth,
+                  const float* ref_sigma, const float* grad_x, const float* grad_y,
+                  const float K[9], const float xi[6], int w, int h, int level_index,
+                  const orc_params* P, float upd[6], float* residual, int* valid_pixels,
+                  uint8_t* mask, float* sys_A, float* sys_B);
 
 typedef struct orc_iter_log {
     int level, iteration, valid_pixels;

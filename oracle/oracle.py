@@ -23,6 +23,7 @@ class OrcParams(C.Structure):
         ("map_roi_x0", C.c_int), ("map_roi_x1", C.c_int), ("map_roi_y0", C.c_int), ("map_roi_y1", C.c_int),
         ("min_movement", C.c_float), ("max_forward", C.c_int),
         ("accept_depth_lo", C.c_float), ("accept_depth_hi", C.c_float), ("accept_sigma_hi", C.c_float),
+        ("huber_delta", C.c_float), ("min_gradient", C.c_float),
     ]
 
 
@@ -221,6 +222,20 @@ class Oracle:
         self.lib.orc_optimize(*[_p(a) for a in arrs], _p(K), _p(xi), C.c_int(w), C.c_int(h), C.c_int(level_index),
                               C.byref(P), _p(upd), _p(res), C.byref(valid), mask.ctypes.data_as(U8P))
         return upd, float(res[0]), valid.value, mask
+
+    def optimize_system(self, obj_gray, warped_gray, ref_depth, ref_sigma, gx, gy, K, xi, level_index, params=None):
+        """Track::optimize plus the stacked system it hands to cv::solve: (upd, residual, valid, A[valid, 6], b[valid]) with
+        A x = b the reference's `cv::solve(A, -B, x, DECOMP_SVD)` and upd = -x (optimize.cpp:87-98)."""
+        arrs = [_f32(a) for a in (obj_gray, warped_gray, ref_depth, ref_sigma, gx, gy)]
+        h, w = arrs[0].shape
+        K = _f32(K).reshape(-1); xi = _f32(xi)
+        P = params or self.params()
+        upd = np.empty(6, np.float32); res = np.empty(1, np.float32); valid = C.c_int(0)
+        A = np.empty((h * w, 6), np.float32); B = np.empty(h * w, np.float32)
+        self.lib.orc_optimize_system.argtypes = None
+        self.lib.orc_optimize_system(*[_p(a) for a in arrs], _p(K), _p(xi), C.c_int(w), C.c_int(h), C.c_int(level_index),
+                                     C.byref(P), _p(upd), _p(res), C.byref(valid), None, _p(A), _p(B))
+        return upd, float(res[0]), valid.value, A[:valid.value].copy(), B[:valid.value].copy()
 
     # ---- frames
     def frame_create(self, gray, K, levels, culls, depth=None, sigma=None):

@@ -2,9 +2,14 @@
 """Summaries of ncu output for profiles/ (run here, no GPU needed).
   launches <launches.csv>            per-kernel count / total / average / share of device time
   full <prof.ncu-rep>                selected raw metrics per profiled launch
-  traffic <prof.ncu-rep>             JSON {kernel: {dram_bytes, dram_read, dram_write, duration_us}} of the FIRST captured launch of each
-                                     kernel (dram__bytes_read.sum + dram__bytes_write.sum) - bench.py's roofline.traffic reads it
+  traffic <prof.ncu-rep>             JSON {kernel: {dram_bytes, dram_read, dram_write, duration_us, ...}} of the FIRST captured launch of each
+                                     kernel (dram__bytes_read.sum + dram__bytes_write.sum) - bench.py's roofline.traffic reads it; also the
+                                     issue figures bench.py's roofline.issue reads (warp instructions, IPC, issue-slot utilisation)
+  issue <prof.ncu-rep>               for every captured launch: issue-slot utilisation, IPC, per-pipe utilisation (ALU / FMA / XU / LSU /
+                                     FP64 / ...) and the warp stall reasons, largest first - every column of the report that matches
+  sass <lib.so> <kernel> [lo hi]     SASS of one kernel with an instruction histogram (cuobjdump; no GPU)
 """
+import re
 import collections
 import csv
 import io
@@ -66,11 +71,72 @@ def traffic(path):
         for key, col, mul in (("lts_bytes", "lts__t_sectors.sum", 32.0), ("lts_pct_of_peak", "lts__throughput.avg.pct_of_peak_sustained_elapsed", 1.0),
                               ("l1tex_pct_of_peak", "l1tex__throughput.avg.pct_of_peak_sustained_elapsed", 1.0),
                               ("sm_pct_of_peak", "sm__throughput.avg.pct_of_peak_sustained_elapsed", 1.0),
-                              ("l2_hit_pct", "lts__t_sector_hit_rate.pct", 1.0), ("l1_hit_pct", "l1tex__t_sector_hit_rate.pct", 1.0)):
+                              ("l2_hit_pct", "lts__t_sector_hit_rate.pct", 1.0), ("l1_hit_pct", "l1tex__t_sector_hit_rate.pct", 1.0),
+                              ("warp_inst", "smsp__inst_executed.sum", 1.0), ("ipc_active", "sm__inst_executed.avg.per_cycle_active", 1.0),
+                              ("ipc_elapsed", "sm__inst_executed.avg.per_cycle_elapsed", 1.0),
+                              ("issue_active_pct", "smsp__issue_active.avg.pct_of_peak_sustained_active", 1.0),
+                              ("warps_active_pct", "sm__warps_active.avg.pct_of_peak_sustained_active", 1.0)):
             if col in idx and r[idx[col]] not in ("", "n/a"):
                 res[k][key] = float(r[idx[col]].replace(",", "")) * mul
     print(json.dumps(dict(source=path.split("/")[-1], how="ncu --set full --clock-control none, first captured launch of each kernel", kernels=res), indent=1))
 
 
+ISSUE_PATTERNS = [r"issue_active", r"inst_executed\.avg\.per_cycle", r"inst_issued\.avg\.per_cycle", r"inst_executed\.sum$", r"thread_inst_executed",
+                  r"sm__inst_executed_pipe_", r"sm__pipe_.*cycles_active", r"pipe_.*pct_of_peak", r"issue_stalled", r"warps_eligible",
+                  r"warps_active", r"achieved_occupancy", r"sm__throughput", r"l1tex__throughput", r"lts__throughput", r"gpu__time_duration"]
+
+
+def issue(path):
+    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(out)))
+    hdr, unit = rows[0], rows[1]
+    name_i = hdr.index("Kernel Name")
+    cols = [i for i, h in enumerate(hdr) if any(re.search(p, h) for p in ISSUE_PATTERNS)]
+    for r in rows[2:]:
+        print("== %s  (ID %s)" % (r[name_i].split("(")[0], r[0]))
+        stalls, rest = [], []
+        for i in cols:
+            if r[i] in ("", "n/a"):
+                continue
+            try:
+                v = float(r[i].replace(",", ""))
+            except ValueError:
+                continue
+            (stalls if "issue_stalled" in hdr[i] else rest).append((hdr[i], v, unit[i]))
+        for h, v, u in rest:
+            print("   %-86s %14.4f %s" % (h, v, u))
+        print("   -- warp stall reasons, largest first")
+        for h, v, u in sorted(stalls, key=lambda t: -t[1]):
+            if v > 0:
+                print("   %-86s %14.4f %s" % (h, v, u))
+
+
+def sass(lib, kernel, lo=None, hi=None):
+    """SASS listing of `kernel` (substring of the mangled name) from `lib`, optionally only instruction offsets [lo, hi] (hex), with a
+    mnemonic histogram - the evidence behind "instructions per search step / per pixel" in DESIGN.md."""
+    out = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True).stdout
+    cur = None; lines = []
+    for ln in out.splitlines():
+        m = re.search(r"Function : (\S+)", ln)
+        if m:
+            cur = m.group(1)
+            continue
+        if cur and kernel in cur:
+            m = re.match(r"\s+/\*([0-9a-f]{4,5})\*/\s+(.*?);", ln)
+            if m:
+                lines.append((int(m.group(1), 16), m.group(2).strip()))
+    lo = int(lo, 16) if lo else 0
+    hi = int(hi, 16) if hi else 1 << 30
+    sel = [(o, t) for o, t in lines if lo <= o <= hi]
+    hist = collections.Counter()
+    for o, t in sel:
+        op = t.split()[1] if t.startswith("@") else t.split()[0]
+        hist[op.split(".")[0]] += 1
+        print("/*%04x*/ %s" % (o, t))
+    print("# %d instructions in [%#x, %#x] of %s" % (len(sel), lo, min(hi, lines[-1][0] if lines else 0), kernel))
+    print("# " + ", ".join("%s %d" % kv for kv in hist.most_common()))
+
+
 if __name__ == "__main__":
-    {"launches": launches, "full": full, "traffic": traffic}[sys.argv[1]](sys.argv[2])
+    fn = {"launches": launches, "full": full, "traffic": traffic, "issue": issue, "sass": sass}[sys.argv[1]]
+    fn(*sys.argv[2:])

@@ -6,13 +6,19 @@
 //   in.bin : int32 n, w, h; float K[9]; n gray frames [h][w]; depth0 [h][w]; sigma0 [h][w];
 //            prior depth [h/4][w/4]; prior sigma [h/4][w/4]
 //   out.bin: sequence of (int32 count, float[count]) records, in the order written below
+#include "dvo/core/convert.hpp"
 #include "dvo/core/draw.hpp"
 #include "dvo/core/transform.hpp"
+#include "dvo/math/gaussian.hpp"
+#include "dvo/multi_gpu.hpp"
 #include "dvo/map/implement.hpp"
 #include "dvo/map/mapper.hpp"
 #include "dvo/system/system.hpp"
 #include "dvo/track/tracker.hpp"
 
+#include <algorithm>
+#include <array>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
@@ -131,6 +137,81 @@ int main(int argc, char** argv)
         // the reference's own call forms (src/map/mapper.cpp:37-42): raw images
         put_img(Draw::visualizeGray(kf->gray())); put_img(Draw::visualizeDepth(kf->depth(), kf->sigma()));
         put_img(Draw::visualizeDepth(kf->depth())); put_img(Draw::visualizeAge(kf->age())); put_img(Draw::visualizeGradient(kf->gradX()));
+        // 11. test/update.cpp:51-116, literally (on images culled x8 so that the per-pixel calls stay few): gradients, a noisy
+        //     depth prior, Map::Implement::update per pixel + math::Gaussian::operator(), then Map::Implement::regularize
+        {
+            const Mat1f ref_gray = Convert::cullImage(gray[0], 3), obj_gray = Convert::cullImage(gray[2], 3);
+            const Mat1f Kc = Convert::cullIntrinsic(K, 3);
+            Mat1f ref_gradx = Convert::gradiate(ref_gray, true);
+            Mat1f ref_grady = Convert::gradiate(ref_gray, false);
+            const Mat1f uxi2 = math::se3::xi({-0.1f, 0, 0, 0, 0, 0});  // test/update.cpp:58
+            Mat1f ref_depth = Convert::cullImage(prior_d, 1).clone();  // stands in for the cv::randn noise of :64-68
+            Mat1f ref_sigma(ref_depth.rows, ref_depth.cols, 0.5f);     // :71
+            put(ref_gray); put(Kc); put(ref_gradx); put(ref_grady);
+            for (int y = 0; y < ref_depth.rows; y++)
+                for (int x = 0; x < ref_depth.cols; x++) {             // ref_depth.forEach, row-major
+                    const dvo::Point2i x_i(x, y);
+                    float& depth = ref_depth(x_i);
+                    float sigma = ref_sigma(x_i);
+                    depth = std::max(depth, 0.1f);
+                    auto [new_depth, new_sigma] = Map::Implement::update(obj_gray, ref_gray, ref_gradx, ref_grady, uxi2, Kc, x_i, depth, sigma);
+                    if (new_depth > 0 and new_depth < 6.0) {
+                        math::Gaussian g(depth, sigma);
+                        g(new_depth, new_sigma);
+                        ref_depth(x_i) = g.depth;
+                        ref_sigma(x_i) = g.sigma;
+                    }
+                }
+            put(ref_depth); put(ref_sigma);
+            ref_depth = Map::Implement::regularize(ref_depth, ref_sigma);  // :115
+            put(ref_depth);
+            // math::Gaussian::update: the reset branch draws from the process-wide mt19937
+            dvo_gaussian_reseed();
+            math::Gaussian g1(1.0f, 0.1f), g2(1.0f, 0.1f);
+            const bool f1 = g1.update(3.0f, 0.1f), f2 = g2.update(1.05f, 0.2f);
+            put(f1 ? 1.f : 0.f); put(g1.depth); put(g1.sigma); put(f2 ? 1.f : 0.f); put(g2.depth); put(g2.sigma);
+        }
+        // 12. test/warp.cpp:27-42: cullImage / cullIntrinsic, then Transform::warpImage on the culled images
+        {
+            Mat1f gray_image = Convert::cullImage(gray[0], 1), depth_image = Convert::cullImage(depth0, 1);
+            Mat1f Kw = Convert::cullIntrinsic(K, 1);
+            std::array<float, 6> params_f = {0.02f, -0.01f, 0.03f, 0.01f, -0.02f, 0.005f};
+            Mat1f wxi = math::se3::xi(params_f);
+            put(math::se3::exp(wxi));
+            put(Transform::warpImage(wxi, gray_image, depth_image, Kw));
+        }
+        // 13. the scalar boundary: math::testXi (test/track.cpp:55), Transform::{backProject, transform, project, warp}, mapDepthtoGray
+        {
+            Mat1f bad = math::se3::xi(); bad(3) = std::nanf("");
+            put(math::testXi(xi) ? 1.f : 0.f); put(math::testXi(bad) ? 1.f : 0.f);
+            const Transform::Point2f px(123.25f, 77.5f);
+            const Transform::Point3f xc = Transform::backProject(K, px, 1.7f);
+            const Mat1f Tm = math::se3::exp(xi);
+            const Transform::Point3f xt = Transform::transform(Tm, xc), xt2 = Transform::transform(xi, xc);
+            const Transform::Point2f pj = Transform::project(K, xt), wp = Transform::warp(xi, px, 1.7f, K);
+            const float v[] = {xc.x, xc.y, xc.z, xt.x, xt.y, xt.z, xt2.x, xt2.y, xt2.z, pj.x, pj.y, wp.x, wp.y};
+            put(v, 13);
+            Mat1f invT = math::se3::exp(math::se3::xi({0.05f, -0.01f, 0.0f, 0.01f, 0.02f, -0.01f}));
+            auto md = Transform::mapDepthtoGray(Convert::cullImage(depth0, 1), gray[1], K, Convert::cullIntrinsic(K, 1), invT);
+            put(invT); put(md.first); put(md.second);
+        }
+        // 14. dvo::MultiGpu: 3 sequences over the node's GPUs (one on this box), id mod nGPU; == the single-context run of step 7
+        {
+            dvo_params p = dvo::make_params(w, h, 3, 2, K);
+            p.max_frames = 2; p.max_keyframes = n + 2;
+            dvo::MultiGpu mg(3, p);
+            std::vector<float> g3((size_t)3 * w * h), d3((size_t)3 * prior_d.total()), s3(d3.size()), T3(3 * 16);
+            put((float)mg.world());
+            for (int i = 0; i < n; i++) {
+                for (int q = 0; q < 3; q++) {
+                    std::memcpy(&g3[(size_t)q * w * h], dvo::data(gray[i]), sizeof(float) * (size_t)w * h);
+                    std::memcpy(&d3[q * prior_d.total()], dvo::data(prior_d), sizeof(float) * prior_d.total());
+                    std::memcpy(&s3[q * prior_s.total()], dvo::data(prior_s), sizeof(float) * prior_s.total());
+                }
+                mg.push(g3.data(), i == 0 ? d3.data() : nullptr, i == 0 ? s3.data() : nullptr, T3.data());
+                put(T3.data(), 48);
+            }
+        }
     } catch (const std::exception& e) {
         fprintf(stderr, "dropin_main: %s\n", e.what());
         return 1;

@@ -24,7 +24,7 @@ def build_exe():
     newest = max(newest, os.path.getmtime(SRC))
     if not os.path.exists(EXE) or os.path.getmtime(EXE) < newest:
         subprocess.check_call(["g++", "-std=c++17", "-O1", "-Wall", "-Wextra", "-Werror", "-I" + os.path.join(ROOT, "include"), "-o", EXE, SRC,
-                               "-L" + PKG, "-ldvo_cuda", "-Wl,-rpath," + PKG])
+                               "-L" + PKG, "-ldvo_cuda", "-Wl,-rpath," + PKG, "-pthread"])
     return EXE
 
 
@@ -177,3 +177,93 @@ def test_dropin_matches_oracle(orc, seq160, tmp_path):
     raw = [next(rec) for _ in range(5)]
     assert raw[0].tobytes() == vis["gray"].tobytes() and raw[1].tobytes() == vis["depth_sigma"].tobytes()
     assert raw[2].tobytes() == vis["depth"].tobytes() and raw[3].tobytes() == vis["age"].tobytes() and raw[4].tobytes() == vis["gradx"].tobytes()
+    # 11. test/update.cpp:51-116: Convert::gradiate / cullImage / cullIntrinsic, Implement::update per pixel + math::Gaussian, regularize
+    rg = orc.cull_image(g[0], 3); og = orc.cull_image(g[2], 3); Kc = orc.cull_intrinsic(K, 3)
+    gx = orc.gradiate(rg, True); gy = orc.gradiate(rg, False)
+    assert next(rec).tobytes() == rg.tobytes() and next(rec).tobytes() == np.asarray(Kc, np.float32).tobytes()
+    assert next(rec).tobytes() == gx.tobytes() and next(rec).tobytes() == gy.tobytes()
+    rdm = orc.cull_image(pd, 1).copy(); rsm = np.full_like(rdm, 0.5)
+    uxi2 = np.array([-0.1, 0, 0, 0, 0, 0], np.float32)
+    n_fused = 0
+    for y in range(rdm.shape[0]):
+        for x in range(rdm.shape[1]):
+            rdm[y, x] = max(rdm[y, x], np.float32(0.1))
+            nd, ns = orc.map_update_pixel(og, rg, gx, gy, uxi2, Kc, x, y, float(rdm[y, x]), float(rsm[y, x]))
+            if nd > 0 and nd < 6.0:
+                a, b, ok = orc.gaussian_fuse(float(rdm[y, x]), float(rsm[y, x]), nd, ns)
+                rdm[y, x] = a; rsm[y, x] = b; n_fused += ok
+    assert n_fused > 20, n_fused
+    assert next(rec).tobytes() == rdm.tobytes() and next(rec).tobytes() == rsm.tobytes()
+    assert next(rec).tobytes() == orc.regularize(rdm, rsm).tobytes()
+    import json
+    mt = json.load(open(os.path.join(ROOT, "tests", "golden", "mt19937_libstdcxx.json")))
+    gu = [float(next(rec)[0]) for _ in range(6)]
+    assert gu[0] == 0.0 and gu[1] == np.float32(min(mt["dist"][0], 4.0)) and gu[2] == 0.5     # refused: reset from the engine's first draw
+    a, b, ok = orc.gaussian_fuse(1.0, 0.1, 1.05, 0.2)
+    assert gu[3] == 1.0 and ok and gu[4] == np.float32(a) and gu[5] == np.float32(b)
+    # 12. test/warp.cpp:27-42
+    wxi = np.array([0.02, -0.01, 0.03, 0.01, -0.02, 0.005], np.float32)
+    assert np.abs(next(rec).reshape(4, 4) - orc.se3_exp(wxi)).max() <= 1e-6
+    assert next(rec).tobytes() == orc.warp_image(wxi, orc.cull_image(g[0], 1), orc.cull_image(d[0], 1), orc.cull_intrinsic(K, 1)).tobytes()
+    # 13. scalar boundary
+    assert float(next(rec)[0]) == 1.0 and float(next(rec)[0]) == 0.0
+    v = next(rec)
+    Kf = np.asarray(K, np.float32)
+    Tm = orc.se3_exp(xi)
+    bp = np.array([np.float32(1.7) * (np.float32(123.25) - Kf[0, 2]) / Kf[0, 0], np.float32(1.7) * (np.float32(77.5) - Kf[1, 2]) / Kf[1, 1], 1.7], np.float32)
+    assert np.array_equal(v[:3], bp)
+    wpt = orc.warp_point(Tm, K, 123.25, 77.5, 1.7)
+    assert np.abs(v[9:11] - wpt).max() <= 1e-4 and np.abs(v[11:13] - wpt).max() <= 1e-4 and np.abs(v[3:6] - v[6:9]).max() <= 1e-6
+    invT = next(rec).reshape(4, 4)
+    mapped = next(rec).reshape(h // 2, w // 2); sg = next(rec).reshape(h // 2, w // 2)
+    dd = orc.cull_image(d[0], 1); Kd = np.asarray(orc.cull_intrinsic(K, 1), np.float32)
+    ys, xs = np.mgrid[0:h // 2, 0:w // 2]
+    xs = xs.astype(np.float32); ys = ys.astype(np.float32)
+    ok = ~(np.abs(dd) < np.float32(1e-6))
+    X = (dd * (xs - Kd[0, 2])) / Kd[0, 0]; Y = (dd * (ys - Kd[1, 2])) / Kd[1, 1]
+    R = invT[:3, :3]; t = invT[:3, 3]
+    tx = ((R[0, 0] * X + R[0, 1] * Y) + R[0, 2] * dd) + t[0]; ty = ((R[1, 0] * X + R[1, 1] * Y) + R[1, 2] * dd) + t[1]
+    tz = ((R[2, 0] * X + R[2, 1] * Y) + R[2, 2] * dd) + t[2]
+    with np.errstate(all="ignore"):
+        u = (tx * Kf[0, 0]) / tz + Kf[0, 2]; vv = (ty * Kf[1, 1]) / tz + Kf[1, 2]
+    exp_m = np.full((h // 2, w // 2), -2.0, np.float32)
+    exp_m[ok] = [orc.get_subpixel(g[1], float(a), float(b)) for a, b in zip(u[ok], vv[ok])]
+    assert np.array_equal(sg, np.where(ok, np.float32(0.1), np.float32(1.0)))
+    assert mapped.tobytes() == exp_m.tobytes()
+    # 14. dvo::MultiGpu with 3 copies of the sequence: every sequence == the single-context run of step 7
+    assert int(next(rec)[0]) >= 1
+    for i in range(n):
+        T3 = next(rec).reshape(3, 4, 4)
+        for q in range(3):
+            assert T3[q].tobytes() == T7[i].tobytes(), (i, q)
+
+
+def test_sharding_host_only(tmp_path):
+    """dvo::Sharding (include/dvo/multi_gpu.hpp): ids, owners and local indices of `id mod nGPU` - host arithmetic, no GPU."""
+    src = tmp_path / "shard.cpp"
+    src.write_text('''
+#include "dvo/multi_gpu.hpp"
+#include <cstdio>
+int main() {
+    for (int n : {1, 5, 256}) for (int w : {1, 2, 3, 8}) {
+        dvo::Sharding s(n, w);
+        int total = 0;
+        for (int r = 0; r < w; r++) {
+            auto ids = s.ids(r);
+            if ((int)ids.size() != s.local_count(r)) return 1;
+            for (size_t k = 0; k < ids.size(); k++) {
+                if (s.owner(ids[k]) != r || s.local_index(ids[k]) != (int)k || s.global_id(r, (int)k) != ids[k]) return 2;
+            }
+            total += (int)ids.size();
+        }
+        if (total != n) return 3;
+    }
+    std::puts("ok");
+    return 0;
+}
+''')
+    exe = tmp_path / "shard"
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-Wall", "-Wextra", "-Werror", "-I" + os.path.join(ROOT, "include"), "-o", str(exe), str(src),
+                           "-L" + PKG, "-ldvo_cuda", "-Wl,-rpath," + PKG, "-pthread"])
+    r = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert r.returncode == 0 and r.stdout.strip() == "ok", (r.returncode, r.stdout, r.stderr)

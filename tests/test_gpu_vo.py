@@ -22,7 +22,19 @@ UPD_TOL = 1e-5
 FORCED_TOL = 1e-6  # teacher-forced maps: bit-identical, or within 1e-6 relative (north_star allows 1e-4)
 
 
-def _run_pair(orc, g, K, d0, s0, levels=3, culls=2, n_streams=1, forced=True, upd_tol=None, **params):
+def exact_update(orc, snap, obj_frame, level, xi_before, P):
+    """The update of one Gauss-Newton iteration from the EXACT (fp64) least-squares solution of the reference's own stacked
+    system: A and b are what Track::optimize hands to cv::solve (orc.optimize_system), built from the keyframe images `snap` as
+    they were when the frame was tracked."""
+    im = snap[level]
+    warped = orc.warp_image(xi_before, im["gray"], im["depth"], im["K"])
+    _, _, _, A, b = orc.optimize_system(obj_frame.image(level, "gray"), warped, im["depth"], im["sigma"], im["gradx"], im["grady"], im["K"],
+                                        xi_before, level, params=P)
+    x = np.linalg.lstsq(A.astype(np.float64), b.astype(np.float64), rcond=None)[0]
+    return -x
+
+
+def _run_pair(orc, g, K, d0, s0, levels=3, culls=2, n_streams=1, forced=True, upd_tol=None, exact_solve=False, **params):
     """Runs oracle and GPU side by side.
 
     forced=True (teacher-forced): every frame the GPU tracker runs freely from the same keyframe
@@ -44,7 +56,13 @@ def _run_pair(orc, g, K, d0, s0, levels=3, culls=2, n_streams=1, forced=True, up
     n_kf = 0; n_upd = 0; agreed = 0; n_ulp = [0]
     matched = np.zeros(n_streams, np.uint64)  # running sum of Mapper::update's valid_update counts
     bc = lambda a: np.broadcast_to(a, (n_streams,) + a.shape)
+    P_orc = orc.params(**params)
+    n_exact = [0, 0.0, 0.0]   # iterations decided by the fp64 solve, worst |gpu - exact|, worst |reference - exact| among them
     for i in range(n):
+        snap = None
+        if exact_solve and i > 0:   # the keyframe as tracking of frame i will see it (mapping of frame i changes it afterwards)
+            kf0 = vo.ref_frame()
+            snap = [dict({k: kf0.image(l, k).copy() for k in ("gray", "depth", "sigma", "gradx", "grady")}, K=kf0.K(l)) for l in range(levels)]
         T_o = vo.odometrize(g[i], d0 if i == 0 else None, s0 if i == 0 else None)
         o_xi, o_rel = vo.last_frame().xi()
         if forced and i > 0:
@@ -62,7 +80,17 @@ def _run_pair(orc, g, K, d0, s0, levels=3, culls=2, n_streams=1, forced=True, up
             if forced:
                 assert sched_g == sched_o, "frame %d: GN schedule / valid counts differ" % i
                 for a, b in zip(logs[s], o_log):
-                    assert se3_norm(a["update"], b["update"]) <= upd_tol, (i, a, b)
+                    e = se3_norm(a["update"], b["update"])
+                    if e > upd_tol and snap is not None:
+                        # The reference solves the stacked N x 6 system with an fp32 SVD (cv::solve(DECOMP_SVD), optimize.cpp:97); at
+                        # 10^5 - 10^6 rows its own rounding noise exceeds 1e-5.  Decide against the exact solution of ITS system:
+                        # the GPU (fp64 normal equations) must be within tolerance of it, and closer to it than the reference is.
+                        x64 = exact_update(orc, snap, vo.last_frame(), b["level"], b["xi_before"], P_orc)
+                        eg, er = se3_norm(a["update"], x64), se3_norm(b["update"], x64)
+                        n_exact[0] += 1; n_exact[1] = max(n_exact[1], eg); n_exact[2] = max(n_exact[2], er)
+                        assert eg <= upd_tol and eg <= er, (i, b["level"], b["iteration"], eg, er)
+                    else:
+                        assert e <= upd_tol, (i, a, b)
                     assert se3_norm(a["xi_after"], b["xi_after"]) <= POSE_TOL
             ok &= sched_g == sched_o and se3_norm(st["rel_xi"][s], o_rel) <= POSE_TOL
             if not ok and not forced:
@@ -100,6 +128,9 @@ def _run_pair(orc, g, K, d0, s0, levels=3, culls=2, n_streams=1, forced=True, up
                     else:
                         assert _close(a, b), "frame %d level %d %s" % (i, l, kind)
             assert dv.frame_download(ks, top, "age")[s].tobytes() == kf.image(top, "age").tobytes(), "frame %d age" % i
+    if n_exact[0]:
+        print("%d iterations beyond %g of the reference's fp32 SVD result were decided against the fp64 solution of its system: "
+              "|gpu - exact| <= %.3g, |reference - exact| <= %.3g" % (n_exact[0], upd_tol, n_exact[1], n_exact[2]))
     if n_ulp[0]:
         print("maps not bit-identical (<= %g relative) in %d level-maps" % (FORCED_TOL, n_ulp[0]))
     dv.close()
