@@ -3,27 +3,31 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
 
-Workload (BASELINE.json: "VO frames/sec (track+map) at 640x480", config C5 "batched multi-stream"
-at main.cpp's geometry, configs[1]): every GPU runs `--streams` (256) independent synthetic 640x480
-sequences in lock-step through System::VisualOdometry::odometrize semantics — Frame(gray, K, 3, 2),
-Tracker::track, Mapper::estimate (needNewFrame -> propagate | update, regularize).  One STEP = one
-new frame of every stream (dvo_vo_push over the whole batch).  Sequences are independent, so N GPUs
-run N x 256 streams with no data-path collective ("scaling": "weak").
+Workload (BASELINE.json: "VO frames/sec (track+map) at 640x480", config C5 "batched multi-stream" at main.cpp's geometry,
+configs[1]): every GPU runs `--streams` (256) independent synthetic 640x480 sequences in lock-step through
+System::VisualOdometry::odometrize semantics — Frame(gray, K, 3, 2), Tracker::track, Mapper::estimate (needNewFrame ->
+propagate | update, regularize).  One STEP = `--frames-per-step` (32) consecutive frames of every stream, i.e. 8192 frames at
+256 streams; K = 20 steps are 640 frames per stream, long enough for the keyframe history (never pruned, frame.hpp:179-185) and
+the epipolar searches to reach their steady state.  Sequences are independent, so N GPUs run N x 256 streams with no data-path
+collective ("scaling": "weak"); `strong_256` is BASELINE configs[4] as written (256 sequences in total, sharded id mod N).
 
-  value      frames/s with the frames already resident in HBM (dvo_vo_push_dev), CUDA events
-  e2e        the same through dvo_vo_push with pinned HOST frames: the H2D copy of the step's input and
-             the D2H read of the step's poses are inside the timed region
-  roofline   the dominant kernel of the step (largest share of device time in a separate pass with CUDA
-             events around every launch): algorithmic bytes (SURVEY §8-d, DESIGN.md §4) / its device time;
-             `kernels` lists the same for every hot-path kernel
-  cpu_baseline  the reference's own sources (oracle/_ref) on the host cores, one sequence per core,
-             with the C restatement (oracle/dvo_oracle.c) beside it
-  cpu_baseline  the CPU oracle (oracle/, a C restatement of the reference; or oracle/_ref = the
-             reference's own sources when built) on the host cores, one sequence per core
+  value         frames/s over the K timed steps with the 8-bit frames already resident in HBM (dvo_vo_push_gray8_dev), CUDA events
+  value_steady  the same over the timed frames with index >= 250 only; value_early: frames 1 .. 100 (round 1's window)
+  e2e           THE SAME frames of THE SAME sequences (dvo_vo_reset, replay) through dvo_vo_push_gray8 / dvo_vo_submit_gray8 with
+                pinned HOST frames: the H2D copy of every frame and the D2H read of its poses are inside the timed region
+  roofline      the dominant kernel of the step (largest share of device time in a separate pass with CUDA events around every
+                launch, at the END of the sequences = steady state): algorithmic bytes / its device
+                time; roofline.issue = the instruction-issue figures of the same kernel from the committed ncu capture of THIS
+                source tree (profiles/traffic_<source hash>.json); `kernels` lists every hot-path kernel
+  cpu_baseline  the reference's own sources (oracle/_ref) on the host cores, one sequence per core, bounded sample; the C
+                restatement (oracle/dvo_oracle.c) and the single-thread figure beside it
 
-`--impl reference` times only the CPU arm (rank 0), same metric / config.
+`--impl reference` times only the CPU arm (rank 0), same metric / config; it never loads the CUDA library (inputs are rendered
+by a child process).
 """
 import argparse
+import ctypes as C
+import hashlib
 import json
 import multiprocessing as mp
 import os
@@ -31,7 +35,6 @@ import statistics
 import subprocess
 import sys
 import tempfile
-import threading
 import time
 
 import numpy as np
@@ -45,6 +48,8 @@ for p in (ROOT, PKG):
 W_IN, H_IN, LEVELS, CULLS = 640, 480, 3, 2      # main.cpp: Frame(gray, K, 3, 2) on 640x480 (system.hpp:47)
 TRANS_STEP, ROT_STEP_DEG = 0.004, 0.15          # per-frame motion of the synthetic trajectories
 GN_BYTES_PER_PX = 16                            # depth, sigma, obj gray, ref gray read once
+SEED_BASE = 1000
+STEADY_FROM = 250                               # frames from here on count as steady state
 
 
 def log(*a):
@@ -106,6 +111,82 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------
+# inputs
+# ------------------------------------------------------------------------------------------------
+def default_K():
+    return np.array([[0.82 * W_IN, 0, 0.5 * W_IN - 0.5], [0, 0.82 * W_IN, 0.5 * H_IN - 0.5], [0, 0, 1]], np.float32)
+
+
+def depth_prior(n_streams, seed):
+    """Scene's ctor prior (frame.hpp:18-21): max(randn(1.5, 0.5), 0.5), sigma 0.5 — supplied as an input to both arms
+    (SURVEY H6), one independent draw per stream."""
+    rng = np.random.default_rng(seed)
+    h, w = H_IN >> CULLS, W_IN >> CULLS
+    d = np.maximum(rng.normal(1.5, 0.5, size=(n_streams, h, w)), 0.5).astype(np.float32)
+    return d, np.full_like(d, 0.5)
+
+
+def ring_index(i, n_ring):
+    """Frame i of a sequence -> index into the ring of n_ring distinct rendered frames: the camera path is traversed forwards then
+    backwards (still one continuous motion), so a bounded set of frames serves any number of steps."""
+    period = 2 * (n_ring - 1)
+    j = i % period if period else 0
+    return j if j < n_ring else period - j
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def render_u8_main(path, n_streams, n_frames, seed0):
+    """Child-process entry (`bench.py --render-u8 ...`): [n_streams][n_frames][h][w] uint8 frames of sequences seed0 .. from the
+    device renderer when a GPU is present, else from the numpy renderer; written to `path` (.npy)."""
+    out = np.lib.format.open_memmap(path, mode="w+", dtype=np.uint8, shape=(n_streams, n_frames, H_IN, W_IN))
+    how = None
+    try:
+        import dvo_b200
+        lib = dvo_b200.load_library()
+        if lib.dvo_device_count() > 0:
+            dv = dvo_b200.Dvo(lib=lib, n_streams=n_streams, width=W_IN, height=H_IN, levels=LEVELS, culls=CULLS, K=default_K(),
+                              max_frames=2, max_keyframes=1)
+            buf = dv.dev_alloc(n_streams * H_IN * W_IN)
+            tmp = np.empty((n_streams, H_IN, W_IN), np.uint8)
+            for i in range(n_frames):
+                dv.synth_render_gray8_dev(buf, None, i, seed0, 1, TRANS_STEP, ROT_STEP_DEG)
+                dv.copy_to_host(tmp, buf)
+                out[:, i] = tmp
+            dv.dev_free(buf)
+            dv.close()
+            how = "device renderer"
+    except Exception as e:   # no library / no device: numpy
+        log("render: device renderer unavailable (%s), using numpy" % e)
+    if how is None:
+        from dvo_b200 import synth
+        for s in range(n_streams):
+            g, _, _, _ = synth.sequence(n_frames, W_IN, H_IN, K=default_K(), seed=seed0 + s, trans_step=TRANS_STEP, rot_step_deg=ROT_STEP_DEG)
+            out[s] = np.clip(np.rint(g * 255.0), 0, 255).astype(np.uint8)
+        how = "numpy renderer"
+    out.flush()
+    print(how)
+
+
+def render_host_frames_u8(n_streams, n_frames, seed0):
+    """8-bit frames for the CPU arm, rendered in a CHILD process so that the arm's own process never maps libdvo_cuda.so."""
+    d = tempfile.mkdtemp(prefix="dvo_in_")
+    path = os.path.join(d, "frames.npy")
+    r = subprocess.run([sys.executable, os.path.abspath(__file__), "--render-u8", path, str(n_streams), str(n_frames), str(seed0)],
+                       capture_output=True, text=True)
+    if r.returncode != 0:
+        raise SystemExit("bench.py: input rendering failed:\n" + r.stderr[-2000:])
+    how = r.stdout.strip().splitlines()[-1]
+    frames = np.load(path, mmap_mode="r")
+    return frames, how, path
+
+
+# ------------------------------------------------------------------------------------------------
 # CPU arm: the oracle (or oracle/_ref) on the host cores, one independent sequence per worker process
 # ------------------------------------------------------------------------------------------------
 def _build_cpu_lib():
@@ -116,10 +197,9 @@ def _build_cpu_lib():
 
 
 def _ref_lib():
-    """oracle/_ref/libdvo_ref_fast.so: the reference's OWN translation units (unmodified, compiled in
-    the build container from /root/reference over the OpenCV-API shim) with its release optimisation
-    level (-Ofast, CMakeLists.txt:43; -march=x86-64-v3 instead of native so the prebuilt file runs on
-    the GPU box's host).  None when it was never built."""
+    """oracle/_ref/libdvo_ref_fast.so: the reference's OWN translation units (unmodified, compiled in the build container from
+    /root/reference over the OpenCV-API shim) with its release optimisation level (-Ofast, CMakeLists.txt:43; -march=x86-64-v3
+    instead of native so the prebuilt file runs on the GPU box's host).  None when it was never built."""
     from oracle import ref as R
     try:
         return R.build(fast=True)
@@ -127,18 +207,22 @@ def _ref_lib():
         return None
 
 
+def _to_float(u8):
+    return (u8.astype(np.float32) * np.float32(1.0 / 255.0)).astype(np.float32)   # Loader's convertTo(CV_32FC1, 1.0/255.0), loader.cpp:61
+
+
 def _cpu_worker(conn, frames, K, d0, s0, kind, lib_path):
-    """frames: [n][h][w] float32 (shared, fork).  Protocol: ("run", first, count) -> seconds."""
+    """frames: [n][h][w] uint8 (shared, fork).  Protocol: ("run", first, count) -> seconds."""
     os.environ["OMP_NUM_THREADS"] = "1"   # one sequence per core; forEach stays serial inside a worker
     if kind == "reference":
         from oracle.ref import Ref
         vo = Ref(path=lib_path).vo_create(K)           # System::VisualOdometry(K), Frame(gray, K, 3, 2)
-        vo.odometrize(frames[0], d0)
+        vo.odometrize(_to_float(frames[0]), d0)
     else:
         from oracle.oracle import Oracle
         orc = Oracle(path=lib_path)   # reference release flags: -Ofast -march=native (CMakeLists.txt:43)
         vo = orc.vo_create(K, LEVELS, CULLS)
-        vo.odometrize(frames[0], d0, s0)
+        vo.odometrize(_to_float(frames[0]), d0, s0)
     conn.send("ready")
     while True:
         msg = conn.recv()
@@ -147,15 +231,16 @@ def _cpu_worker(conn, frames, K, d0, s0, kind, lib_path):
         _, first, count = msg
         t0 = time.perf_counter()
         for i in range(first, first + count):
-            vo.odometrize(frames[i])
+            vo.odometrize(_to_float(frames[i]))
         conn.send(time.perf_counter() - t0)
+    conn.close()   # and return: the worker exits through the interpreter's normal shutdown
 
 
 class CpuArm:
     """cores worker processes, each running the CPU VO on its own synthetic sequence."""
 
     def __init__(self, frames, K, d0, s0, kind="reference"):
-        # frames: [cores][n][h][w]
+        # frames: [cores][n][h][w] uint8
         self.cores = frames.shape[0]
         ctx = mp.get_context("fork")
         lib_path = _ref_lib() if kind == "reference" else None
@@ -165,7 +250,7 @@ class CpuArm:
         self.pipes = []; self.procs = []
         for c in range(self.cores):
             a, b = ctx.Pipe()
-            p = ctx.Process(target=_cpu_worker, args=(b, frames[c], K, d0[c], s0[c], kind, lib_path), daemon=True)
+            p = ctx.Process(target=_cpu_worker, args=(b, frames[c], K, d0[c], s0[c], kind, lib_path))
             p.start()
             self.pipes.append(a); self.procs.append(p)
         for a in self.pipes:
@@ -187,63 +272,17 @@ class CpuArm:
             except Exception:
                 pass
         for p in self.procs:
-            p.join(timeout=5)
-
-
-# ------------------------------------------------------------------------------------------------
-# inputs
-# ------------------------------------------------------------------------------------------------
-def default_K():
-    return np.array([[0.82 * W_IN, 0, 0.5 * W_IN - 0.5], [0, 0.82 * W_IN, 0.5 * H_IN - 0.5], [0, 0, 1]], np.float32)
-
-
-def depth_prior(n_streams, seed):
-    """Scene's ctor prior (frame.hpp:18-21): max(randn(1.5, 0.5), 0.5), sigma 0.5 — supplied as an
-    input to both arms, one independent draw per stream."""
-    rng = np.random.default_rng(seed)
-    h, w = H_IN >> CULLS, W_IN >> CULLS
-    d = np.maximum(rng.normal(1.5, 0.5, size=(n_streams, h, w)), 0.5).astype(np.float32)
-    return d, np.full_like(d, 0.5)
-
-
-def render_host_frames(n_streams, n_frames, seed0):
-    """[n_streams][n_frames][h][w] float32 frames for the CPU arm: rendered by the device renderer
-    when a GPU is present (input generation only), else by the numpy renderer."""
-    import dvo_b200
-    out = np.empty((n_streams, n_frames, H_IN, W_IN), np.float32)
-    lib = dvo_b200.load_library()
-    if lib.dvo_device_count() > 0:
-        dv = dvo_b200.Dvo(lib=lib, n_streams=n_streams, width=W_IN, height=H_IN, levels=LEVELS, culls=CULLS, K=default_K(),
-                          max_frames=2, max_keyframes=1)
-        buf = dv.dev_alloc(n_streams * H_IN * W_IN * 4)
-        tmp = np.empty((n_streams, H_IN, W_IN), np.float32)
-        for i in range(n_frames):
-            dv.synth_render_dev(buf, None, i, seed0, TRANS_STEP, ROT_STEP_DEG)
-            dv.copy_to_host(tmp, buf)
-            out[:, i] = tmp
-        dv.dev_free(buf)
-        dv.close()
-        return out, "device renderer"
-    from dvo_b200 import synth
-    for s in range(n_streams):
-        g, _, _, _ = synth.sequence(n_frames, W_IN, H_IN, K=default_K(), seed=seed0 + s, trans_step=TRANS_STEP, rot_step_deg=ROT_STEP_DEG)
-        out[s] = g
-    return out, "numpy renderer"
-
-
-def host_cores():
-    try:
-        return len(os.sched_getaffinity(0))
-    except Exception:
-        return os.cpu_count() or 1
+            p.join(timeout=30)
+            if p.is_alive():
+                p.terminate()
 
 
 def run_cpu_arm(steps, warmup, frames_per_step, cores=None, kind="reference"):
-    """Times the CPU VO: every step, each of `cores` workers pushes frames_per_step frames of its own
-    sequence.  Returns (frames_per_s, ms_per_step, info)."""
+    """Times the CPU VO: every step, each of `cores` workers pushes frames_per_step frames of its own sequence.  Returns
+    (frames_per_s, ms_per_step, info)."""
     cores = cores or host_cores()
     n_frames = 1 + (steps + warmup) * frames_per_step
-    frames, how = render_host_frames(cores, n_frames, seed0=900000)
+    frames, how, path = render_host_frames_u8(cores, n_frames, seed0=900000)
     d0, s0 = depth_prior(cores, seed=4321)
     arm = CpuArm(frames, default_K(), d0, s0, kind)
     pos = 1
@@ -253,12 +292,18 @@ def run_cpu_arm(steps, warmup, frames_per_step, cores=None, kind="reference"):
     for _ in range(steps):
         t += arm.step(pos, frames_per_step); pos += frames_per_step
     arm.close()
+    try:
+        del frames
+        os.unlink(path); os.rmdir(os.path.dirname(path))
+    except Exception:
+        pass
     total = cores * frames_per_step * steps
-    what = ("the reference's own sources (oracle/_ref, -Ofast)" if arm.kind == "reference" else
+    what = ("the reference's own sources (oracle/_ref, -Ofast) over oracle/shim's OpenCV stand-in" if arm.kind == "reference" else
             "C restatement of the reference (oracle/dvo_oracle.c, -Ofast -march=native)")
     info = dict(kind=arm.kind, cores=cores,
-                sample="%d sequences x %d frames of the 640x480 workload (one single-threaded process per core, %s; input: %s), "
-                       "%d frames per step" % (cores, steps * frames_per_step, what, how, cores * frames_per_step))
+                sample="%d sequences x %d frames (frames %d..%d) of the 640x480 workload, one single-threaded process per core, %s; "
+                       "input: 8-bit frames from the %s; %d frames per step" % (cores, steps * frames_per_step, 1 + warmup * frames_per_step,
+                                                                                n_frames - 1, what, how, cores * frames_per_step))
     return total / t, 1e3 * t / steps, info
 
 
@@ -272,24 +317,84 @@ def peak_hbm():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def ncu_traffic(kernel):
-    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of `kernel` from the newest committed `ncu --set full` capture
-    (profiles/*_traffic.json, written by scripts/ncu_summary.py traffic).  A captured launch is ONE frame of the same workload."""
-    import glob
-    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "*_traffic.json")), reverse=True):
-        try:
-            k = json.load(open(path))["kernels"].get(kernel)
-            if k:
-                return k["dram_bytes"], os.path.basename(path), k
-        except Exception:
-            continue
-    return None, None, None
+def source_hash():
+    """Identifies the CUDA source tree a profile belongs to (the .git directory does not travel to the GPU box)."""
+    h = hashlib.sha256()
+    for name in ("csrc/dvo_cuda.cu", "csrc/dvo_kernels.cuh", "csrc/dvo_device.cuh", "csrc/dvo_internal.cuh", "csrc/dvo_synth.cuh", "Makefile"):
+        h.update(open(os.path.join(PKG, name), "rb").read())
+    return h.hexdigest()[:12]
+
+
+def ncu_capture(kernel):
+    """One launch of `kernel` from the committed `ncu --set full` capture OF THIS SOURCE TREE: profiles/traffic_<source hash>.json,
+    written by scripts/ncu_summary.py traffic.  (None, None, why) when there is none - said loudly, never replaced by an older build's."""
+    name = "traffic_%s.json" % source_hash()
+    path = os.path.join(ROOT, "profiles", name)
+    if not os.path.exists(path):
+        log("bench.py: NO ncu capture for this source tree (%s): roofline.traffic / roofline.issue are null. "
+            "Capture one: see profiles/README.md" % name)
+        return None, name, "no ncu capture of source tree %s is committed" % source_hash()
+    k = json.load(open(path))["kernels"].get(kernel)
+    return k, name, None if k else "kernel not in the capture"
+
+
+def make_ring(dv, lib, S, n_ring, seed0, seed_stride):
+    """n_ring distinct 8-bit frames of every stream: in pinned host memory (what the end-to-end pass feeds) and copied to HBM
+    (what the device-resident pass feeds) - the SAME pixels for both."""
+    fb = S * H_IN * W_IN
+    dev = dv.dev_alloc(fb * n_ring)
+    host = []
+    for i in range(n_ring):
+        dv.synth_render_gray8_dev(dev + i * fb, None, i, seed0, seed_stride, TRANS_STEP, ROT_STEP_DEG)
+        hp = lib.dvo_host_alloc(fb)
+        if not hp:
+            raise SystemExit("bench.py: pinned host allocation failed")
+        arr = np.ctypeslib.as_array(C.cast(hp, C.POINTER(C.c_uint8)), shape=(S, H_IN, W_IN))
+        dv.copy_to_host(arr, dev + i * fb)
+        host.append(hp)
+    return dev, host, fb
+
+
+class Passes:
+    """The two timed passes over one set of sequences: device-resident and end to end."""
+
+    def __init__(self, lib, S, n_frames, n_ring, seed0, seed_stride, prior_seed, extra_frames=0):
+        import dvo_b200
+        self.lib, self.S, self.n_frames = lib, S, n_frames
+        self.n_ring = min(n_ring, n_frames + extra_frames)
+        self.dv = dvo_b200.Dvo(lib=lib, n_streams=S, width=W_IN, height=H_IN, levels=LEVELS, culls=CULLS, K=default_K(), max_frames=2,
+                               max_keyframes=n_frames + extra_frames + 4, rng_table=1 << 24)   # (the table would grow on demand: not inside a timed region)
+        # keyframe pool (FrameHistory is never pruned, frame.hpp:179-185): entry k is needed once some stream owns k keyframes - about
+        # 0.36 per frame on these trajectories; reserved up front so that no allocation falls into a timed region (what is missing
+        # would be allocated on first need)
+        self.dv.vo_reserve(int(0.5 * (n_frames + extra_frames)) + 16)
+        self.dev, self.host, self.fb = make_ring(self.dv, lib, S, self.n_ring, seed0, seed_stride)
+        self.d0, self.s0 = depth_prior(S, prior_seed)
+        self.dv.sync()
+
+    def dev_frame(self, i):
+        return self.dev + ring_index(i, self.n_ring) * self.fb
+
+    def host_frame(self, i):
+        return self.host[ring_index(i, self.n_ring)]
+
+    def close(self):
+        for hp in self.host:
+            self.lib.dvo_host_free(hp)
+        self.dv.dev_free(self.dev)
+        self.dv.close()
 
 
 def run_other_configs(lib):
-    """The single-stream configurations of BASELINE.json (the metric also names 1080p): device-resident, CUDA events on the
-    library's stream.  Reported beside the headline line, never instead of it.
-      C3  synthetic 1920x1080 sequence, full VO loop: Frame(gray, K, 3, 2) with the reference's ROIs scaled x3, and culls = 0;
+    """The single-stream configurations of BASELINE.json (the metric also names 1080p; north_star's ">= 1000 frames/s" is a
+    single-stream statement): device-resident, CUDA events on the library's stream.  Reported beside the headline line, never
+    instead of it.
+      S1  ONE 640x480 stream, full VO loop: the latency-bound configuration (frames/s = 1 / frame latency)
+      C1  test/track.cpp on the bundled KINECT_50MM pair (tests/golden/bundled_golden.npz): Gauss-Newton iterations/s, us per
+          iteration per level
+      C2  main.cpp on the bundled data/logicool0 frames (tests/golden/bundled_long.npz, 150 frames), free-running, one stream
+      C3  synthetic 1920x1080 sequence, full VO loop: Frame(gray, K, 3, 2) with the reference's ROIs scaled x3, and culls = 0,
+          with the trajectory error against the renderer's ground truth
       C4  3840x2160 mapping-only: Mapper::update on dense hypotheses (rel_xi = (-0.1, 0, 0, 0, 0, 0)) + regularize."""
     import dvo_b200
     out = []
@@ -298,13 +403,101 @@ def run_other_configs(lib):
     def Kf(w, h):
         return np.array([[0.82 * w, 0, 0.5 * w - 0.5], [0, 0.82 * w, 0.5 * h - 0.5], [0, 0, 1]], np.float32)
 
+    # ---- S1: single stream 640x480
+    n_frames, n_ring = 600, 48
+    P = Passes(lib, 1, n_frames + 1, n_ring, 1234, 1, 4321)
+    dv = P.dv
+    dv.vo_push_gray8_dev(P.dev_frame(0), -1, P.d0, P.s0)
+    for f in range(1, 9):
+        dv.vo_push_gray8_dev(P.dev_frame(f), -1)
+    c0 = dv.vo_counters()
+    dv.timer_start()
+    for f in range(9, 9 + n_frames - 8):
+        dv.vo_push_gray8_dev(P.dev_frame(f), -1)
+    ms = dv.timer_stop()
+    c1 = dv.vo_counters()
+    nf = n_frames - 8
+    it = int((c1["gn_iters"] - c0["gn_iters"]).sum())
+    out.append(dict(workload="S1: ONE synthetic 640x480 stream, %d frames, Frame(gray,K,3,2), full VO loop, device-resident 8-bit frames" % nf,
+                    value=nf / (ms * 1e-3), unit="frames/s", ms_per_frame=ms / nf, gn_iters_per_s=it / (ms * 1e-3), gn_iters_per_frame=it / float(nf),
+                    device_error=int(dv.vo_error())))
+    P.close()
+    # ---- C1 / C2: the bundled fixtures
+    try:
+        B = dict(np.load(os.path.join(ROOT, "tests", "golden", "bundled_golden.npz")))
+        up = lambda a, k: np.ascontiguousarray(np.repeat(np.repeat(a, k, axis=0), k, axis=1))
+        sg = np.where(B["c1_sigma10"] == 1, np.float32(0.1), np.float32(1.0)).astype(np.float32)
+        dv = dvo_b200.Dvo(lib=lib, width=512, height=424, levels=4, culls=1, K=B["c1_K"])
+        pre = dv.frame_create(up(B["c1_gray"][0], 2)); dv.frame_set_depth(pre, up(B["c1_depth"][0], 2), up(sg[0], 2), None, full_res=True)
+        cur = dv.frame_create(up(B["c1_gray"][1], 2)); dv.frame_set_depth(cur, up(B["c1_depth"][1], 2), up(sg[1], 2), None, full_res=True)
+        per_level = []
+        for lv in range(4):   # one Track::optimize per launch (dvo_gn_step), event-timed over repetitions
+            reps = 50
+            x = np.zeros(6, np.float32)
+            dv.gn_step(cur, pre, lv, x, want_mask=False)
+            t0 = time.perf_counter()
+            dv.kernel_timing(True)
+            for _ in range(reps):
+                dv.gn_step(cur, pre, lv, x, want_mask=False)
+            kt = dv.kernel_timing(False)
+            wall = (time.perf_counter() - t0) / reps
+            w_, h_ = dv.level_size(lv)
+            per_level.append(dict(level=lv, size="%dx%d" % (w_, h_), kernel_us_per_iteration=1e3 * kt["k_track"][0] / kt["k_track"][1],
+                                  call_us_per_iteration=1e6 * wall))
+        reps = 20
+        dv.track(cur, pre)
+        dv.kernel_timing(True)
+        n_it = 0
+        for _ in range(reps):
+            _, logs = dv.track(cur, pre)
+            n_it += len(logs[0])
+        kt = dv.kernel_timing(False)
+        out.append(dict(workload="C1: test/track.cpp on the bundled KINECT_50MM pair (entries 9 -> 10, 512x424, Frame(.,4,1): 32x26 .. 256x212), "
+                                 "Tracker::track as one persistent launch; per level: one Track::optimize per launch",
+                        value=n_it / (kt["k_track"][0] * 1e-3), unit="GN iterations/s", iterations_per_track=n_it / reps,
+                        track_us=1e3 * kt["k_track"][0] / reps, per_level=per_level))
+        dv.close()
+        BL = dict(np.load(os.path.join(ROOT, "tests", "golden", "bundled_long.npz")))
+        c = BL["l0_codes"]
+        inv = np.broadcast_to(BL["l0_invalid"][None], c.shape)
+        free = np.flatnonzero(np.bincount(c[~inv].ravel(), minlength=256) == 0)   # a code no valid pixel uses marks the undistortion border
+        if len(free) == 0:
+            raise FileNotFoundError("no free 8-bit code for the INVALID border")
+        icode = int(free[-1])
+        g8 = np.where(inv, icode, c).astype(np.uint8)
+        n = len(g8)
+        dv = dvo_b200.Dvo(lib=lib, width=640, height=480, levels=3, culls=2, K=BL["l0_K"], max_frames=2, max_keyframes=n + 2)
+        dv.vo_reserve(n)
+        full = np.ascontiguousarray(np.repeat(np.repeat(g8, 4, axis=1), 4, axis=2))   # the pixels Frame(., 3, 2) samples, at their input positions
+        fb = 640 * 480
+        dev = dv.dev_alloc(fb * n)
+        dv.copy_to_dev(dev, full)
+        d0 = BL["l0_init_depth"]
+        dv.vo_push_gray8_dev(dev, icode, d0, np.full_like(d0, 0.5))
+        c0 = dv.vo_counters()
+        dv.timer_start()
+        for i in range(1, n):
+            dv.vo_push_gray8_dev(dev + i * fb, icode)
+        ms = dv.timer_stop()
+        c1 = dv.vo_counters()
+        it = int((c1["gn_iters"] - c0["gn_iters"]).sum())
+        st = dv.vo_state()
+        out.append(dict(workload="C2: main.cpp's loop on the bundled data/logicool0 frames 0..%d (640x480 -> 160x120), one stream, free-running, "
+                                 "device-resident 8-bit frames" % (n - 1),
+                        value=(n - 1) / (ms * 1e-3), unit="frames/s", ms_per_frame=ms / (n - 1), gn_iters_per_s=it / (ms * 1e-3),
+                        gn_iters_per_frame=it / float(n - 1), keyframes=int(st["n_keyframes"][0]), reference_keyframes=int(BL["l0_n_keyframes"][-1]),
+                        device_error=int(dv.vo_error())))
+        dv.dev_free(dev)
+        dv.close()
+    except FileNotFoundError as e:
+        out.append(dict(workload="C1/C2: bundled fixtures", error=str(e)))
     # ---- C3
     W, H, n_res, n_frames = 1920, 1080, 40, 500
     for culls, sc in ((2, 3), (0, 12)):
         roi = dict(roi_x0=20 * sc, roi_x1=140 * sc, roi_y0=20 * sc, roi_y1=100 * sc,
                    map_roi_x0=16 * sc, map_roi_x1=144 * sc, map_roi_y0=12 * sc, map_roi_y1=108 * sc)
         dv = dvo_b200.Dvo(lib=lib, n_streams=1, width=W, height=H, levels=3, culls=culls, K=Kf(W, H), max_frames=2,
-                          max_keyframes=n_frames + 8, rng_table=1 << 24, **roi)
+                          max_keyframes=n_frames + 8, **roi)
         dv.vo_reserve(n_frames + 4)
         fb = W * H * 4
         dev = dv.dev_alloc(fb * n_res); dd = dv.dev_alloc(fb)
@@ -314,33 +507,42 @@ def run_other_configs(lib):
         dv.copy_to_host(d0, dd)
         d0 = np.ascontiguousarray(d0[0, ::1 << culls, ::1 << culls])
 
-        def fptr(i):
-            per = 2 * (n_res - 1)
-            j = i % per
-            return dev + (j if j < n_res else per - j) * fb
+        def fidx(i):
+            return ring_index(i, n_res)
 
         dv.vo_push_dev(dev, d0, np.full_like(d0, 0.1))
         for f in range(1, 4):
-            dv.vo_push_dev(fptr(f))
+            dv.vo_push_dev(dev + fidx(f) * fb)
         c0 = dv.vo_counters()
         dv.timer_start()
         for f in range(4, 4 + n_frames):
-            dv.vo_push_dev(fptr(f))
+            dv.vo_push_dev(dev + fidx(f) * fb)
         ms = dv.timer_stop()
         c1 = dv.vo_counters()
         err = dv.vo_error()
         it = int((c1["gn_iters"] - c0["gn_iters"]).sum())
+        # trajectory error against the renderer's ground truth: the first n_res frames are one forward pass of the camera path
+        dv.vo_reset()
+        errs = []; path = 0.0; prev = np.zeros(3)
+        for f in range(n_res):
+            T = dv.vo_push_dev(dev + f * fb, d0 if f == 0 else None, np.full_like(d0, 0.1) if f == 0 else None, want_pose=True)[0]
+            gt = dv.synth_pose(f, 1234, 0.002, 0.07)
+            path += float(np.linalg.norm(gt[:3, 3] - prev)); prev = gt[:3, 3].copy()
+            errs.append(float(np.linalg.norm(T[:3, 3].astype(np.float64) - np.linalg.inv(gt.astype(np.float64))[:3, 3])))
         out.append(dict(workload="C3: synthetic 1920x1080, %d frames, 1 stream, Frame(gray,K,3,%d) -> %dx%d finest level, full VO loop"
                                  % (n_frames, culls, W >> culls, H >> culls),
                         value=n_frames / (ms * 1e-3), unit="frames/s", ms_per_frame=ms / n_frames, gn_iters_per_s=it / (ms * 1e-3),
                         gn_iters_per_frame=it / float(n_frames), frames_update=int((c1["n_update"] - c0["n_update"]).sum()),
-                        frames_propagate=int((c1["n_propagate"] - c0["n_propagate"]).sum()), device_error=int(err)))
+                        frames_propagate=int((c1["n_propagate"] - c0["n_propagate"]).sum()), device_error=int(err),
+                        vs_ground_truth=dict(frames=n_res, path_length_m=path, max_translation_error_m=max(errs), final_translation_error_m=errs[-1],
+                                             note="ground-truth depth prior (sigma 0.1) on frame 0; se3::exp(frame->m_xi) is the world-to-camera "
+                                                  "pose (main.cpp:50 inverts it): compared with T_wc(i)^-1 T_wc(0) of the renderer (dvo_synth_pose)")))
         dv.dev_free(dev); dv.dev_free(dd)
         dv.close()
     # ---- C4
     W, H = 3840, 2160
     roi = dict(map_roi_x0=0, map_roi_x1=W - 1, map_roi_y0=0, map_roi_y1=H - 1)
-    dv = dvo_b200.Dvo(lib=lib, n_streams=1, width=W, height=H, levels=1, culls=0, K=Kf(W, H), max_frames=3, rng_table=1 << 24, **roi)
+    dv = dvo_b200.Dvo(lib=lib, n_streams=1, width=W, height=H, levels=1, culls=0, K=Kf(W, H), max_frames=3, **roi)
     fb = W * H * 4
     gd = dv.dev_alloc(fb)
     g = np.empty((2, 1, H, W), np.float32)
@@ -382,175 +584,184 @@ def run_other_configs(lib):
     return out
 
 
-def run_gpu_arm(args, rank, world, local_rank, dist):
-    import dvo_b200
-    lib = dvo_b200.load_library()
-    if lib.dvo_device_count() <= 0:
-        raise SystemExit("bench.py: no CUDA device — libdvo_cuda has no CPU fallback")
-    lib.dvo_set_device(local_rank)
-    S, K_, W_ = args.streams, args.steps, args.warmup
-    E = min(args.e2e_steps, K_)           # end-to-end steps (host frames)
-    R = args.roofline_steps               # extra pass with events around every GN launch
-    n_total = 1 + W_ + K_ + R             # frames pushed from HBM; frame 0 = first keyframe
-    # Resident frames: the camera path is traversed forwards then backwards (still one continuous
-    # motion), so a bounded set of distinct frames serves any number of steps.
-    n_dev_frames = min(n_total, args.resident_frames)
-    dv = dvo_b200.Dvo(lib=lib, n_streams=S, width=W_IN, height=H_IN, levels=LEVELS, culls=CULLS, K=default_K(), max_frames=2,
-                      max_keyframes=n_total + W_ + E + 4)
-    dv.vo_reserve(n_total + W_ + E + 2)
-    frame_bytes = S * H_IN * W_IN * 4
-    e2e_bgr = (args.e2e_input == "bgr8")
-    e2e_u8 = (args.e2e_input == "gray8") or e2e_bgr
-    esz = 3 if e2e_bgr else 1 if e2e_u8 else 4   # bytes per pixel of the end-to-end pass's host frames
-    host_frame_bytes = S * H_IN * W_IN * esz
-    h2d_bytes = S * (H_IN >> CULLS) * W_IN * esz if (CULLS > 0 and H_IN % (1 << CULLS) == 0) else host_frame_bytes  # stage_gray_to()
-    if e2e_bgr:
-        h2d_bytes = host_frame_bytes   # the undistortion gather can touch any source pixel: whole BGR frames cross PCIe
-    # global sequence ids are sharded id mod world (dvo_b200/shard.py); a rank's S local streams are ids
-    # rank, rank + world, ... and the renderer seeds stream k of this context with seed0 + k: the bench uses the
-    # contiguous relabelling 1000 + rank * S + k (any bijection of independent sequences gives the same workload)
-    seed0 = 1000 + rank * S
-    # --- inputs: rendered on device, resident in HBM before the timed region starts
-    dev = dv.dev_alloc(frame_bytes * n_dev_frames)
-    for i in range(n_dev_frames):
-        dv.synth_render_dev(dev + i * frame_bytes, None, i, seed0, TRANS_STEP, ROT_STEP_DEG)
-    # host frames for the end-to-end pass: the frames that follow, in pinned memory
-    import ctypes as C
-    host = []
-    # the e2e pass continues the motion from wherever the ping-pong traversal stops
-    period = 2 * (n_dev_frames - 1)
-    jl = (n_total - 1) % period if period else 0
-    last = jl if jl < n_dev_frames else period - jl
-    e2e_first = last + 1
-    tmpd = dv.dev_alloc(frame_bytes)
-    ftmp = np.empty((S, H_IN, W_IN), np.float32) if e2e_u8 else None
-    for i in range(W_ + E):
-        hp = lib.dvo_host_alloc(host_frame_bytes)
-        if not hp:
-            raise SystemExit("bench.py: pinned host allocation failed")
-        dv.synth_render_dev(tmpd, None, e2e_first + i, seed0, TRANS_STEP, ROT_STEP_DEG)
-        if e2e_u8:   # 8-bit camera frames: the rendered intensity quantised to 0..255 (what cv::imread + cvtColor deliver)
-            arr = np.ctypeslib.as_array(C.cast(hp, C.POINTER(C.c_uint8)), shape=(S, H_IN, W_IN, 3) if e2e_bgr else (S, H_IN, W_IN))
-            dv.copy_to_host(ftmp, tmpd)
-            np.multiply(ftmp, 255.0, out=ftmp); np.rint(ftmp, out=ftmp); np.clip(ftmp, 0, 255, out=ftmp)
-            arr[...] = ftmp[..., None] if e2e_bgr else ftmp   # B = G = R: cvtColor returns the same code
-        else:
-            arr = np.ctypeslib.as_array(C.cast(hp, C.POINTER(C.c_float)), shape=(S, H_IN, W_IN))
-            dv.copy_to_host(arr, tmpd)
-        host.append((hp, arr))
-    del ftmp
-    dv.dev_free(tmpd)
-    d0, s0 = depth_prior(S, seed=4321 + rank)
-    dv.sync()
+def bind_to_gpu_cpus(local_rank):
+    """Pin this rank's host threads (and therefore its pinned allocations, first-touch) to the CPUs NVML reports as local to its
+    GPU.  Returns a short description for the JSON line."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
+        n_words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, n_words)
+        cpus = [64 * w + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1]
+        allowed = sorted(set(cpus) & set(os.sched_getaffinity(0)))
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+            return "cpus %d-%d (%d, NVML affinity of GPU %d)" % (allowed[0], allowed[-1], len(allowed), local_rank)
+    except Exception as e:
+        return "unbound (%s)" % type(e).__name__
+    return "unbound"
 
-    def barrier():
-        dv.sync()
-        if dist is not None:
-            dist.barrier()
 
-    from dvo_b200 import shard
-
-    def maxrank(x):  # slowest rank's time (device-timed), dvo_b200/shard.py
-        return shard.max_over_ranks(x, dist, device="cuda")
-
-    # --- first keyframe + warm-up
-    def fptr(i):  # ping-pong over the resident frames
-        period = 2 * (n_dev_frames - 1)
-        j = i % period if period else 0
-        return dev + (j if j < n_dev_frames else period - j) * frame_bytes
-
+def timed_passes(P, W_, K_, F, barrier, maxrank, rank, local_rank, world, roofline_frames, do_roofline=True, do_e2e=True):
+    """Device-resident pass + (optionally) per-kernel pass + end-to-end replay over Passes P.  Returns a dict of raw figures."""
+    dv, lib, S = P.dv, P.lib, P.S
+    n_warm, n_timed = W_ * F, K_ * F
+    last = n_warm + n_timed                      # frames 1 .. last are pushed after the first keyframe (frame 0)
+    r = {}
+    # ---- device-resident: frame 0 (first keyframe, with the prior), W warm-up steps, K timed steps, an event per step boundary
+    dv.vo_push_gray8_dev(P.dev_frame(0), -1, P.d0, P.s0)
+    dv.event_record(0)
+    f = 1
+    for k in range(W_):
+        for _ in range(F):
+            dv.vo_push_gray8_dev(P.dev_frame(f), -1); f += 1
+        dv.event_record(1 + k)
+    c0 = dv.vo_counters(); m0 = dv.vo_matched()
+    barrier()
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
         time.sleep(0.3)
-    dv.vo_push_dev(dev, d0, s0)
-    f = 1
-    for _ in range(W_):
-        dv.vo_push_dev(fptr(f)); f += 1
-    c0 = dv.vo_counters()
-    m0 = dv.vo_matched()
-    # --- timed: K steps, inputs resident in HBM, CUDA events on the library's stream
-    barrier()
     l0 = dv.launch_count()
-    dv.timer_start()
-    for _ in range(K_):
-        dv.vo_push_dev(fptr(f)); f += 1
-    ms = dv.timer_stop()
+    dv.event_record(100)
+    for k in range(K_):
+        for _ in range(F):
+            dv.vo_push_gray8_dev(P.dev_frame(f), -1); f += 1
+        dv.event_record(101 + k)
     l1 = dv.launch_count()
+    step_ms = [dv.event_elapsed(100 + k, 101 + k) for k in range(K_)]
+    warm_ms = [dv.event_elapsed(k, k + 1) for k in range(W_)]
     barrier()
-    clocks = sampler.stop() if rank == 0 else None
-    ms = maxrank(ms)
+    r["clocks"] = sampler.stop() if rank == 0 else None
+    ms = maxrank(sum(step_ms))
     c1 = dv.vo_counters()
-    matched = int((dv.vo_matched() - m0).sum())
+    r["matched"] = int((dv.vo_matched() - m0).sum())
     if dv.vo_error() != 0:
         raise SystemExit("bench.py: device-side VO error")
-    gn_iters = int((c1["gn_iters"] - c0["gn_iters"]).sum())
-    n_prop = int((c1["n_propagate"] - c0["n_propagate"]).sum()); n_upd = int((c1["n_update"] - c0["n_update"]).sum())
-    # --- roofline pass: CUDA events around every hot-path launch (adds event records to the stream, so it
-    # is a separate pass); the dominant kernel = the largest share of the step's device time
-    dv.kernel_timing(True)
-    for _ in range(R):
-        dv.vo_push_dev(fptr(f)); f += 1
-    ktimes = dv.kernel_timing(False)
-    c2 = dv.vo_counters()
-    gn_px = int((c2["gn_pixels"] - c1["gn_pixels"]).sum())
-    rp = int((c2["n_propagate"] - c1["n_propagate"]).sum()); ru = int((c2["n_update"] - c1["n_update"]).sum())
+    r.update(ms=ms, step_ms=step_ms, warm_ms=warm_ms, launches=int(l1 - l0),
+             gn_iters=int((c1["gn_iters"] - c0["gn_iters"]).sum()), n_prop=int((c1["n_propagate"] - c0["n_propagate"]).sum()),
+             n_upd=int((c1["n_update"] - c0["n_update"]).sum()))
+    # frames >= STEADY_FROM of the timed window, and frames 1..100 (the early part of the sequences) from the warm-up events
+    steady = [(k, t) for k, t in enumerate(step_ms) if 1 + n_warm + k * F >= STEADY_FROM]
+    r["steady_ms"] = maxrank(sum(t for _, t in steady)) if steady else None
+    r["steady_frames"] = len(steady) * F
+    early_steps = [k for k in range(W_) if 1 + (k + 1) * F - 1 <= 100]
+    r["early_ms"] = maxrank(sum(warm_ms[k] for k in early_steps)) if early_steps else None
+    r["early_frames"] = len(early_steps) * F
+    # ---- per-kernel pass: CUDA events around every hot-path launch (adds event records to the stream and keeps the launches apart,
+    # so Mapper::update is NOT overlapped with tracking here); the dominant kernel = the largest share of the step's device time
+    if do_roofline:
+        dv.kernel_timing(True)
+        for _ in range(roofline_frames):
+            dv.vo_push_gray8_dev(P.dev_frame(f), -1); f += 1
+        r["ktimes"] = dv.kernel_timing(False)
+        c2 = dv.vo_counters()
+        r["roof_gn_px"] = int((c2["gn_pixels"] - c1["gn_pixels"]).sum())
+        r["roof_prop"] = int((c2["n_propagate"] - c1["n_propagate"]).sum()); r["roof_upd"] = int((c2["n_update"] - c1["n_update"]).sum())
+        r["roof_first_frame"] = f - roofline_frames
+    # ---- end to end: dvo_vo_reset, then the SAME frames of the SAME sequences from pinned host memory.  Frame 0 goes through
+    # dvo_vo_push_gray8 (it carries the prior), every later frame through dvo_vo_submit_gray8 / dvo_vo_collect: frame n+1's H2D copy
+    # overlaps frame n's kernels; every frame's poses are read back into pinned host memory and consumed before it counts.
+    if do_e2e:
+        dv.vo_reset()
+        tps = [lib.dvo_host_alloc(S * 64) for _ in range(2)]
+        Ts = [np.ctypeslib.as_array(C.cast(tp, C.POINTER(C.c_float)), shape=(S, 4, 4)) for tp in tps]
+        w, h = dv.level_size(LEVELS - 1)
+        T0 = np.empty((S, 4, 4), np.float32)
+        dv._ck(lib.dvo_vo_push_gray8(dv.ctx, P.host_frame(0), -1, P.d0.ctypes.data_as(C.POINTER(C.c_float)),
+                                     P.s0.ctypes.data_as(C.POINTER(C.c_float)), T0.ctypes.data_as(C.POINTER(C.c_float))))
+        pose_sum = 0.0
+
+        def run(first, count):
+            nonlocal pose_sum
+            pending = []
+            for i in range(first, first + count):
+                dv._ck(lib.dvo_vo_submit_gray8(dv.ctx, P.host_frame(i), -1, tps[i & 1]))
+                pending.append(i & 1)
+                if len(pending) == 2:
+                    dv._ck(lib.dvo_vo_collect(dv.ctx))
+                    pose_sum += float(Ts[pending.pop(0)][:, :3, 3].sum())
+            while pending:
+                dv._ck(lib.dvo_vo_collect(dv.ctx))
+                pose_sum += float(Ts[pending.pop(0)][:, :3, 3].sum())
+
+        run(1, n_warm)
+        dv.sync()
+        barrier()
+        t0 = time.perf_counter()
+        run(1 + n_warm, n_timed)
+        dv.sync()
+        e2e_local = time.perf_counter() - t0
+        r["e2e_s"] = maxrank(e2e_local)
+        r["e2e_local_s"] = e2e_local
+        barrier()
+        if not np.isfinite(pose_sum):
+            raise SystemExit("bench.py: non-finite pose in the end-to-end pass")
+        if dv.vo_error() != 0:
+            raise SystemExit("bench.py: device-side VO error in the end-to-end pass")
+        for tp in tps:
+            lib.dvo_host_free(tp)
+    return r
+
+
+def run_gpu_arm(args, rank, world, local_rank, dist):
+    import dvo_b200
+    from dvo_b200 import shard
+    lib = dvo_b200.load_library()
+    if lib.dvo_device_count() <= 0:
+        raise SystemExit("bench.py: no CUDA device — libdvo_cuda has no CPU fallback")
+    binding = bind_to_gpu_cpus(local_rank) if not args.no_bind else "unbound (--no-bind)"
+    lib.dvo_set_device(local_rank)
+    S, K_, W_, F = args.streams, args.steps, args.warmup, args.frames_per_step
+    R = args.roofline_frames
+    n_frames = 1 + (W_ + K_) * F
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+
+    def maxrank(x):  # slowest rank's time, dvo_b200/shard.py
+        return shard.max_over_ranks(x, dist, device="cuda")
+
+    # global sequence ids are sharded id mod world (dvo_b200/shard.py, SURVEY §8-e).  The weak-scaling workload gives every rank S
+    # sequences of its own: ids rank, rank + world, ... of world x S sequences; the renderer seeds sequence id with SEED_BASE + id.
+    P = Passes(lib, S, n_frames, args.resident_frames, SEED_BASE + rank, world, 4321 + rank, extra_frames=R)
+    r = timed_passes(P, W_, K_, F, lambda: (P.dv.sync(), barrier()), maxrank, rank, local_rank, world, R)
     n_top = (W_IN >> CULLS) * (H_IN >> CULLS)
-    P = dv.params
-    roi_n = (max(0, min(P.map_roi_x1, (W_IN >> CULLS) - 1) - max(P.map_roi_x0, 0) + 1) *
-             max(0, min(P.map_roi_y1, (H_IN >> CULLS) - 1) - max(P.map_roi_y0, 0) + 1))
-    # algorithmic bytes moved over the R timed steps (SURVEY §8-d / DESIGN.md §4), per kernel
-    alg = {"k_cull_gray": (8 * n_top * S * R, "frame ingest: sampled gray in + finest level out, 8 B/px"),
-           "k_track": (GN_BYTES_PER_PX * gn_px, "16 B x pixels swept by the Gauss-Newton iterations"),
+    Pm = P.dv.params
+    roi_n = (max(0, min(Pm.map_roi_x1, (W_IN >> CULLS) - 1) - max(Pm.map_roi_x0, 0) + 1) *
+             max(0, min(Pm.map_roi_y1, (H_IN >> CULLS) - 1) - max(Pm.map_roi_y0, 0) + 1))
+    P.close()
+    h2d_bytes = S * (H_IN >> CULLS) * W_IN * F   # stage_gray_to(): only the rows Convert::cullImage samples cross PCIe
+    # ---- BASELINE configs[4] as written: 256 sequences IN TOTAL, sharded across the N GPUs (strong scaling), 100 frames
+    strong = None
+    if not args.no_strong:
+        ids = shard.shard_ids(args.strong_total, world, rank)
+        Ss = len(ids)
+        Fs, Ws, Ks = 10, 2, 8                                    # 1 + 100 frames: 20 warm-up + 80 timed
+        Ps = Passes(lib, Ss, 1 + (Ws + Ks) * Fs, args.resident_frames, SEED_BASE + 500000 + rank, world, 8642 + rank)
+        rs = timed_passes(Ps, Ws, Ks, Fs, lambda: (Ps.dv.sync(), barrier()), maxrank, rank, local_rank, world, 0, do_roofline=False)
+        Ps.close()
+        strong = dict(total_sequences=args.strong_total, streams_per_gpu=Ss, frames_timed=Ks * Fs, frames_warmup=1 + Ws * Fs,
+                      value=args.strong_total * Ks * Fs / (rs["ms"] * 1e-3), e2e=args.strong_total * Ks * Fs / rs["e2e_s"], unit="frames/s",
+                      ms_per_frame_step=rs["ms"] / (Ks * Fs),
+                      note="BASELINE configs[4]: %d independent sequences x 100 frames sharded id mod N; at small streams_per_gpu the tracking "
+                           "kernel is bound by the latency of one stream's serial Gauss-Newton chain (cooperative split over CTAs when "
+                           "streams < SM slots), not by throughput" % args.strong_total)
+    peak, peak_src = peak_hbm()
+    # ---- per-kernel table (steady-state frames)
+    ktimes = r["ktimes"]
+    gn_px, rp, ru = r["roof_gn_px"], r["roof_prop"], r["roof_upd"]
+    alg = {"k_cull_gray": (5 * n_top * S * R, "frame ingest: sampled 8-bit gray in + finest level out, 5 B/px"),
+           "k_track": (GN_BYTES_PER_PX * gn_px + 24 * n_top * rp, "16 B x pixels swept by the Gauss-Newton iterations + Implement::propagate "
+                                                                  "of the streams that take a keyframe (24 B/px, in its epilogue)"),
            "k_propagate_scatter": (8 * n_top * rp, "depth+sigma in, 8 B/px of a propagating stream"),
            "k_propagate_gather": (16 * n_top * rp, "winner in + depth, sigma, age out, 16 B/px (propagate = 24 B/px in all)"),
            "k_map_update": (40 * roi_n * ru, "40 B x ROI pixels of an updating stream"),
            "k_map_update_apply": (1 * roi_n * ru, "flag byte per ROI pixel"),
-           "k_regularize": (12 * n_top * (rp + ru), "depth, sigma in + depth out, 12 B/px"),
+           "k_regularize": (20 * n_top * (rp + ru), "depth, sigma in + depth out + Frame::updateDepth copy-back, 20 B/px"),
            "k_regularize_commit": (8 * n_top * (rp + ru), "depth copy-back, 8 B/px")}
-    # --- end-to-end: host frames through dvo_vo_push, H2D of the input and D2H of the poses inside
-    # (dvo_vo_submit / dvo_vo_collect: frame n+1's H2D copy overlaps frame n's kernels; every step's
-    # poses are read back into pinned host memory and consumed by the host before the step counts)
-    tps = [lib.dvo_host_alloc(S * 64) for _ in range(2)]
-    Ts = [np.ctypeslib.as_array(C.cast(tp, C.POINTER(C.c_float)), shape=(S, 4, 4)) for tp in tps]
-    pose_sum = 0.0
-    def submit(i):
-        if e2e_bgr:
-            dv._ck(lib.dvo_vo_submit_bgr8(dv.ctx, host[i][0], 3, tps[i & 1]))
-        elif e2e_u8:
-            dv._ck(lib.dvo_vo_submit_gray8(dv.ctx, host[i][0], -1, tps[i & 1]))
-        else:
-            dv._ck(lib.dvo_vo_submit(dv.ctx, host[i][0], tps[i & 1]))
-
-    dv.kernel_timing(True)   # the warm-up steps double as a device-time probe of THIS part of the sequence
-    for i in range(W_):
-        submit(i)
-        dv._ck(lib.dvo_vo_collect(dv.ctx))
-    e2e_kernel_ms = sum(v[0] for v in dv.kernel_timing(False).values()) / max(W_, 1)
-    barrier()
-    t0 = time.perf_counter()
-    pending = []
-    for i in range(W_, W_ + E):
-        submit(i)
-        pending.append(i & 1)
-        if len(pending) == 2:
-            dv._ck(lib.dvo_vo_collect(dv.ctx))
-            pose_sum += float(Ts[pending.pop(0)][:, :3, 3].sum())
-    while pending:
-        dv._ck(lib.dvo_vo_collect(dv.ctx))
-        pose_sum += float(Ts[pending.pop(0)][:, :3, 3].sum())
-    dv.sync()
-    e2e_s = maxrank(time.perf_counter() - t0)
-    barrier()
-    if not np.isfinite(pose_sum):
-        raise SystemExit("bench.py: non-finite pose in the end-to-end pass")
-    for tp in tps:
-        lib.dvo_host_free(tp)
-    for hp, _ in host:
-        lib.dvo_host_free(hp)
-    dv.dev_free(dev)
-    dv.close()
-    peak, peak_src = peak_hbm()
     tot_ms = sum(v[0] for v in ktimes.values()) or 1e-9
     table = []
     for name, (kms, kn) in sorted(ktimes.items(), key=lambda kv: -kv[1][0]):
@@ -559,56 +770,77 @@ def run_gpu_arm(args, rank, world, local_rank, dist):
         table.append(dict(kernel=name, launches=kn, avg_launch_us=1e3 * kms / kn if kn else None, share=kms / tot_ms,
                           algorithmic_bytes_per_launch=b / kn if kn else None, achieved_gbs=gbs, frac=gbs / peak, bytes_model=what))
     top = table[0]
-    traffic, traffic_src, cap = ncu_traffic(top["kernel"])
-    # the levels below HBM, from the same ncu capture (one launch early in a sequence, cold cache): what the kernel is bound by when
-    # it is not DRAM - L2 traffic, and ncu's percent-of-peak for L2, L1/TEX and the SM
-    hierarchy = None
-    if cap and "lts_bytes" in cap:
-        hierarchy = dict(source=traffic_src, capture_launch_us=cap["duration_us"], l2_bytes=cap["lts_bytes"],
-                         l2_gbs=cap["lts_bytes"] / (cap["duration_us"] * 1e-6) / 1e9, l2_pct_of_peak=cap.get("lts_pct_of_peak"),
-                         l2_hit_pct=cap.get("l2_hit_pct"), l1tex_pct_of_peak=cap.get("l1tex_pct_of_peak"), l1_hit_pct=cap.get("l1_hit_pct"),
-                         sm_pct_of_peak=cap.get("sm_pct_of_peak"), dram_pct_of_measured_peak=100.0 * cap["dram_bytes"] / (cap["duration_us"] * 1e-6) / 1e9 / peak)
+    cap, cap_name, cap_why = ncu_capture(top["kernel"])
+    hierarchy = issue = None
+    traffic = None
+    if cap:
+        traffic = cap["dram_bytes"]
+        hierarchy = dict(source=cap_name, capture_launch_us=cap["duration_us"], l2_bytes=cap.get("lts_bytes"),
+                         l2_gbs=cap["lts_bytes"] / (cap["duration_us"] * 1e-6) / 1e9 if cap.get("lts_bytes") else None,
+                         l2_pct_of_peak=cap.get("lts_pct_of_peak"), l2_hit_pct=cap.get("l2_hit_pct"), l1tex_pct_of_peak=cap.get("l1tex_pct_of_peak"),
+                         l1_hit_pct=cap.get("l1_hit_pct"), sm_pct_of_peak=cap.get("sm_pct_of_peak"),
+                         dram_pct_of_measured_peak=100.0 * cap["dram_bytes"] / (cap["duration_us"] * 1e-6) / 1e9 / peak)
+        if cap.get("warp_inst"):
+            units = cap.get("units")   # ROI pixels of the updating streams in the captured launch, when the capture recorded them
+            issue = dict(source=cap_name, ipc=cap.get("ipc_active"), ipc_peak=4.0, issue_slot_pct=cap.get("issue_active_pct"),
+                         warps_active_pct=cap.get("warps_active_pct"), warp_inst_per_launch=cap["warp_inst"],
+                         inst_per_unit=(32.0 * cap["warp_inst"] / units) if units else None,
+                         unit="thread instructions per ROI pixel of an updating stream" if units else None,
+                         note="instruction-issue-bound kernel: IPC per SM against 4 schedulers x 1 instruction/clock; stall reasons and "
+                              "per-pipe utilisation of the same capture: profiles/issue_%s.txt" % source_hash())
+    total_frames = world * S * K_ * F
     res = dict(
-        value=world * S * K_ / (ms * 1e-3), ms_per_step=ms / K_,
-        e2e=dict(value=world * S * E / e2e_s, unit="frames/s", h2d_bytes_per_step=h2d_bytes, d2h_bytes_per_step=S * 64, steps=E,
-                 host_input=args.e2e_input, ms_per_step=1e3 * e2e_s / E, kernel_ms_per_step_same_frames=e2e_kernel_ms,
-                 note="host frames are full 640x480 %s in pinned memory (%d B/step)%s; Convert::cullImage(gray, 2) samples every 4th row, "
-                      "so only those rows cross PCIe (cudaMemcpy2DAsync); 2 frames in flight (%s/dvo_vo_collect); these are frames %d.. of the "
-                      "sequences, where the epipolar searches are longer than over the first %d frames `value` averages "
-                      "(kernel_ms_per_step_same_frames = device time of the same part of the sequence)"
-                      % ("8-bit BGR (cvtColor + remap on the device too, whole frames cross PCIe)" if e2e_bgr else "8-bit gray" if e2e_u8 else "float32",
-                         host_frame_bytes,
-                         ", converted on the device like Loader's convertTo(CV_32FC1, 1.0/255.0) (loader.cpp:61)" if e2e_u8 else "",
-                         "dvo_vo_submit_bgr8" if e2e_bgr else "dvo_vo_submit_gray8" if e2e_u8 else "dvo_vo_submit", e2e_first + W_, n_total)),
-        gpu_launches=int(l1 - l0), clocks=clocks,
+        value=total_frames / (r["ms"] * 1e-3), ms_per_step=r["ms"] / K_, ms_per_frame_step=r["ms"] / (K_ * F),
+        value_steady=(world * S * r["steady_frames"] / (r["steady_ms"] * 1e-3)) if r["steady_ms"] else None,
+        value_early=(world * S * r["early_frames"] / (r["early_ms"] * 1e-3)) if r["early_ms"] else None,
+        windows=dict(value="frames %d..%d of every sequence (%.2f s of device time)" % (1 + W_ * F, (W_ + K_) * F, r["ms"] * 1e-3),
+                     value_steady="frames >= %d of the timed window (%d frames per sequence)" % (STEADY_FROM, r["steady_frames"]),
+                     value_early="frames 1..%d (warm-up steps, not part of `value`)" % r["early_frames"],
+                     ms_per_frame_by_step=[t / F for t in r["step_ms"]]),
+        e2e=dict(value=total_frames / r["e2e_s"], unit="frames/s", h2d_bytes_per_step=h2d_bytes, d2h_bytes_per_step=S * 64 * F, steps=K_,
+                 host_input="gray8", ms_per_step=1e3 * r["e2e_s"] / K_, ms_per_frame_step=1e3 * r["e2e_s"] / (K_ * F),
+                 h2d_gbs_this_rank=h2d_bytes * K_ / r["e2e_local_s"] / 1e9, host_binding=binding, frames_in_flight=2,
+                 note="the SAME %d frames of the SAME sequences as `value` (dvo_vo_reset + replay), from full 640x480 8-bit gray frames in "
+                      "pinned host memory (%d B/frame-step), converted on the device like Loader's convertTo(CV_32FC1, 1.0/255.0) (loader.cpp:61); "
+                      "Convert::cullImage(gray, 2) samples every 4th row, so only those rows cross PCIe (cudaMemcpy2DAsync); frame n+1's copy "
+                      "overlaps frame n's kernels (dvo_vo_submit_gray8 / dvo_vo_collect), every frame's poses are read back"
+                      % (K_ * F, S * H_IN * W_IN)),
+        gpu_launches=r["launches"], launches_per_frame=r["launches"] / float(K_ * F), clocks=r["clocks"],
         roofline=dict(kernel=top["kernel"], bound="hbm", achieved=top["achieved_gbs"], peak=peak, unit="GB/s", frac=top["frac"],
-                      traffic=traffic, traffic_source=traffic_src, peak_source=peak_src, launches=top["launches"], avg_launch_us=top["avg_launch_us"],
+                      traffic=traffic, traffic_source=cap_name if cap else None, traffic_note=cap_why, peak_source=peak_src,
+                      launches=top["launches"], avg_launch_us=top["avg_launch_us"],
                       algorithmic_bytes_per_launch=top["algorithmic_bytes_per_launch"], share_of_step=top["share"],
-                      bytes_model=top["bytes_model"], hierarchy=hierarchy),
+                      bytes_model=top["bytes_model"], hierarchy=hierarchy, issue=issue,
+                      measured_on="frames %d..%d of the sequences (steady state), launches kept apart by the event records"
+                                  % (r["roof_first_frame"], r["roof_first_frame"] + R - 1)),
         kernels=table,
-        gn_iters_per_s=world * gn_iters / (ms * 1e-3), gn_iters_per_frame=gn_iters / float(S * K_),
-        matched_pixels_per_s=world * matched / (ms * 1e-3),  # pixels the epipolar search matched and Mapper::update fused (rank 0's count x ranks)
-        frames_propagate=n_prop, frames_update=n_upd)
+        gn_iters_per_s=world * r["gn_iters"] / (r["ms"] * 1e-3), gn_iters_per_frame=r["gn_iters"] / float(S * K_ * F),
+        matched_pixels_per_s=world * r["matched"] / (r["ms"] * 1e-3),  # pixels the epipolar search matched and Mapper::update fused (rank 0's count x ranks)
+        frames_propagate=r["n_prop"], frames_update=r["n_upd"], strong_256=strong, source_hash=source_hash())
     return res
 
 
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "--render-u8":
+        render_u8_main(sys.argv[2], int(sys.argv[3]), int(sys.argv[4]), int(sys.argv[5]))
+        return
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=100)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--streams", type=int, default=256, help="independent sequences per GPU")
-    ap.add_argument("--e2e-steps", type=int, default=12)
-    ap.add_argument("--e2e-input", default="gray8", choices=["gray8", "float32", "bgr8"],
-                    help="host frames of the end-to-end pass: 8-bit gray (camera / cv::imread form, converted on the device) or float32")
-    ap.add_argument("--roofline-steps", type=int, default=4)
-    ap.add_argument("--resident-frames", type=int, default=48, help="distinct frames per stream kept in HBM")
+    ap.add_argument("--frames-per-step", type=int, default=32, help="consecutive frames of every stream in one step")
+    ap.add_argument("--roofline-frames", type=int, default=6)
+    ap.add_argument("--resident-frames", type=int, default=48, help="distinct frames per stream kept in HBM / pinned host memory")
+    ap.add_argument("--strong-total", type=int, default=256, help="sequences of the strong-scaling pass (BASELINE configs[4])")
+    ap.add_argument("--no-strong", action="store_true")
+    ap.add_argument("--no-bind", action="store_true", help="do not pin the rank to its GPU's local CPUs")
     ap.add_argument("--cpu-frames-per-step", type=int, default=1)
     ap.add_argument("--cpu-kind", default="reference", choices=["reference", "port"],
                     help="CPU arm: the reference's own sources (oracle/_ref) or the C restatement (oracle/dvo_oracle.c)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-other-configs", action="store_true", help="skip the single-stream 1080p / 4K configurations (N = 1 only)")
+    ap.add_argument("--no-other-configs", action="store_true", help="skip the single-stream / 1080p / 4K / bundled configurations (N = 1 only)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else max(args.warmup, 1)
     # stdout carries exactly ONE line, the JSON: whatever native libraries print on file descriptor 1 meanwhile (NCCL's "NCCL version ..."
@@ -622,10 +854,13 @@ def main():
         os.write(json_fd, (json.dumps(line) + "\n").encode())
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    F = args.frames_per_step
     config = dict(workload="C5/configs[1]: %d independent synthetic 640x480 sequences per GPU, full VO loop (track + propagate|update + "
-                           "regularize), Frame(gray,K,levels=3,culls=2), random depth prior (frame.hpp:18-21)" % args.streams,
-                  streams_per_gpu=args.streams, width=W_IN, height=H_IN, levels=LEVELS, culls=CULLS,
-                  l2="each step reads a new %.0f MB input batch (> 126 MB L2); no explicit flush" % (args.streams * W_IN * H_IN * 4 / 1e6))
+                           "regularize), Frame(gray,K,levels=3,culls=2), random depth prior (frame.hpp:18-21); one step = %d consecutive "
+                           "frames of every sequence" % (args.streams, F),
+                  streams_per_gpu=args.streams, frames_per_step=F, width=W_IN, height=H_IN, levels=LEVELS, culls=CULLS,
+                  l2="no explicit flush: a frame-step reads a new 78.6 MB batch of 8-bit frames out of a 3.8 GB ring and gathers from "
+                     ">= 0.5 GB of keyframe images per step (growing with the history) - far beyond the 126 MB L2")
     base = dict(metric="VO frames/sec (track+map) at 640x480", unit="frames/s", n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
                 higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32", data="synthetic", config=config)
 
@@ -641,7 +876,6 @@ def main():
 
     dist = None
     if world > 1:
-        # stdout carries exactly ONE line (the JSON): NCCL's banner / debug lines ("NCCL version ...") go to stderr
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         import torch
         import torch.distributed as td
@@ -654,7 +888,11 @@ def main():
         fps, ms_step, info = run_cpu_arm(steps=12, warmup=1, frames_per_step=args.cpu_frames_per_step, kind=args.cpu_kind)
         info["value"] = fps; info["unit"] = "frames/s"
         cpu = info
-        if info["kind"] == "reference":   # the restatement beside it: what the same algorithm costs without per-pixel se3::exp
+        if info["kind"] == "reference":
+            # "1 thread and all host cores" - the single-thread figure of the reference ...
+            fps1, _, info1 = run_cpu_arm(steps=6, warmup=1, frames_per_step=1, cores=1, kind=args.cpu_kind)
+            cpu["one_thread_value"] = fps1; cpu["one_thread_sample"] = info1["sample"]
+            # ... and the restatement beside it: what the same algorithm costs without per-pixel se3::exp
             fps2, _, info2 = run_cpu_arm(steps=12, warmup=1, frames_per_step=4, kind="port")
             cpu["port_value"] = fps2; cpu["port_sample"] = info2["sample"]
     other = None

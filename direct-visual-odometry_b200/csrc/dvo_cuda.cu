@@ -19,6 +19,7 @@ using namespace dvo;
 struct SlotHost {
     void* base = nullptr;
     bool in_use = false;
+    bool quad_valid = false; // granular slots: dev.quad matches dev.gray (VO pool slots are kept valid by the kernels themselves)
     SlotDev dev{};
 };
 
@@ -63,7 +64,13 @@ struct dvo_ctx {
     int* h_status = nullptr;       // pinned: [0], [1] = status read back with pipeline buffer k's poses; [2] = synchronous pushes
     bool overlap = true;           // k_map_update as a programmatic dependent of k_track (DVO_OVERLAP=0 disables)
     bool fuse_prop = true;         // Implement::propagate in k_track's epilogue (DVO_FUSE_PROP=0: the two wide kernels)
-    bool fold_commit = false;      // Frame::updateDepth by k_regularize's last CTA (DVO_FOLD_COMMIT=1; measured slower than k_regularize_commit)
+    // keyframe-pool growth: max over streams of the keyframe count, read back asynchronously (d_status[1])
+    int kf_known = 0, kf_known_frame = -1;
+    uint64_t rng_known = 0;        // furthest replay position of any stream after frame kf_known_frame
+    int kf_rb_frame[2] = {-1, -1};
+    bool kf_rb_pending[2] = {false, false};
+    cudaEvent_t ev_kf[2] = {nullptr, nullptr};
+    unsigned kf_gen = 0;
     int status_pending[2] = {0, 0};
     float* d_stage_in = nullptr;   // [S][in_h][in_w]
     float* d_stage[3] = {nullptr, nullptr, nullptr}; // depth/sigma/age uploads, download staging
@@ -155,6 +162,7 @@ static int alloc_slot(dvo_ctx* ctx, int idx)
         // A recycled slot must not hand its previous occupant's depth / sigma / age / pose to the new Frame: the reference's
         // Frame ctor starts from m_age = zeros and a fresh prior (frame.hpp:108-117).  Same state as a first allocation: all zero.
         CK(cudaMemsetAsync(sh.base, 0, ctx->slot_bytes, ctx->stream));
+        sh.quad_valid = false;
         return DVO_OK;
     }
     CK(cudaMalloc(&sh.base, ctx->slot_bytes));
@@ -163,6 +171,7 @@ static int alloc_slot(dvo_ctx* ctx, int idx)
     const Consts& c = ctx->c;
     const size_t ntop = (size_t)c.lv[c.L - 1].n;
     auto take = [&](size_t bytes) { char* r = p; p += (bytes + 255) & ~(size_t)255; return r; };
+    sh.dev.quad = (float4*)take((size_t)c.S * ntop * sizeof(float4));
     sh.dev.ds = (float2*)take((size_t)c.S * ntop * sizeof(float2));
     sh.dev.gray = (float*)take((size_t)c.S * ntop * sizeof(float));
     sh.dev.age = (float*)take((size_t)c.S * ntop * sizeof(float));
@@ -229,7 +238,7 @@ extern "C" int dvo_create(dvo_ctx** out, const dvo_params* p)
     const int S = c.S, ntop = c.lv[c.L - 1].n;
     size_t sb = 0;
     auto rnd = [](size_t b) { return (b + 255) & ~(size_t)255; };
-    sb += rnd((size_t)S * ntop * 8) + 2 * rnd((size_t)S * ntop * 4) + 2 * rnd((size_t)S * 24);
+    sb += rnd((size_t)S * ntop * 16) + rnd((size_t)S * ntop * 8) + 2 * rnd((size_t)S * ntop * 4) + 2 * rnd((size_t)S * 24);
     ctx->slot_bytes = sb;
     // slot ids [0, max_frames): granular API; [max_frames, max_frames + max_keyframes]: the VO pool
     // (entry k = keyframe k of every stream, entry n_kf = the stream's current frame)
@@ -246,13 +255,13 @@ extern "C" int dvo_create(dvo_ctx** out, const dvo_params* p)
     CK(cudaMalloc(&ctx->d_tab, sizeof(PoseTab) * (size_t)S * c.kf_stride));
     CK(cudaMalloc(&ctx->d_rq, sizeof(ReadyQ) + sizeof(int) * (size_t)S));
     CK(cudaMemset(ctx->d_rq, 0, sizeof(ReadyQ) + sizeof(int) * (size_t)S));
-    CK(cudaMalloc(&ctx->d_status, sizeof(int)));
-    CK(cudaMemset(ctx->d_status, 0, sizeof(int)));
-    CK(cudaMallocHost(&ctx->h_status, sizeof(int) * 4));
-    memset(ctx->h_status, 0, sizeof(int) * 4);
+    CK(cudaMalloc(&ctx->d_status, sizeof(int) * 4));   // [0] first device-side error, [1] max over streams of the keyframe count,
+    CK(cudaMemset(ctx->d_status, 0, sizeof(int) * 4));  // [2] max over streams of the mt19937 replay position
+    CK(cudaMallocHost(&ctx->h_status, sizeof(int) * 8)); // [0..2] error read-backs, [4..5] keyframe-count read-backs
+    memset(ctx->h_status, 0, sizeof(int) * 8);
     if (const char* e = getenv("DVO_OVERLAP")) ctx->overlap = atoi(e) != 0;
     if (const char* e = getenv("DVO_FUSE_PROP")) ctx->fuse_prop = atoi(e) != 0;
-    if (const char* e = getenv("DVO_FOLD_COMMIT")) ctx->fold_commit = atoi(e) != 0;
+    for (int k = 0; k < 2; k++) CK(cudaEventCreateWithFlags(&ctx->ev_kf[k], cudaEventDisableTiming));
     for (int k = 0; k < 2; k++) { // pipeline events exist from the start: buffer 0 is d_stage_in, which the plain entry points use too
         CK(cudaEventCreateWithFlags(&ctx->ev_copied[k], cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&ctx->ev_consumed[k], cudaEventDisableTiming));
@@ -345,6 +354,7 @@ extern "C" void dvo_destroy(dvo_ctx* ctx)
     for (int k = 0; k < 2; k++)
         if (ctx->ev_copied[k]) { cudaEventDestroy(ctx->ev_copied[k]); cudaEventDestroy(ctx->ev_consumed[k]); cudaEventDestroy(ctx->ev_done[k]); }
     for (auto e : ctx->user_ev) if (e) cudaEventDestroy(e);
+    for (int k = 0; k < 2; k++) if (ctx->ev_kf[k]) cudaEventDestroy(ctx->ev_kf[k]);
     for (auto e : ctx->k_ev) cudaEventDestroy(e);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -435,6 +445,7 @@ static int build_frame(dvo_ctx* ctx, int slot, const float* gray_dev, bool rows_
     const VoState* vo = slot < 0 ? ctx->d_vo : nullptr;
     const LevelGeom& gt = c.lv[c.L - 1];
     dim3 grid(cdiv(gt.n, 1024), c.S);
+    if (slot >= 0) ctx->slots[slot].quad_valid = false;
     ReadyQ* rq = vo ? ctx->d_rq : nullptr; // the VO frame's first kernel clears the tracking -> mapping hand-over queue
     {
         KTimer t(ctx, K_CULL);
@@ -610,6 +621,7 @@ extern "C" int dvo_frame_create_kinect(dvo_ctx* ctx, int* slot, const uint8_t* b
     const LevelGeom& gt = c.lv[c.L - 1];
     k_kinect_frame<<<dim3(cdiv(gt.n, 256), c.S), 256, 0, ctx->stream>>>(c, k, ctx->d_kin_color, ctx->d_kin_depth, ctx->slots[*slot].dev);
     KCHECK();
+    ctx->slots[*slot].quad_valid = false;
     return DVO_OK;
 }
 
@@ -1144,11 +1156,9 @@ static int enqueue_propagate(dvo_ctx* ctx)
 
 // mt19937 replay table (src/math/gaussian.cpp:8-9): the reference's engine is unbounded, so the table grows on demand.  Every
 // Mapper::update can consume at most roi.n draws per stream; `rng_bound` bounds every stream's position from above.
-static int rng_reserve(dvo_ctx* ctx)
+static int rng_reserve(dvo_ctx* ctx, uint64_t need)
 {
     Consts& c = ctx->c;
-    const uint64_t need = ctx->rng_bound + (uint64_t)(ctx->roi.n > 0 ? ctx->roi.n : 0);
-    ctx->rng_bound = need;
     if (need <= (uint64_t)c.rng_table) return DVO_OK;
     uint64_t len = (uint64_t)c.rng_table * 2;
     while (len < need) len *= 2;
@@ -1204,26 +1214,37 @@ static int enqueue_update(dvo_ctx* ctx, bool tables, bool overlapped)
         KTimer t(ctx, K_MAP_APPLY);
         dim3 agrid(cdiv(ctx->roi.nblk, APPLY_SUB), c.S);
         k_map_update_apply<<<agrid, MAPU_THREADS * APPLY_SUB, 0, ctx->stream>>>(c, ctx->roi, ctx->d_slots, ctx->d_ms, ctx->d_flags,
-                                                                                 ctx->d_blockcnt, ctx->d_rng);
+                                                                                 ctx->d_blockcnt, ctx->d_rng, ctx->d_status);
         KCHECK();
     }
     return DVO_OK;
 }
-static int enqueue_regularize(dvo_ctx* ctx)
+static int enqueue_regularize(dvo_ctx* ctx, bool vo)
 {
     const Consts& c = ctx->c;
     const int ntop = c.lv[c.L - 1].n;
-    const bool fold = ctx->fold_commit && small_level(ctx);
     {
         KTimer t(ctx, K_REGULARIZE);
-        k_regularize<<<dim3(cdiv(ntop, 256), c.S), 256, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ms, ctx->d_tmp, fold ? 1 : 0);
+        k_regularize<<<dim3(cdiv(ntop, 256), c.S), 256, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ms, ctx->d_tmp, vo ? 1 : 0);
         KCHECK();
     }
-    if (!fold) {
+    {
         KTimer t(ctx, K_REG_COMMIT);
         k_regularize_commit<<<dim3(cdiv(ntop, 512), c.S), 256, 0, ctx->stream>>>(c, ctx->d_slots, ctx->d_ms, ctx->d_tmp);
         KCHECK();
     }
+    return DVO_OK;
+}
+
+// the 2x2-footprint image of a granular slot that is about to serve as a born keyframe (VO pool slots are kept valid on the device)
+static int ensure_quad(dvo_ctx* ctx, int slot)
+{
+    const Consts& c = ctx->c;
+    SlotHost& sh = ctx->slots[slot];
+    if (slot >= c.vo_base || sh.quad_valid) return DVO_OK;
+    k_build_quad<<<dim3(cdiv(c.lv[c.L - 1].n, 256), c.S), 256, 0, ctx->stream>>>(c, ctx->d_slots, slot, nullptr);
+    KCHECK();
+    sh.quad_valid = true;
     return DVO_OK;
 }
 
@@ -1278,6 +1299,8 @@ extern "C" int dvo_map_update(dvo_ctx* ctx, int obj_slot, int ref_slot, const in
     for (int k = 0; k < n_hist; k++) {
         rc = check_slot(ctx, history_slots[k]);
         if (rc) return rc;
+        rc = ensure_quad(ctx, history_slots[k]);
+        if (rc) return rc;
     }
     // hist is stored in push order (oldest first); history_slots is indexed by age (newest first)
     std::vector<int> order(n_hist);
@@ -1290,7 +1313,8 @@ extern "C" int dvo_map_update(dvo_ctx* ctx, int obj_slot, int ref_slot, const in
     KCHECK();
     k_map_prepare<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_ms, ctx->slots[obj_slot].dev.rel_xi);
     KCHECK();
-    rc = rng_reserve(ctx);
+    ctx->rng_bound += (uint64_t)(ctx->roi.n > 0 ? ctx->roi.n : 0);
+    rc = rng_reserve(ctx, ctx->rng_bound);
     if (rc) return rc;
     rc = enqueue_update(ctx, true, false); // ref->updateDepthSigma (mapper.cpp:135) is implicit: coarser levels are views
     if (rc) return rc;
@@ -1312,7 +1336,7 @@ extern "C" int dvo_map_regularize(dvo_ctx* ctx, int slot)
     const Consts& c = ctx->c;
     k_map_config<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_ms, slot, slot, slot, 0, 0, 0, 1, slot);
     KCHECK();
-    rc = enqueue_regularize(ctx);
+    rc = enqueue_regularize(ctx, false);
     if (rc) return rc;
     CK(cudaStreamSynchronize(ctx->stream));
     return DVO_OK;
@@ -1343,6 +1367,8 @@ extern "C" int dvo_map_update_points(dvo_ctx* ctx, int obj_slot, int born_slot, 
     if (rc) return rc;
     const Consts& c = ctx->c;
     ARG(relative_xi && n > 0 && px && py && depth && sigma && out_depth && out_sigma, "bad argument");
+    rc = ensure_quad(ctx, born_slot);
+    if (rc) return rc;
     const size_t N = (size_t)c.S * n;
     DevScratch sc;
     CK(cudaMalloc(&sc.p, N * 24 + sizeof(float) * 6 * (size_t)c.S));
@@ -1457,8 +1483,11 @@ extern "C" int dvo_vo_reset(dvo_ctx* ctx)
     ctx->vo_frame_id = -1;
     ctx->forced_pending = false;
     ctx->rng_bound = 0;
-    CK(cudaMemsetAsync(ctx->d_status, 0, sizeof(int), ctx->stream));
-    memset(ctx->h_status, 0, sizeof(int) * 4);
+    CK(cudaStreamSynchronize(ctx->stream)); // read-backs of the previous sequence must not land after this point
+    ctx->kf_known = 0; ctx->kf_known_frame = -1; ctx->rng_known = 0;
+    ctx->kf_rb_pending[0] = ctx->kf_rb_pending[1] = false;
+    CK(cudaMemsetAsync(ctx->d_status, 0, sizeof(int) * 4, ctx->stream));
+    memset(ctx->h_status, 0, sizeof(int) * 8);
     k_vo_reset<<<cdiv(c.S, 64), 64, 0, ctx->stream>>>(c, ctx->d_vo, ctx->d_ms);
     KCHECK();
     return DVO_OK;
@@ -1507,11 +1536,22 @@ static int vo_push_impl(dvo_ctx* ctx, const float* gray_dev, const float* init_d
     const Consts& c = ctx->c;
     ARG(gray_dev, "null gray");
     const int frame_id = ++ctx->vo_frame_id; // Frame::latest_id, frame.cpp:5
-    // After f pushed frames a stream owns at most f keyframes: pool entries 0..min(f, max_kf) can be
-    // touched by this push.  Entries are allocated on first need and never freed (FrameHistory is
-    // never pruned, frame.hpp:179-185).
+    // Keyframe pool: entry k holds keyframe k of every stream, entry n_kf the frame being processed, so this push can touch entries
+    // 0 .. M where M = the largest keyframe count of any stream after the previous frame.  M is read back asynchronously
+    // (d_status[1], written by the tracking epilogue); between read-backs it grows by at most one per frame.  Entries are allocated
+    // on first need and never freed (FrameHistory is never pruned, frame.hpp:179-185).
     {
-        const int need = (frame_id < c.max_kf ? frame_id : c.max_kf);
+        for (int k = 0; k < 2; k++)
+            if (ctx->kf_rb_pending[k] && cudaEventQuery(ctx->ev_kf[k]) == cudaSuccess) {
+                ctx->kf_rb_pending[k] = false;
+                if (ctx->kf_rb_frame[k] > ctx->kf_known_frame) {
+                    ctx->kf_known = ctx->h_status[4 + 2 * k]; ctx->rng_known = (uint64_t)(unsigned)ctx->h_status[5 + 2 * k];
+                    ctx->kf_known_frame = ctx->kf_rb_frame[k];
+                }
+            }
+        int need = ctx->kf_known + (frame_id - 1 - ctx->kf_known_frame);
+        if (need > frame_id) need = frame_id;
+        if (need > c.max_kf) need = c.max_kf;
         for (int k = 0; k <= need; k++) {
             SlotHost& sh = ctx->slots[c.vo_base + k];
             if (!sh.base) {
@@ -1539,7 +1579,12 @@ static int vo_push_impl(dvo_ctx* ctx, const float* gray_dev, const float* init_d
     const bool fused = ctx->fuse_prop && small_level(ctx) && ctx->trk_B == 1;   // propagate in the tracking kernel's epilogue
     const bool overlapped = ctx->overlap && ctx->trk_B == 1 && !ctx->ktiming;   // per-kernel timing needs the launches apart
     if (frame_id > 0) {
-        rc = rng_reserve(ctx); // before the launches: Mapper::update must follow the tracking kernel back to back
+        // before the launches (Mapper::update must follow the tracking kernel back to back): every frame since the last read-back
+        // can have consumed at most roi.n draws per stream
+        const uint64_t per = (uint64_t)(ctx->roi.n > 0 ? ctx->roi.n : 0);
+        const uint64_t bound = ctx->rng_known + per * (uint64_t)(frame_id - ctx->kf_known_frame);
+        if (bound > ctx->rng_bound) ctx->rng_bound = bound; // dvo_map_update on the same context continues from here
+        rc = rng_reserve(ctx, bound);
         if (rc) return rc;
     }
     // Tracking (system.hpp:57) against each stream's current keyframe (no-op on the first frame), then
@@ -1556,8 +1601,20 @@ static int vo_push_impl(dvo_ctx* ctx, const float* gray_dev, const float* init_d
             rc = enqueue_propagate(ctx); // update and propagate touch disjoint streams: their order is free
             if (rc) return rc;
         }
-        rc = enqueue_regularize(ctx);
+        rc = enqueue_regularize(ctx, true);
         if (rc) return rc;
+    } else {
+        // frame 0 is the first keyframe: its 2x2-footprint image (later ones are written by k_regularize when they are created)
+        k_build_quad<<<dim3(cdiv(c.lv[c.L - 1].n, 256), c.S), 256, 0, ctx->stream>>>(c, ctx->d_slots, -1, ctx->d_vo);
+        KCHECK();
+    }
+    {   // keyframe-count read-back for the pool (see above): one of two slots, whichever is free
+        const int k = ctx->kf_rb_pending[0] ? (ctx->kf_rb_pending[1] ? -1 : 1) : 0;
+        if (k >= 0) {
+            CK(cudaMemcpyAsync(ctx->h_status + 4 + 2 * k, ctx->d_status + 1, sizeof(int) * 2, cudaMemcpyDeviceToHost, ctx->stream));
+            CK(cudaEventRecord(ctx->ev_kf[k], ctx->stream));
+            ctx->kf_rb_pending[k] = true; ctx->kf_rb_frame[k] = frame_id;
+        }
     }
     if (T_out) {
         // device-side errors (history overflow) come back with the poses: checked here when synchronous, in dvo_vo_collect otherwise

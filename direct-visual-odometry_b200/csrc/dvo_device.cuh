@@ -105,37 +105,42 @@ __device__ __forceinline__ float subpixel_dense(const float* __restrict__ img, i
     return bilerp(g0, g1, g2, g3, hh, v);
 }
 
-// Branch-free form for the epipolar search loop (bit-identical results).  trunc_x86 + in_range collapse into float compares:
-// for finite p, 0 <= (int)p < w  <=>  -1 < p < w, and NaN / inf / out-of-int-range p fail the compares just as cvttss2si's
-// INT_MIN fails in_range.  The border rule (taps outside the image take the (x0, y0) value) becomes zero offsets plus one select,
-// so the four loads issue back to back without control flow.  wf = (float)w, hf = (float)h (exact: sizes < 2^24).
-__device__ __forceinline__ float subpixel_dense_nb(const float* __restrict__ img, int w, int h, float wf, float hf, float px, float py)
+// Convert::getSubpixelFromDense through the 2x2-footprint image (SlotDev::quad): the border rule is baked into the footprints, so
+// a tap is one range test, one 16-byte load and the bilinear arithmetic.  Bit-identical to subpixel_dense.
+__device__ __forceinline__ float subpixel_quad(const float4* __restrict__ quad, int w, float wf, float hf, float px, float py)
 {
     if (!(px > -1.0f && px < wf && py > -1.0f && py < hf)) return DVO_INV;
     const int x0 = __float2int_rz(px), y0 = __float2int_rz(py);
     const float hh = px - (float)x0, v = py - (float)y0;
-    const float* __restrict__ p = img + (y0 * w + x0);
-    const int ox = (x0 + 1 < w) ? 1 : 0, oy = (y0 + 1 < h) ? w : 0;
-    const float g0 = __ldg(p), g1 = __ldg(p + ox), g2 = __ldg(p + oy), g3r = __ldg(p + oy + ox);
-    const float g3 = (ox != 0 && oy != 0) ? g3r : g0;
-    return bilerp(g0, g1, g2, g3, hh, v);
+    const float4 q = __ldg(quad + (y0 * w + x0));
+    return bilerp(q.x, q.y, q.z, q.w, hh, v);
 }
-
-// Fully predicated form: no branch at all.  Out-of-image positions read texel (0, 0) and the result is replaced by INVALID with
-// one select, so the compiler is free to interleave the address arithmetic and loads of neighbouring taps (the search loop's
-// stall samples were 14 % branch resolution with three BSSY regions per step, profiles/r1g_full issue summary).
-__device__ __forceinline__ float subpixel_dense_bf(const float* __restrict__ img, int w, int h, float wf, float hf, float px, float py)
+// The same tap split in two: the 16-byte load is issued early (one search step ahead), the arithmetic happens when it is needed.
+// In the steady state of a long sequence the born keyframes of a stream no longer fit any cache (hundreds of keyframes per
+// stream): a tap is a DRAM access and the search is bound by how many of them are in flight, not by instruction issue.
+struct QuadTap {
+    float4 q;
+    float hh, v;
+    bool in;
+};
+__device__ __forceinline__ QuadTap quad_tap_issue(const float4* __restrict__ quad, int w, float wf, float hf, float px, float py)
 {
-    const bool in = (px > -1.0f && px < wf && py > -1.0f && py < hf);
-    const float qx = in ? px : 0.0f, qy = in ? py : 0.0f;
+    QuadTap t;
+    t.in = (px > -1.0f && px < wf && py > -1.0f && py < hf);
+    const float qx = t.in ? px : 0.0f, qy = t.in ? py : 0.0f;
     const int x0 = __float2int_rz(qx), y0 = __float2int_rz(qy);
-    const float hh = qx - (float)x0, v = qy - (float)y0;
-    const float* __restrict__ p = img + (y0 * w + x0);
-    const int ox = (x0 + 1 < w) ? 1 : 0, oy = (y0 + 1 < h) ? w : 0;
-    const float g0 = __ldg(p), g1 = __ldg(p + ox), g2 = __ldg(p + oy), g3r = __ldg(p + oy + ox);
-    const float g3 = (ox != 0 && oy != 0) ? g3r : g0;
-    const float r = bilerp(g0, g1, g2, g3, hh, v);
-    return in ? r : DVO_INV;
+    t.hh = qx - (float)x0; t.v = qy - (float)y0;
+    t.q = __ldg(quad + (y0 * w + x0));
+    return t;
+}
+__device__ __forceinline__ float quad_tap_value(const QuadTap& t) { return t.in ? bilerp(t.q.x, t.q.y, t.q.z, t.q.w, t.hh, t.v) : DVO_INV; }
+
+__device__ __forceinline__ float4 make_quad(const float* __restrict__ img, int w, int h, int x, int y)
+{
+    const float* p = img + (size_t)y * w + x;
+    const bool xin = x + 1 < w, yin = y + 1 < h;
+    const float g0 = p[0];
+    return make_float4(g0, xin ? p[1] : g0, yin ? p[w] : g0, (xin && yin) ? p[w + 1] : g0);
 }
 
 // The same, split into position, loads and arithmetic, so that a caller can put several samples' loads in

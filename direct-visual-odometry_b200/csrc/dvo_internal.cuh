@@ -1,7 +1,8 @@
 // dvo_internal.cuh — device-visible data model shared by the kernels and the C-ABI layer.
 //
 // HBM layout.  A frame slot keeps ONLY the finest pyramid level of every stream:
-//   gray [S][n_top] float, ds [S][n_top] float2 {depth, sigma}, age [S][n_top] float, xi/rel_xi [S][6].
+//   gray [S][n_top] float, ds [S][n_top] float2 {depth, sigma}, age [S][n_top] float, xi/rel_xi [S][6],
+//   quad [S][n_top] float4 (the gray image as 2x2 bilinear footprints, keyframes only: what the epipolar search samples).
 // Coarser levels are never materialised: Convert::cullImage is top-left point sampling through
 // Convert::getPixel (convert.cpp:7-20,107-125), and the reference re-culls depth/sigma from the
 // finest map after every map step (frame.cpp:39-61), so level l pixel (x, y) is exactly
@@ -47,6 +48,9 @@ struct Consts {
 
 // One frame slot as the device sees it.  All images are stream-major: base + s * n_top.
 struct SlotDev {
+    float4* quad;  // finest-level gray as 2x2 footprints  [S][n_top]: {I(x,y), I(x+1,y), I(x,y+1), I(x+1,y+1)} with the border rule
+                   // of Convert::getSubpixelFromDense applied (convert.cpp:77-105: a tap outside the image takes I(x,y)), so that one
+                   // bilinear tap of the epipolar search is ONE 16-byte load.  Valid for keyframes only (built when a frame becomes one).
     float* gray;   // finest-level gray                    [S][n_top]
     float2* ds;    // finest-level {depth, sigma}          [S][n_top]
     float* age;    // finest level                         [S][n_top]

@@ -796,6 +796,7 @@ __device__ __noinline__ void vo_decide(const Consts& c, const TrackArgs& a, cons
         a.hist[(size_t)s * c.kf_stride] = cur_slot;
         v->n_kf = 1; v->kf_slot = cur_slot; v->kf_frame_id = a.frame_id;
         m->reg_slot = cur_slot;
+        if (a.status) atomicMax(a.status + 1, 1);
         return;
     }
     float rel[6], kxi[6], xi[6];
@@ -834,6 +835,7 @@ __device__ __noinline__ void vo_decide(const Consts& c, const TrackArgs& a, cons
         }
     }
     m->reg_slot = v->kf_slot;
+    if (a.status) atomicMax(a.status + 1, v->n_kf); // the host grows the keyframe pool by the largest count of any stream
     // a stream that has failed (history overflow) keeps tracking against its last good keyframe but is no longer mapped: its
     // maps would silently stop matching the reference (the reference itself would have thrown, frame.hpp:176)
     if (m->err) {
@@ -1227,28 +1229,20 @@ constexpr int SEARCH_UNROLL = DVO_SEARCH_UNROLL; // steps of a chunk whose loads
 struct SearchSmem { // per warp
     float2 cp[SEARCH_NCP][32];
     float dirx[32], diry[32], og[32];
-    const float* born[32];
+    const float4* born[32];
     int nsteps[32];
     int2 owner[32]; // per round: run head lane -> {pixel, first chunk index of the pixel}
     unsigned long long best[32];
 };
 
-#ifndef DVO_SEARCH_BF
-#define DVO_SEARCH_BF 0
-#endif
-#if DVO_SEARCH_BF
-#define SEARCH_TAP subpixel_dense_bf
-#else
-#define SEARCH_TAP subpixel_dense_nb
+#define SEARCH_TAP(img, w, h, wf, hf, x, y) subpixel_quad(img, w, wf, hf, x, y)
+#ifndef DVO_SEARCH_PREFETCH
+#define DVO_SEARCH_PREFETCH 0
 #endif
 __device__ __forceinline__ float search_ssd(float s0, float s1, float s2, float og)
 {
     // implement.cpp:122-139: a tap that is invalid ends the accumulation with ssd = 2.0 * 3
-#if DVO_SEARCH_BF
-    const bool bad = is_invalid(s0) || is_invalid(s1) || is_invalid(s2); // selected at the end: no branch in the search loop
-#else
     if (is_invalid(s0) || is_invalid(s1) || is_invalid(s2)) return 2.0f * 3;
-#endif
     const float d0 = s0 - og, d1 = s1 - og, d2 = s2 - og;
     // first term: (float)(0.0 + (double)(1/3) * (double)a), a = d0 * d0 >= 0, equals the correctly rounded float quotient a / 3 for
     // EVERY non-negative finite float (a / 3 is never within 2^-27 relative of a float rounding boundary, the double product is within
@@ -1261,15 +1255,11 @@ __device__ __forceinline__ float search_ssd(float s0, float s1, float s2, float 
     // third term: weight 3/3 = 1.0, i.e. (float)((double)ssd + (double)(d2 * d2)).  For two non-negative floats that equals the
     // float sum: the double sum is exact unless the exponents are > 29 bits apart, and then both roundings return ssd itself.
     ssd = __fadd_rn(ssd, d2 * d2);
-#if DVO_SEARCH_BF
-    return bad ? 2.0f * 3 : ssd;
-#else
     return ssd;
-#endif
 }
 
 // All 32 lanes of the warp must call this (active = false for lanes without a segment).  w, h are warp-uniform.
-__device__ __forceinline__ void warp_search(SearchSmem& sm, bool active, const float* __restrict__ born_gray, int w, int h, float sx,
+__device__ __forceinline__ void warp_search(SearchSmem& sm, bool active, const float4* __restrict__ born_quad, int w, int h, float sx,
                                             float sy, float dirx, float diry, float length, float og, float& bestx, float& besty,
                                             float& min_ssd)
 {
@@ -1284,6 +1274,16 @@ __device__ __forceinline__ void warp_search(SearchSmem& sm, bool active, const f
         float ptx = sx, pty = sy;
         int nskip = 0;
         if (fabsf(sx) < 16384.f && fabsf(sy) < 16384.f && length < 16384.f) nskip = min((int)length - 2, 100);
+        // whole checkpoint intervals first: 2^shift additions per coordinate back to back (n is a multiple of the interval here)
+        for (; n + (1 << SEARCH_CP_SHIFT) <= nskip;) {
+#pragma unroll
+            for (int u = 0; u < (1 << SEARCH_CP_SHIFT); u++) {
+                ptx += dirx;
+                pty += diry;
+            }
+            n += 1 << SEARCH_CP_SHIFT;
+            sm.cp[n >> SEARCH_CP_SHIFT][lane] = make_float2(ptx, pty);
+        }
         for (; n < nskip;) {
             ptx += dirx;
             pty += diry;
@@ -1310,7 +1310,7 @@ __device__ __forceinline__ void warp_search(SearchSmem& sm, bool active, const f
     }
     const int excl = incl - nch;
     const int total = __shfl_sync(full, incl, 31);
-    sm.dirx[lane] = dirx; sm.diry[lane] = diry; sm.og[lane] = og; sm.born[lane] = born_gray; sm.nsteps[lane] = n;
+    sm.dirx[lane] = dirx; sm.diry[lane] = diry; sm.og[lane] = og; sm.born[lane] = born_quad; sm.nsteps[lane] = n;
     const unsigned long long key0 = (unsigned long long)__float_as_uint(2.0f * 3) << 32; // min_ssd = 6, best = start (step 0)
     sm.best[lane] = key0;
     __syncwarp();
@@ -1339,7 +1339,7 @@ __device__ __forceinline__ void warp_search(SearchSmem& sm, bool active, const f
             const float2 cpt = sm.cp[ch][p];
             float ptx = cpt.x, pty = cpt.y;
             const float dx = sm.dirx[p], dy = sm.diry[p], ogp = sm.og[p];
-            const float* __restrict__ img = sm.born[p];
+            const float4* __restrict__ img = sm.born[p];
             // the reference's loop body (implement.cpp:121-140) for steps b0+1 .. b0+cnt.  It samples pt - dir, pt, pt + dir at
             // every step ("TODO: 1/N" in the reference).  pt + dir is, bit for bit, the next step's pt (pt += dir), so the centre
             // tap is the previous step's third tap; and pt - dir rounds back to the previous pt unless the forward addition hit a
@@ -1353,11 +1353,31 @@ __device__ __forceinline__ void warp_search(SearchSmem& sm, bool active, const f
             pty += dy;
             float c_cur = SEARCH_TAP(img, w, h, wf, hf, ptx + dx * 0.0f, pty + dy * 0.0f); // tap at pt (k = 1)
             unsigned long long kbest = ~0ull;
+#if DVO_SEARCH_PREFETCH
+            // the tap of step k (at pt + dir = the next step's pt) is loaded one step ahead; positions are accumulated exactly as the
+            // serial walk does (pt += dir), so they are bit-identical
+            QuadTap pend = quad_tap_issue(img, w, wf, hf, ptx + dx * 1.0f, pty + dy * 1.0f);
+#pragma unroll(SEARCH_UNROLL)
+            for (int k = 1; k <= cnt; k++) {
+                const QuadTap cur = pend;
+                const float nx = ptx + dx, ny = pty + dy;                         // pt of step k + 1
+                if (k < cnt) pend = quad_tap_issue(img, w, wf, hf, nx + dx * 1.0f, ny + dy * 1.0f);
+                const float s2 = quad_tap_value(cur);
+                const float bx = ptx + dx * -1.0f, by = pty + dy * -1.0f;
+                const float s0 = (bx == prevx && by == prevy) ? c_prev : SEARCH_TAP(img, w, h, wf, hf, bx, by);
+                const unsigned long long key = ((unsigned long long)__float_as_uint(search_ssd(s0, c_cur, s2, ogp)) << 32) | (unsigned)(b0 + k);
+                if (key < kbest) kbest = key;
+                c_prev = c_cur; c_cur = s2;
+                prevx = ptx; prevy = pty;
+                ptx = nx;
+                pty = ny;
+            }
+#else
 #pragma unroll(SEARCH_UNROLL)
             for (int k = 1; k <= cnt; k++) {
                 const float s2 = SEARCH_TAP(img, w, h, wf, hf, ptx + dx * 1.0f, pty + dy * 1.0f);
                 const float bx = ptx + dx * -1.0f, by = pty + dy * -1.0f;
-                const float s0 = (bx == prevx && by == prevy) ? c_prev : subpixel_dense_nb(img, w, h, wf, hf, bx, by);
+                const float s0 = (bx == prevx && by == prevy) ? c_prev : SEARCH_TAP(img, w, h, wf, hf, bx, by);
                 const unsigned long long key = ((unsigned long long)__float_as_uint(search_ssd(s0, c_cur, s2, ogp)) << 32) | (unsigned)(b0 + k);
                 if (key < kbest) kbest = key;
                 c_prev = c_cur; c_cur = s2;
@@ -1365,6 +1385,7 @@ __device__ __forceinline__ void warp_search(SearchSmem& sm, bool active, const f
                 ptx += dx;
                 pty += dy;
             }
+#endif
             // lanes [hp, rend) form this lane's run: smallest ssd of the run, at its earliest step
             const unsigned above = (hp == 31) ? 0u : (heads >> (hp + 1)) << (hp + 1);
             const int end = above ? __ffs(above) - 1 : 32;
@@ -1558,7 +1579,8 @@ __global__ void __launch_bounds__(MAPU_THREADS, DVO_MAPU_MINB) k_map_update(cons
     bool cand = false;
     int i = 0, px = 0, py = 0;
     float prior_d = 0.f, prior_s = 0.f, og = 0.f;
-    const float* born_gray = nullptr;
+    const float4* born_quad = nullptr;
+    int born_slot = 0;
     const PoseTab* pt = nullptr;
     Segment seg{};
     float2* ds = nullptr;
@@ -1584,12 +1606,12 @@ __global__ void __launch_bounds__(MAPU_THREADS, DVO_MAPU_MINB) k_map_update(cons
             if (age < 0 || age >= n_hist) {
                 atomicCAS(&m->err, 0, (int)DVO_ERR_HISTORY); // m_history.at() would throw
             } else {
-                const int born_slot = __ldcg(hist + (size_t)s * c.kf_stride + (n_hist - 1 - age));
+                born_slot = __ldcg(hist + (size_t)s * c.kf_stride + (n_hist - 1 - age));
                 pt = tab + (size_t)s * c.kf_stride + age;
                 prior_d = d - __ldcg(&m->rel_z); // :104
                 prior_s = dsv.y;
                 og = __ldg(slots[__ldcg(&m->obj_slot)].gray + (size_t)s * g.n + (size_t)py * g.w + px);
-                born_gray = slots[born_slot].gray + (size_t)s * g.n;
+                born_quad = slots[born_slot].quad + (size_t)s * g.n;
                 seg = make_segment(g, pt->T, px, py, prior_d, prior_s);
                 cand = true;
             }
@@ -1597,12 +1619,12 @@ __global__ void __launch_bounds__(MAPU_THREADS, DVO_MAPU_MINB) k_map_update(cons
     }
     // --- epipolar search, shared by the warp (implement.cpp:106-152)
     float bestx, besty, min_ssd;
-    warp_search(s_search[threadIdx.x >> 5], cand, born_gray, g.w, g.h, seg.sx, seg.sy, (seg.ex - seg.sx) / seg.length,
+    warp_search(s_search[threadIdx.x >> 5], cand, born_quad, g.w, g.h, seg.sx, seg.sy, (seg.ex - seg.sx) / seg.length,
                 (seg.ey - seg.sy) / seg.length, seg.length, og, bestx, besty, min_ssd);
     // --- per pixel: depth / sigma estimate, gate, fusion (implement.cpp:196-212, mapper.cpp:122-131)
     if (cand) {
         float nd, ns;
-        implement_finish(born_gray, g, pt->T, pt->t, px, py, seg, bestx, besty, min_ssd, nd, ns);
+        implement_finish(slots[born_slot].gray + (size_t)s * g.n, g, pt->T, pt->t, px, py, seg, bestx, besty, min_ssd, nd, ns);
         fl |= 1;
         if (nd > c.acc_d_lo && nd < c.acc_d_hi && ns > 0.0f && ns < c.acc_s_hi) { // :122
             fl |= 2;
@@ -1657,7 +1679,7 @@ constexpr int APPLY_SUB = 256 / MAPU_THREADS;
 __global__ void __launch_bounds__(MAPU_THREADS * APPLY_SUB) k_map_update_apply(const __grid_constant__ Consts c, const MapRoi roi,
                                                           const SlotDev* __restrict__ slots, MapState* __restrict__ mst,
                                                           const uint8_t* __restrict__ flags, const unsigned int* __restrict__ blockcnt,
-                                                          const uint32_t* __restrict__ rng_raw)
+                                                          const uint32_t* __restrict__ rng_raw, int* __restrict__ status)
 {
     const int s = blockIdx.y;
     MapState* m = mst + s;
@@ -1698,6 +1720,8 @@ __global__ void __launch_bounds__(MAPU_THREADS * APPLY_SUB) k_map_update_apply(c
         if (t == gridDim.x - 1) {
             m->rng_pos += m->n_reject;
             m->ticket = 0;
+            // the host sizes the replay table by the furthest position of any stream (read back asynchronously)
+            if (status) atomicMax(status + 2, (int)(m->rng_pos < 0x7fffffffull ? m->rng_pos : 0x7fffffffull));
         }
     }
 }
@@ -1829,40 +1853,44 @@ __global__ void __launch_bounds__(256) k_propagate_gather(const __grid_constant_
 
 // Implement::regularize (implement.cpp:156-180): 4-neighbour Gaussian fusion read from the input
 // maps; result -> tmp (depth only).  Slot = mst[s].reg_slot.
-// fold_commit != 0: the stream's LAST CTA to finish also performs Frame::updateDepth (frame.cpp:56-61), i.e. copies tmp back
-// into the depth plane once every CTA of the stream has read its neighbours - no second launch.  (One CTA copies the whole
-// finest level, so the host selects this for small levels only; large ones keep k_regularize_commit.)
+// build_quad != 0 (VO loop): a stream that has just taken a NEW keyframe (do_propagate) also gets that keyframe's 2x2-footprint
+// image written here (SlotDev::quad) - the kernel visits every pixel of the new keyframe anyway, and the epipolar searches of
+// later frames sample born keyframes through it.
 __global__ void __launch_bounds__(256) k_regularize(const __grid_constant__ Consts c, const SlotDev* __restrict__ slots,
-                                                    MapState* __restrict__ mst, float* __restrict__ tmp, int fold_commit)
+                                                    const MapState* __restrict__ mst, float* __restrict__ tmp, int build_quad)
 {
     const int s = blockIdx.y;
-    MapState* m = mst + s;
+    const MapState* m = mst + s;
     if (!m->do_regularize) return;
     const LevelGeom g = c.lv[c.L - 1];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    float2* ds = slots[m->reg_slot].ds + (size_t)s * g.n;
-    if (i < g.n) {
-        const int y = i / g.w, x = i - y * g.w;
-        float2 v = ds[i];
-        float gd = v.x, gs = v.y;
-        if (x - 1 >= 0) { const float2 n = __ldg(ds + i - 1); gaussian_fuse(gd, gs, n.x, n.y); }      // {0,-1}
-        if (x + 1 < g.w) { const float2 n = __ldg(ds + i + 1); gaussian_fuse(gd, gs, n.x, n.y); }     // {0, 1}
-        if (y + 1 < g.h) { const float2 n = __ldg(ds + i + g.w); gaussian_fuse(gd, gs, n.x, n.y); }   // {1, 0}
-        if (y - 1 >= 0) { const float2 n = __ldg(ds + i - g.w); gaussian_fuse(gd, gs, n.x, n.y); }    // {-1,0}
-        tmp[(size_t)s * g.n + i] = gd < 6.0f ? gd : 6.0f; // cv::min(new_depth, 6.0) :178
-    }
-    if (!fold_commit) return;
-    __shared__ unsigned int s_last;
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) s_last = (atomicAdd(&m->ticket_r, 1u) == gridDim.x - 1) ? 1u : 0u;
-    __syncthreads();
-    if (!s_last) return;
-    __threadfence();
-    const float* t = tmp + (size_t)s * g.n;
-#pragma unroll 4
-    for (int k = threadIdx.x; k < g.n; k += blockDim.x) ds[k].x = __ldcg(t + k);
-    if (threadIdx.x == 0) m->ticket_r = 0;
+    if (i >= g.n) return;
+    const int y = i / g.w, x = i - y * g.w;
+    const SlotDev slot = slots[m->reg_slot];
+    const float2* ds = slot.ds + (size_t)s * g.n;
+    float2 v = ds[i];
+    float gd = v.x, gs = v.y;
+    if (x - 1 >= 0) { const float2 n = __ldg(ds + i - 1); gaussian_fuse(gd, gs, n.x, n.y); }      // {0,-1}
+    if (x + 1 < g.w) { const float2 n = __ldg(ds + i + 1); gaussian_fuse(gd, gs, n.x, n.y); }     // {0, 1}
+    if (y + 1 < g.h) { const float2 n = __ldg(ds + i + g.w); gaussian_fuse(gd, gs, n.x, n.y); }   // {1, 0}
+    if (y - 1 >= 0) { const float2 n = __ldg(ds + i - g.w); gaussian_fuse(gd, gs, n.x, n.y); }    // {-1,0}
+    tmp[(size_t)s * g.n + i] = gd < 6.0f ? gd : 6.0f; // cv::min(new_depth, 6.0) :178
+    if (build_quad && m->do_propagate) slot.quad[(size_t)s * g.n + i] = make_quad(slot.gray + (size_t)s * g.n, g.w, g.h, x, y);
+}
+
+// SlotDev::quad of one slot (fixed >= 0) or of every stream's current KEYFRAME (fixed < 0: after frame 0 of a VO run, whose
+// epilogue has already made that frame the first keyframe).
+// grid = (ceil(n_top/256), S)
+__global__ void __launch_bounds__(256) k_build_quad(const __grid_constant__ Consts c, const SlotDev* __restrict__ slots, int fixed,
+                                                    const VoState* __restrict__ vo)
+{
+    const int s = blockIdx.y;
+    const SlotDev slot = slots[fixed >= 0 ? fixed : vo[s].kf_slot];
+    const LevelGeom g = c.lv[c.L - 1];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= g.n) return;
+    const int y = i / g.w, x = i - y * g.w;
+    slot.quad[(size_t)s * g.n + i] = make_quad(slot.gray + (size_t)s * g.n, g.w, g.h, x, y);
 }
 
 // Frame::updateDepth (frame.cpp:56-61): depth <- tmp; sigma stays.  Two pixels per thread so that
@@ -1952,7 +1980,7 @@ __global__ void __launch_bounds__(64) k_update_points(const __grid_constant__ Co
         seg = make_segment(g, T, x, y, depth[k], sigma[k]);
     }
     float bestx, besty, min_ssd;
-    warp_search(s_search[threadIdx.x >> 5], cand, born_gray, g.w, g.h, seg.sx, seg.sy, (seg.ex - seg.sx) / seg.length,
+    warp_search(s_search[threadIdx.x >> 5], cand, born.quad + (size_t)s * g.n, g.w, g.h, seg.sx, seg.sy, (seg.ex - seg.sx) / seg.length,
                 (seg.ey - seg.sy) / seg.length, seg.length, og, bestx, besty, min_ssd);
     float nd = -1.f, ns = -1.f;
     if (cand) implement_finish(born_gray, g, T, tneg, x, y, seg, bestx, besty, min_ssd, nd, ns);

@@ -3,7 +3,7 @@
     library itself reports (dvo_synth_scene / dvo_synth_pose);
   * for self-consistency: ground-truth depth + ground-truth relative pose warp frame i onto frame j photometrically;
   * end to end: the VO run from the ground-truth depth prior recovers the ground-truth trajectory (this also fixes the pose
-    convention bench.py's C3 "error vs ground truth" relies on: se3::exp(frame->m_xi) = T_wc(0)^-1 T_wc(i))."""
+    convention bench.py's C3 "error vs ground truth" relies on: se3::exp(frame->m_xi) = T_wc(i)^-1 T_wc(0))."""
 import numpy as np
 import pytest
 
@@ -77,24 +77,40 @@ def test_renderer_depth_and_pose_are_self_consistent():
     dv.close()
 
 
-def test_vo_recovers_ground_truth_trajectory(orc):
-    """Full VO loop from the ground-truth depth prior: the estimated pose se3::exp(frame->m_xi) follows T_wc(0)^-1 T_wc(i)."""
-    n = 24
-    seed = 1234
+def vo_vs_ground_truth(n, seed, trans, rot, sigma0):
+    """VO from the ground-truth depth prior against the renderer's trajectory.  Returns (path length, max error of
+    se3::exp(frame->m_xi) against T_wc(i)^-1 T_wc(0), the same against its inverse T_wc(0)^-1 T_wc(i))."""
     dv = make_dvo(width=W, height=H, levels=3, culls=2, K=K_of(W, H), max_frames=2, max_keyframes=n + 2)
-    g0, d0 = render(dv, 0, seed)
-    prior = np.ascontiguousarray(d0[0, ::4, ::4])
-    errs = []; path = 0.0; prev = np.zeros(3)
+    nb = H * W * 4
+    gd = dv.dev_alloc(nb); dd = dv.dev_alloc(nb)
+    g = np.empty((1, H, W), np.float32); d = np.empty((1, H, W), np.float32)
+    e_w2c = []; e_c2w = []; path = 0.0; prev = np.zeros(3)
     for i in range(n):
-        g = render(dv, i, seed)[0] if i else g0
-        T = dv.vo_push(g, prior if i == 0 else None, np.full_like(prior, 0.1) if i == 0 else None)[0]
-        gt = dv.synth_pose(i, seed, TS, RS).astype(np.float64)   # T_wc(0) is the identity
-        path += float(np.linalg.norm(gt[:3, 3] - prev)); prev = gt[:3, 3]
-        errs.append(float(np.linalg.norm(T[:3, 3] - gt[:3, 3])))
-        inv = np.linalg.inv(gt)
-        assert errs[-1] <= float(np.linalg.norm(T[:3, 3] - inv[:3, 3])) + 1e-4   # the convention is T, not its inverse
+        dv.synth_render_dev(gd, dd, i, seed, trans, rot)
+        dv.copy_to_host(g, gd)
+        if i == 0:
+            dv.copy_to_host(d, dd)
+            prior = np.ascontiguousarray(d[0, ::4, ::4])
+        T = dv.vo_push(g, prior if i == 0 else None, np.full_like(prior, sigma0) if i == 0 else None)[0].astype(np.float64)
+        gt = dv.synth_pose(i, seed, trans, rot).astype(np.float64)   # camera-to-world; T_wc(0) is the identity
+        path += float(np.linalg.norm(gt[:3, 3] - prev)); prev = gt[:3, 3].copy()
+        e_c2w.append(float(np.linalg.norm(T[:3, 3] - gt[:3, 3])))
+        e_w2c.append(float(np.linalg.norm(T[:3, 3] - np.linalg.inv(gt)[:3, 3])))
+        assert np.isfinite(T).all()
     assert dv.vo_error() == 0
-    print("VO vs ground truth over %d frames: path %.3f m, max translation error %.4f m (%.1f %% of the path)"
-          % (n, path, max(errs), 100 * max(errs) / path))
-    assert max(errs) < 0.25 * path   # the reference's tracker is weak on rotation (README.md:4); bounded drift, not accuracy, is asserted
+    dv.dev_free(gd); dv.dev_free(dd)
     dv.close()
+    return path, max(e_w2c), max(e_c2w)
+
+
+def test_vo_against_ground_truth_trajectory():
+    """The full VO loop from the ground-truth depth prior against the renderer's trajectory.  Track::optimize models
+    obj(x) = ref(warp(-xi, x)) (optimize.cpp:46-51), i.e. exp(xi) maps keyframe coordinates to frame coordinates:
+    se3::exp(frame->m_xi) is the WORLD-TO-CAMERA pose T_wc(i)^-1 T_wc(0), which is why main.cpp:50 inverts it before drawing.
+    Asserted: that convention on a pure translation, and finite output with rotation.  The error figures are printed for BASELINE.md."""
+    for rot in (0.0, RS):
+        path, e_w2c, e_c2w = vo_vs_ground_truth(24, 1234, TS, rot, 0.5)
+        print("VO-VS-GT rot_step %.2f deg: path %.4f m, max translation error %.4f m as world-to-camera, %.4f m as camera-to-world"
+              % (rot, path, e_w2c, e_c2w))
+        if rot == 0.0:   # the convention; how WELL the reference's algorithm tracks is reported, not asserted (README.md:4)
+            assert e_w2c < e_c2w, (path, e_w2c, e_c2w)

@@ -79,19 +79,26 @@ def _run_pair(orc, g, K, d0, s0, levels=3, culls=2, n_streams=1, forced=True, up
             sched_o = [(a["level"], a["iteration"], a["valid_pixels"]) for a in o_log]
             if forced:
                 assert sched_g == sched_o, "frame %d: GN schedule / valid counts differ" % i
+                xb_gpu = np.zeros(6, np.float32)   # the GPU tracker's own pose before each iteration (tracker.cpp:28: xi = 0 at the start)
                 for a, b in zip(logs[s], o_log):
                     e = se3_norm(a["update"], b["update"])
                     if e > upd_tol and snap is not None:
-                        # The reference solves the stacked N x 6 system with an fp32 SVD (cv::solve(DECOMP_SVD), optimize.cpp:97); at
-                        # 10^5 - 10^6 rows its own rounding noise exceeds 1e-5.  Decide against the exact solution of ITS system:
-                        # the GPU (fp64 normal equations) must be within tolerance of it, and closer to it than the reference is.
-                        x64 = exact_update(orc, snap, vo.last_frame(), b["level"], b["xi_before"], P_orc)
-                        eg, er = se3_norm(a["update"], x64), se3_norm(b["update"], x64)
+                        # Within a frame both trackers run freely, so the pose an iteration starts from already differs by the
+                        # sum of the earlier (<= 1e-5) differences, and a Gauss-Newton update moves by as much as its starting
+                        # pose does.  At 10^5 - 10^6 rows per system that accumulated difference can pass 1e-5 although each side
+                        # solves ITS OWN system accurately.  Show exactly that: the fp64 least-squares solution of the reference's
+                        # stacked system (optimize.cpp:87-97) built at the GPU's own pose is what the GPU returns, and the one
+                        # built at the reference's pose is what the reference's fp32 SVD returns, both within 1e-5.
+                        xg64 = exact_update(orc, snap, vo.last_frame(), b["level"], xb_gpu, P_orc)
+                        xo64 = exact_update(orc, snap, vo.last_frame(), b["level"], b["xi_before"], P_orc)
+                        eg, er = se3_norm(a["update"], xg64), se3_norm(b["update"], xo64)
                         n_exact[0] += 1; n_exact[1] = max(n_exact[1], eg); n_exact[2] = max(n_exact[2], er)
-                        assert eg <= upd_tol and eg <= er, (i, b["level"], b["iteration"], eg, er)
+                        assert eg <= upd_tol and er <= upd_tol, (i, b["level"], b["iteration"], e, eg, er)
+                        assert e <= 10 * upd_tol + 2 * se3_norm(xb_gpu, b["xi_before"]), (i, e)
                     else:
                         assert e <= upd_tol, (i, a, b)
                     assert se3_norm(a["xi_after"], b["xi_after"]) <= POSE_TOL
+                    xb_gpu = a["xi_after"]
             ok &= sched_g == sched_o and se3_norm(st["rel_xi"][s], o_rel) <= POSE_TOL
             if not ok and not forced:
                 break
@@ -129,8 +136,9 @@ def _run_pair(orc, g, K, d0, s0, levels=3, culls=2, n_streams=1, forced=True, up
                         assert _close(a, b), "frame %d level %d %s" % (i, l, kind)
             assert dv.frame_download(ks, top, "age")[s].tobytes() == kf.image(top, "age").tobytes(), "frame %d age" % i
     if n_exact[0]:
-        print("%d iterations beyond %g of the reference's fp32 SVD result were decided against the fp64 solution of its system: "
-              "|gpu - exact| <= %.3g, |reference - exact| <= %.3g" % (n_exact[0], upd_tol, n_exact[1], n_exact[2]))
+        print("%d iterations differed by more than %g between the two free-running trackers; against the fp64 solution of the "
+              "reference's stacked system at each side's own pose: |gpu - exact| <= %.3g, |reference - exact| <= %.3g"
+              % (n_exact[0], upd_tol, n_exact[1], n_exact[2]))
     if n_ulp[0]:
         print("maps not bit-identical (<= %g relative) in %d level-maps" % (FORCED_TOL, n_ulp[0]))
     dv.close()
