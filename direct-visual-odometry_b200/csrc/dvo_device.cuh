@@ -115,26 +115,6 @@ __device__ __forceinline__ float subpixel_quad(const float4* __restrict__ quad, 
     const float4 q = __ldg(quad + (y0 * w + x0));
     return bilerp(q.x, q.y, q.z, q.w, hh, v);
 }
-// The same tap split in two: the 16-byte load is issued early (one search step ahead), the arithmetic happens when it is needed.
-// In the steady state of a long sequence the born keyframes of a stream no longer fit any cache (hundreds of keyframes per
-// stream): a tap is a DRAM access and the search is bound by how many of them are in flight, not by instruction issue.
-struct QuadTap {
-    float4 q;
-    float hh, v;
-    bool in;
-};
-__device__ __forceinline__ QuadTap quad_tap_issue(const float4* __restrict__ quad, int w, float wf, float hf, float px, float py)
-{
-    QuadTap t;
-    t.in = (px > -1.0f && px < wf && py > -1.0f && py < hf);
-    const float qx = t.in ? px : 0.0f, qy = t.in ? py : 0.0f;
-    const int x0 = __float2int_rz(qx), y0 = __float2int_rz(qy);
-    t.hh = qx - (float)x0; t.v = qy - (float)y0;
-    t.q = __ldg(quad + (y0 * w + x0));
-    return t;
-}
-__device__ __forceinline__ float quad_tap_value(const QuadTap& t) { return t.in ? bilerp(t.q.x, t.q.y, t.q.z, t.q.w, t.hh, t.v) : DVO_INV; }
-
 __device__ __forceinline__ float4 make_quad(const float* __restrict__ img, int w, int h, int x, int y)
 {
     const float* p = img + (size_t)y * w + x;

@@ -1236,9 +1236,6 @@ struct SearchSmem { // per warp
 };
 
 #define SEARCH_TAP(img, w, h, wf, hf, x, y) subpixel_quad(img, w, wf, hf, x, y)
-#ifndef DVO_SEARCH_PREFETCH
-#define DVO_SEARCH_PREFETCH 0
-#endif
 __device__ __forceinline__ float search_ssd(float s0, float s1, float s2, float og)
 {
     // implement.cpp:122-139: a tap that is invalid ends the accumulation with ssd = 2.0 * 3
@@ -1353,26 +1350,6 @@ __device__ __forceinline__ void warp_search(SearchSmem& sm, bool active, const f
             pty += dy;
             float c_cur = SEARCH_TAP(img, w, h, wf, hf, ptx + dx * 0.0f, pty + dy * 0.0f); // tap at pt (k = 1)
             unsigned long long kbest = ~0ull;
-#if DVO_SEARCH_PREFETCH
-            // the tap of step k (at pt + dir = the next step's pt) is loaded one step ahead; positions are accumulated exactly as the
-            // serial walk does (pt += dir), so they are bit-identical
-            QuadTap pend = quad_tap_issue(img, w, wf, hf, ptx + dx * 1.0f, pty + dy * 1.0f);
-#pragma unroll(SEARCH_UNROLL)
-            for (int k = 1; k <= cnt; k++) {
-                const QuadTap cur = pend;
-                const float nx = ptx + dx, ny = pty + dy;                         // pt of step k + 1
-                if (k < cnt) pend = quad_tap_issue(img, w, wf, hf, nx + dx * 1.0f, ny + dy * 1.0f);
-                const float s2 = quad_tap_value(cur);
-                const float bx = ptx + dx * -1.0f, by = pty + dy * -1.0f;
-                const float s0 = (bx == prevx && by == prevy) ? c_prev : SEARCH_TAP(img, w, h, wf, hf, bx, by);
-                const unsigned long long key = ((unsigned long long)__float_as_uint(search_ssd(s0, c_cur, s2, ogp)) << 32) | (unsigned)(b0 + k);
-                if (key < kbest) kbest = key;
-                c_prev = c_cur; c_cur = s2;
-                prevx = ptx; prevy = pty;
-                ptx = nx;
-                pty = ny;
-            }
-#else
 #pragma unroll(SEARCH_UNROLL)
             for (int k = 1; k <= cnt; k++) {
                 const float s2 = SEARCH_TAP(img, w, h, wf, hf, ptx + dx * 1.0f, pty + dy * 1.0f);
@@ -1385,7 +1362,6 @@ __device__ __forceinline__ void warp_search(SearchSmem& sm, bool active, const f
                 ptx += dx;
                 pty += dy;
             }
-#endif
             // lanes [hp, rend) form this lane's run: smallest ssd of the run, at its earliest step
             const unsigned above = (hp == 31) ? 0u : (heads >> (hp + 1)) << (hp + 1);
             const int end = above ? __ffs(above) - 1 : 32;

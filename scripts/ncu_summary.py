@@ -65,7 +65,9 @@ def traffic(path):
             continue
         rd = float(r[idx["dram__bytes_read.sum"]]) * scale[unit[idx["dram__bytes_read.sum"]]]
         wr = float(r[idx["dram__bytes_write.sum"]]) * scale[unit[idx["dram__bytes_write.sum"]]]
-        res[k] = dict(dram_bytes=rd + wr, dram_read=rd, dram_write=wr, duration_us=float(r[idx["gpu__time_duration.sum"]]))
+        tscale = {"ns": 1e-3, "us": 1.0, "usecond": 1.0, "ms": 1e3, "msecond": 1e3, "s": 1e6, "second": 1e6, "nsecond": 1e-3}
+        res[k] = dict(dram_bytes=rd + wr, dram_read=rd, dram_write=wr,
+                      duration_us=float(r[idx["gpu__time_duration.sum"]]) * tscale.get(unit[idx["gpu__time_duration.sum"]], 1.0))
         # the other levels of the hierarchy (BASELINE.json: "% HBM/L2 roofline"): L2 traffic (32 B sectors) and ncu's own
         # percent-of-peak figures for L2, L1/TEX and the SM
         for key, col, mul in (("lts_bytes", "lts__t_sectors.sum", 32.0), ("lts_pct_of_peak", "lts__throughput.avg.pct_of_peak_sustained_elapsed", 1.0),
