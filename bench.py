@@ -497,7 +497,7 @@ def run_other_configs(lib):
         roi = dict(roi_x0=20 * sc, roi_x1=140 * sc, roi_y0=20 * sc, roi_y1=100 * sc,
                    map_roi_x0=16 * sc, map_roi_x1=144 * sc, map_roi_y0=12 * sc, map_roi_y1=108 * sc)
         dv = dvo_b200.Dvo(lib=lib, n_streams=1, width=W, height=H, levels=3, culls=culls, K=Kf(W, H), max_frames=2,
-                          max_keyframes=n_frames + 8, **roi)
+                          max_keyframes=n_frames + 8, rng_table=(1 << 24) if culls else (1 << 28), **roi)   # grows on demand otherwise: not while timing
         dv.vo_reserve(n_frames + 4)
         fb = W * H * 4
         dev = dv.dev_alloc(fb * n_res); dd = dv.dev_alloc(fb)
@@ -542,7 +542,7 @@ def run_other_configs(lib):
     # ---- C4
     W, H = 3840, 2160
     roi = dict(map_roi_x0=0, map_roi_x1=W - 1, map_roi_y0=0, map_roi_y1=H - 1)
-    dv = dvo_b200.Dvo(lib=lib, n_streams=1, width=W, height=H, levels=1, culls=0, K=Kf(W, H), max_frames=3, **roi)
+    dv = dvo_b200.Dvo(lib=lib, n_streams=1, width=W, height=H, levels=1, culls=0, K=Kf(W, H), max_frames=3, rng_table=1 << 26, **roi)
     fb = W * H * 4
     gd = dv.dev_alloc(fb)
     g = np.empty((2, 1, H, W), np.float32)

@@ -1160,8 +1160,9 @@ static int rng_reserve(dvo_ctx* ctx, uint64_t need)
 {
     Consts& c = ctx->c;
     if (need <= (uint64_t)c.rng_table) return DVO_OK;
-    uint64_t len = (uint64_t)c.rng_table * 2;
+    uint64_t len = (uint64_t)c.rng_table * 4; // growing costs a device synchronisation: in big steps
     while (len < need) len *= 2;
+    if (len > 0xffffffffull && need <= 0xffffffffull) len = 0xffffffffull;
     if (len > 0xffffffffull) {
         ctx->err = "mt19937 replay table would exceed 2^32 draws";
         return DVO_ERR_RNG;
@@ -1192,6 +1193,7 @@ static int enqueue_update(dvo_ctx* ctx, bool tables, bool overlapped)
     }
     if (ctx->roi.n <= 0) return DVO_OK;
     dim3 grid(ctx->roi.nblk, c.S);
+    const int fold = ctx->roi.nblk <= 4096 ? 1 : 0; // the stream's last phase-A CTA scans the reject counts itself
     {
         KTimer t(ctx, K_MAP_UPDATE);
         if (overlapped) {
@@ -1202,16 +1204,20 @@ static int enqueue_update(dvo_ctx* ctx, bool tables, bool overlapped)
             at[0].val.programmaticStreamSerializationAllowed = 1;
             cfg.attrs = at; cfg.numAttrs = 1;
             CK(cudaLaunchKernelEx(&cfg, k_map_update, c, ctx->roi, (const SlotDev*)ctx->d_slots, ctx->d_ms, (const int*)ctx->d_hist,
-                                  (const PoseTab*)ctx->d_tab, ctx->d_flags, ctx->d_blockcnt, ctx->d_rq, ctx->d_status));
+                                  (const PoseTab*)ctx->d_tab, ctx->d_flags, ctx->d_blockcnt, ctx->d_rq, ctx->d_status, fold));
             ctx->launches++;
         } else {
             k_map_update<<<grid, MAPU_THREADS, 0, ctx->stream>>>(c, ctx->roi, ctx->d_slots, ctx->d_ms, ctx->d_hist, ctx->d_tab, ctx->d_flags,
-                                                                ctx->d_blockcnt, nullptr, ctx->d_status);
+                                                                ctx->d_blockcnt, nullptr, ctx->d_status, fold);
             KCHECK();
         }
     }
     {
         KTimer t(ctx, K_MAP_APPLY);
+        if (!fold) {
+            k_map_scan<<<c.S, 1024, 0, ctx->stream>>>(c, ctx->roi, ctx->d_ms, ctx->d_blockcnt);
+            KCHECK();
+        }
         dim3 agrid(cdiv(ctx->roi.nblk, APPLY_SUB), c.S);
         k_map_update_apply<<<agrid, MAPU_THREADS * APPLY_SUB, 0, ctx->stream>>>(c, ctx->roi, ctx->d_slots, ctx->d_ms, ctx->d_flags,
                                                                                  ctx->d_blockcnt, ctx->d_rng, ctx->d_status);

@@ -1505,7 +1505,7 @@ struct MapRoi {
 __global__ void __launch_bounds__(MAPU_THREADS, DVO_MAPU_MINB) k_map_update(const __grid_constant__ Consts c, const MapRoi roi, const SlotDev* __restrict__ slots,
                                                        MapState* __restrict__ mst, const int* __restrict__ hist,
                                                        const PoseTab* __restrict__ tab, uint8_t* __restrict__ flags,
-                                                       unsigned int* __restrict__ blockcnt, ReadyQ* rq, int* status)
+                                                       unsigned int* __restrict__ blockcnt, ReadyQ* rq, int* status, int fold_scan)
 {
     __shared__ SearchSmem s_search[MAPU_THREADS / 32];
     __shared__ int s_sel[2];
@@ -1622,6 +1622,13 @@ __global__ void __launch_bounds__(MAPU_THREADS, DVO_MAPU_MINB) k_map_update(cons
     // and their total - no separate scan launch, and nothing quadratic in the CTA count (129 600 CTAs at 3840x2160).
     unsigned int* bc = blockcnt + (size_t)s * roi.nblk;
     __shared__ unsigned int s_last;
+    if (!fold_scan) { // large grids (1080p, 4K single streams): k_map_scan does it with a thousand threads
+        if (threadIdx.x == 0) {
+            bc[tile] = (unsigned)nrej;
+            if (nval) atomicAdd(&m->valid_update, nval);
+        }
+        return;
+    }
     if (threadIdx.x == 0) {
         bc[tile] = (unsigned)nrej;
         if (nval) atomicAdd(&m->valid_update, nval);
@@ -1646,6 +1653,44 @@ __global__ void __launch_bounds__(MAPU_THREADS, DVO_MAPU_MINB) k_map_update(cons
         off += v;
     }
     if (threadIdx.x == MAPU_THREADS - 1) { m->n_reject = off; m->ticket_a = 0; }
+}
+
+// The scan of the per-CTA reject counts as a kernel of its own, for grids too large for one 64-thread CTA to scan in passing
+// (27 000 CTAs at 1920x1080, 129 600 at 3840x2160).  grid = S, 1024 threads.
+__global__ void __launch_bounds__(1024) k_map_scan(const __grid_constant__ Consts c, const MapRoi roi, MapState* __restrict__ mst,
+                                                   unsigned int* __restrict__ blockcnt)
+{
+    const int s = blockIdx.x;
+    MapState* m = mst + s;
+    if (!m->do_update) return;
+    unsigned int* bc = blockcnt + (size_t)s * roi.nblk;
+    const int per = (roi.nblk + 1023) / 1024;
+    const int b0 = threadIdx.x * per, b1 = min(roi.nblk, b0 + per);
+    unsigned int sum = 0;
+#pragma unroll 8
+    for (int b = b0; b < b1; b++) sum += bc[b];
+    // exclusive scan of the 1024 partial sums: warp scans + a scan of the 32 warp totals
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned int incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const unsigned int v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
+    __shared__ unsigned int s_warp[32];
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        unsigned int w = s_warp[lane];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const unsigned int v = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += v; }
+        s_warp[lane] = w; // inclusive
+    }
+    __syncthreads();
+    unsigned int off = (incl - sum) + (warp ? s_warp[warp - 1] : 0u);
+    for (int b = b0; b < b1; b++) {
+        const unsigned int v = bc[b];
+        bc[b] = off;
+        off += v;
+    }
+    if (threadIdx.x == 1023) m->n_reject = s_warp[31];
 }
 
 // Mapper::update phase B: replay of the mt19937 stream for the rejected pixels in row-major order.

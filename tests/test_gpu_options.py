@@ -183,3 +183,4 @@ def test_vo_is_schedule_independent_and_repeatable():
     kf_same = sum(M4[s][2].tobytes() == M0[s][2].tobytes() for s in range(4))
     print("SCHEDULES: 48 streams x %d frames bit-identical across repeat / overlap / fused-propagate settings; 4-stream split-CTA run: "
           "max pose difference %.3g, age maps identical in %d of 4 streams" % (n, float(np.abs(T4 - T0[:, :4]).max()), kf_same))
+
