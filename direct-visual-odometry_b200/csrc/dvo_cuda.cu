@@ -1588,7 +1588,19 @@ static int vo_push_impl(dvo_ctx* ctx, const float* gray_dev, const float* init_d
         // before the launches (Mapper::update must follow the tracking kernel back to back): every frame since the last read-back
         // can have consumed at most roi.n draws per stream
         const uint64_t per = (uint64_t)(ctx->roi.n > 0 ? ctx->roi.n : 0);
-        const uint64_t bound = ctx->rng_known + per * (uint64_t)(frame_id - ctx->kf_known_frame);
+        uint64_t bound = ctx->rng_known + per * (uint64_t)(frame_id - ctx->kf_known_frame);
+        if (bound > (uint64_t)c.rng_table && ctx->kf_known_frame < frame_id - 1) {
+            // The bound is pessimistic by roi.n draws for every frame the host has run ahead of the last read-back (a caller that
+            // never reads poses enqueues hundreds of frames).  Before paying for a bigger table, wait for the device and read the
+            // actual position: one drain of the stream instead of a host-side mt19937 run of 10^8..10^9 draws.
+            int now[2] = {0, 0};
+            CK(cudaStreamSynchronize(ctx->stream));
+            CK(cudaMemcpy(now, ctx->d_status + 1, sizeof(int) * 2, cudaMemcpyDeviceToHost));
+            ctx->kf_known = now[0]; ctx->rng_known = (uint64_t)(unsigned)now[1];
+            ctx->kf_known_frame = frame_id - 1;
+            ctx->kf_rb_pending[0] = ctx->kf_rb_pending[1] = false; // both have landed; they are older than what was just read
+            bound = ctx->rng_known + per;
+        }
         if (bound > ctx->rng_bound) ctx->rng_bound = bound; // dvo_map_update on the same context continues from here
         rc = rng_reserve(ctx, bound);
         if (rc) return rc;

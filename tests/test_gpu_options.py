@@ -114,6 +114,35 @@ def test_rng_table_grows_on_demand(orc):
     assert n_upd >= 4
 
 
+def test_rng_bound_of_a_caller_that_runs_ahead(orc):
+    """A caller that never reads poses enqueues all frames at once: the replay-table bound then grows by roi.n per frame in flight.
+    Before growing the table the library drains the stream and reads the actual position - same poses and same replay position as
+    a frame-by-frame run with a table that never needs to grow, and the table stays small."""
+    from dvo_b200 import synth
+    n = 40
+    g, d, poses, K = synth.sequence(n, 640, 480, seed=5, trans_step=0.01, rot_step_deg=0.2)
+    d0 = orc.cull_image(d[0], 2)
+    s0 = np.full_like(d0, 0.4)
+    out = []
+    for table, ahead in ((1 << 22, False), (1 << 16, True)):   # roi.n = 128 x 96 = 12288 draws per frame in flight: 2^16 = 5 frames
+        dv = make_dvo(width=640, height=480, levels=3, culls=2, K=K, max_frames=2, max_keyframes=n + 2, accept_sigma_hi=5.0,
+                      min_movement=0.05, rng_table=table)
+        dev = dv.dev_alloc(g[0].nbytes * n)
+        for i in range(n):
+            dv.copy_to_dev(dev + i * g[0].nbytes, g[i])
+        T = None
+        for i in range(n):
+            T = dv.vo_push_dev(dev + i * g[0].nbytes, d0 if i == 0 else None, s0 if i == 0 else None, want_pose=(not ahead) or i == n - 1)
+        out.append((T.copy(), dv.rng_position().copy(), dv.vo_counters()["n_update"].copy()))
+        assert dv.vo_error() == 0
+        dv.dev_free(dev)
+        dv.close()
+    assert out[0][2].sum() >= 20 and out[0][1].max() > 0        # updates happened and consumed draws
+    assert np.array_equal(out[0][0], out[1][0]) and np.array_equal(out[0][1], out[1][1])
+    print("RNG-RUN-AHEAD: %d frames enqueued without a read-back, %d update frames, furthest replay position %d (table 65536, pessimistic "
+          "bound %d)" % (n, int(out[1][2].sum()), int(out[1][1].max()), 12288 * n))
+
+
 def test_history_overflow_is_reported(orc):
     import dvo_b200
     from dvo_b200 import synth
