@@ -62,6 +62,7 @@ struct dvo_ctx {
     ReadyQ* d_rq = nullptr;        // tracking -> Mapper::update hand-over of one frame
     int* d_status = nullptr;       // first device-side error of any stream
     int* h_status = nullptr;       // pinned: [0], [1] = status read back with pipeline buffer k's poses; [2] = synchronous pushes
+    unsigned int* d_noalloc = nullptr; // device address of g_noalloc_counts on this context's device (dvo_mask_compact_noalloc)
     bool overlap = true;           // k_map_update as a programmatic dependent of k_track (DVO_OVERLAP=0 disables)
     bool fuse_prop = true;         // Implement::propagate in k_track's epilogue (DVO_FUSE_PROP=0: the two wide kernels)
     // keyframe-pool growth: max over streams of the keyframe count, read back asynchronously (d_status[1])
@@ -99,6 +100,10 @@ struct dvo_ctx {
     int vo_frame_id = -1;
     std::mt19937 engine; // default seed 5489, src/math/gaussian.cpp:8
 };
+
+// Scratch of dvo_mask_compact_noalloc: one count per 256-byte tile of the mask.  Host code never passes this name to a kernel (there it
+// is a host-side handle, not a device address): dvo_create resolves the address per device with cudaGetSymbolAddress.
+static __device__ __align__(256) unsigned int g_noalloc_counts[DVO_NOALLOC_MAX_N / 256];
 
 #define CK(call)                                                                                   \
     do {                                                                                           \
@@ -194,6 +199,9 @@ extern "C" int dvo_create(dvo_ctx** out, const dvo_params* p)
         return DVO_ERR_CUDA;
     }
     CK(cudaGetDevice(&ctx->device));
+    // dvo_mask_compact_noalloc's scratch: in host code `g_noalloc_counts` is only a handle, the array's address on THIS device (the
+    // current one) comes from the runtime.  Once per context = once per device the caller works on; allocates nothing.
+    CK(cudaGetSymbolAddress((void**)&ctx->d_noalloc, g_noalloc_counts));
     ARG(p->n_streams >= 1 && p->width > 0 && p->height > 0, "bad geometry");
     ARG(p->levels >= 1 && p->levels <= MAXL && p->culls >= 0 && p->culls < 16, "bad levels/culls");
     ARG(p->max_frames >= 2 && p->max_keyframes >= 1, "bad capacities");
@@ -1448,6 +1456,34 @@ extern "C" int dvo_mask_compact(dvo_ctx* ctx, const uint8_t* mask, int n, int32_
     if (total) CK(cudaMemcpy(idx, i.p, sizeof(int32_t) * (size_t)total, cudaMemcpyDeviceToHost));
     *count = total;
     return DVO_OK;
+}
+
+// The same compaction for callers that may not allocate (code under CUDA graph capture, serving loops, harnesses that forbid
+// cudaMalloc): mask, idx and count are DEVICE buffers of the caller, and the per-CTA counts - the one piece of scratch the three
+// kernels share - live in a file-scope device array instead of a cudaMalloc'ed buffer.  Every GPU that loads the library holds
+// these 128 KiB until exit.  Nothing in the array has to start at zero: k_compact_count overwrites every count a call reads, so the
+// previous call's contents (which stay there) are harmless.  All calls share the array: two calls that overlap on the GPU (different
+// contexts or streams on one device) race; calls on one context are ordered by its stream.
+extern "C" int dvo_mask_compact_noalloc(dvo_ctx* ctx, const uint8_t* mask_dev, int n, int32_t* idx_dev, int* count_dev)
+{
+    ARG(mask_dev && idx_dev && count_dev && n > 0, "bad argument");
+    if (n > DVO_NOALLOC_MAX_N) {
+        ctx->err = "dvo_mask_compact_noalloc: n = " + std::to_string(n) + " exceeds DVO_NOALLOC_MAX_N = " + std::to_string(DVO_NOALLOC_MAX_N) +
+                   " (the static scratch holds one count per 256 mask bytes); use dvo_mask_compact";
+        return DVO_ERR_ARG;
+    }
+    if (!ctx->d_noalloc) {
+        ctx->err = "dvo_mask_compact_noalloc: the scratch array's device address was not resolved (dvo_create failed early)";
+        return DVO_ERR_STATE;
+    }
+    const int nb = cdiv(n, 256);
+    k_compact_count<<<dim3(nb, 1), 256, 0, ctx->stream>>>(mask_dev, n, ctx->d_noalloc);
+    KCHECK();
+    k_compact_scan<<<1, 256, 0, ctx->stream>>>(nb, ctx->d_noalloc, count_dev);
+    KCHECK();
+    k_compact_scatter<<<dim3(nb, 1), 256, 0, ctx->stream>>>(mask_dev, n, ctx->d_noalloc, idx_dev);
+    KCHECK();
+    return DVO_OK; // asynchronous on the context's stream: dvo_sync (or any synchronising call) before the results are read
 }
 
 extern "C" int dvo_select_pixels(dvo_ctx* ctx, int slot, int level, float min_gradient, int32_t* idx, int* count)

@@ -48,7 +48,7 @@ EXPORTS = [
     "dvo_host_alloc", "dvo_host_free", "dvo_frame_create", "dvo_frame_create_dev", "dvo_frame_release",
     "dvo_frame_set_depth", "dvo_frame_download", "dvo_visualize", "dvo_visualize_image", "dvo_inverse_pose", "dvo_write_trajectory_csv", "dvo_write_png", "dvo_frame_set_xi", "dvo_frame_get_xi", "dvo_warp_image",
     "dvo_gn_step", "dvo_track", "dvo_map_propagate", "dvo_map_update", "dvo_map_regularize", "dvo_rng_position",
-    "dvo_mask_compact", "dvo_vo_reset", "dvo_vo_reserve", "dvo_vo_force_pose", "dvo_vo_push", "dvo_vo_push_dev", "dvo_vo_state", "dvo_vo_ref_slot",
+    "dvo_mask_compact", "dvo_mask_compact_noalloc", "dvo_vo_reset", "dvo_vo_reserve", "dvo_vo_force_pose", "dvo_vo_push", "dvo_vo_push_dev", "dvo_vo_state", "dvo_vo_ref_slot",
     "dvo_vo_last_slot", "dvo_vo_last_log", "dvo_vo_counters", "dvo_vo_matched", "dvo_vo_error", "dvo_synth_render_dev", "dvo_dev_alloc", "dvo_dev_free",
     "dvo_copy_to_host", "dvo_copy_to_dev", "dvo_timer_start", "dvo_timer_stop", "dvo_launch_count", "dvo_gn_timing", "dvo_kernel_timing",
     "dvo_map_update_points", "dvo_se3_exp", "dvo_se3_log", "dvo_se3_concatenate", "dvo_vo_submit", "dvo_vo_collect",
@@ -104,6 +104,7 @@ def load_library(path=None):
     lib.dvo_map_regularize.argtypes = [C.c_void_p, C.c_int]
     lib.dvo_rng_position.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
     lib.dvo_mask_compact.argtypes = [C.c_void_p, U8P, C.c_int, I32P, I32P]
+    lib.dvo_mask_compact_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
     lib.dvo_vo_reset.argtypes = [C.c_void_p]
     lib.dvo_vo_reserve.argtypes = [C.c_void_p, C.c_int]
     lib.dvo_vo_push.argtypes = [C.c_void_p, C.c_void_p, F32P, F32P, F32P]
@@ -465,6 +466,10 @@ class Dvo:
         idx = np.empty(m.size, np.int32); cnt = C.c_int(0)
         self._ck(self.lib.dvo_mask_compact(self.ctx, m.ctypes.data_as(U8P), m.size, idx.ctypes.data_as(I32P), C.byref(cnt)))
         return idx[:cnt.value].copy()
+
+    def mask_compact_noalloc(self, mask_dev, n, idx_dev, count_dev):
+        """dvo_mask_compact_noalloc: device pointers in and out, no allocation inside; asynchronous (call sync())."""
+        self._ck(self.lib.dvo_mask_compact_noalloc(self.ctx, mask_dev, n, idx_dev, count_dev))
 
     def select_pixels(self, slot, level, min_gradient):
         """Semi-dense selection by gradient threshold, compacted on the device: list of index arrays, one per stream."""

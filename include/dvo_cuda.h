@@ -249,6 +249,17 @@ int dvo_map_depth_to_gray(const float* depth, int w, int h, const float* gray, i
 /* Row-major compaction of a byte mask on device: idx receives the linear indices of non-zero
  * entries in increasing order; returns their number in *count. */
 int dvo_mask_compact(dvo_ctx* ctx, const uint8_t* mask, int n, int32_t* idx, int* count);
+/* dvo_mask_compact for callers that may not allocate device memory (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * mask_dev ([n] bytes), idx_dev ([n] int32) and count_dev ([1] int) are DEVICE buffers of the caller (e.g. from dvo_dev_alloc, made
+ * once, outside the loop); the result is the same as dvo_mask_compact's: idx_dev[0 .. *count_dev) = the linear indices of the
+ * non-zero mask bytes in increasing order (entries past the count are left untouched).  The call allocates and frees nothing: its
+ * scratch (one count per 256 mask bytes) is a static device array of DVO_NOALLOC_MAX_N / 256 * 4 = 128 KiB that every GPU
+ * loading the library holds until exit; n > DVO_NOALLOC_MAX_N is DVO_ERR_ARG.  The kernels are enqueued on the context's stream
+ * and the call returns without waiting: dvo_sync before reading the outputs.  ALL calls on a device share the scratch array: calls
+ * on one context are ordered by its stream; calls from different contexts of the same device that overlap on the GPU race. */
+#define DVO_NOALLOC_MAX_N (1 << 23) /* 8 388 608 mask bytes: one 3840x2160 level */
+int dvo_mask_compact_noalloc(dvo_ctx* ctx, const uint8_t* mask_dev, int n, int32_t* idx_dev, int* count_dev);
 /* Semi-dense pixel selection of one pyramid level of a frame by gradient threshold (north_star; no reference counterpart), selected
  * and compacted on the device: pixel (x, y) is kept iff its gray, Convert::gradiate x and y values are all valid and
  * gx^2 + gy^2 >= min_gradient^2.  idx ([n_streams][w_l h_l], row-major linear indices in increasing order, the first count[s]
