@@ -279,7 +279,8 @@ extern "C" int dvo_create(dvo_ctx** out, const dvo_params* p)
     // stream's pixels are split over B co-resident CTAs (cooperative launch, global barrier).
     {
         int per_sm = 0, n_sm = 0;
-        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_track, TRK_THREADS, 0));
+        // the split form runs k_track_staged (coarse reference levels in shared memory): its occupancy bounds the co-resident grid
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_track_staged, TRK_THREADS, 0));
         CK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, ctx->device));
         ctx->trk_capacity = per_sm * n_sm;
         int coop = 0;
@@ -977,7 +978,7 @@ static int launch_track(dvo_ctx* ctx, TrackArgs a)
     if (ctx->trk_B > 1) { // CTAs of a stream meet at a global barrier: they must be co-resident
         Consts cc = c;
         void* params[] = {(void*)&cc, (void*)&a};
-        CK(cudaLaunchCooperativeKernel((const void*)k_track, grid, dim3(TRK_THREADS), params, 0, ctx->stream));
+        CK(cudaLaunchCooperativeKernel((const void*)k_track_staged, grid, dim3(TRK_THREADS), params, 0, ctx->stream));
         ctx->launches++;
     } else {
         k_track<<<grid, TRK_THREADS, 0, ctx->stream>>>(c, a);

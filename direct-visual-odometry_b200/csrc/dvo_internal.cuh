@@ -19,6 +19,7 @@ constexpr int MAXL = DVO_MAX_LEVELS;
 #define DVO_TRK_THREADS 512
 #endif
 constexpr int TRK_THREADS = DVO_TRK_THREADS;   // threads per tracking CTA
+constexpr int TRK_STAGE_PIXELS = 80 * 60; // k_track_staged: reference levels up to 80x60 (19.2 KB) as a shared-memory tile
 constexpr int TRK_MINB = 1024 / TRK_THREADS;   // <= 64 registers per thread: 1024 tracking threads per SM
 constexpr int NACC = 29;         // 21 J^T J + 6 J^T (w r) + sum r^2 + valid count
 

@@ -446,7 +446,9 @@ struct Sample3 {
     float I, gx, gy;
     bool in; // (x0, y0) in range
 };
-template <bool WANT_GRAD>
+template <bool SMEM>
+__device__ __forceinline__ float tap_ld(const float* p) { return SMEM ? *p : __ldg(p); }
+template <bool WANT_GRAD, bool SMEM = false>
 __device__ __forceinline__ Sample3 sample_level(const float* __restrict__ gray, const LevelView& lv, float px, float py)
 {
     Sample3 r;
@@ -460,34 +462,34 @@ __device__ __forceinline__ Sample3 sample_level(const float* __restrict__ gray, 
     const float* p = gray + top_index(lv, x0, y0);
     const int dx = 1 << lv.t;
     const ptrdiff_t dy = (ptrdiff_t)lv.W << lv.t;
-    const float b0 = level_value(lv, __ldg(p));
-    const float b1 = xin ? level_value(lv, __ldg(p + dx)) : b0;
-    const float c0 = yin ? level_value(lv, __ldg(p + dy)) : b0;
-    const float c1 = (xin && yin) ? level_value(lv, __ldg(p + dy + dx)) : b0;
+    const float b0 = level_value(lv, tap_ld<SMEM>(p));
+    const float b1 = xin ? level_value(lv, tap_ld<SMEM>(p + dx)) : b0;
+    const float c0 = yin ? level_value(lv, tap_ld<SMEM>(p + dy)) : b0;
+    const float c1 = (xin && yin) ? level_value(lv, tap_ld<SMEM>(p + dy + dx)) : b0;
     if (WANT_GRAD) {
         // gradient of a footprint pixel: INVALID on the image border or next to an invalid tap
         const bool xl = x0 - 1 >= 0, xr = x0 + 2 < w, yu = y0 - 1 >= 0, yd = y0 + 2 < h;
-        const float bm = xl ? __ldg(p - dx) : DVO_INV;
-        const float b2 = xr ? __ldg(p + 2 * dx) : DVO_INV;
-        const float a0 = yu ? __ldg(p - dy) : DVO_INV;
-        const float d0 = yd ? __ldg(p + 2 * dy) : DVO_INV;
+        const float bm = xl ? tap_ld<SMEM>(p - dx) : DVO_INV;
+        const float b2 = xr ? tap_ld<SMEM>(p + 2 * dx) : DVO_INV;
+        const float a0 = yu ? tap_ld<SMEM>(p - dy) : DVO_INV;
+        const float d0 = yd ? tap_ld<SMEM>(p + 2 * dy) : DVO_INV;
         float gx00 = DVO_INV, gy00 = DVO_INV; // texel (x0, y0)
         if (xl && xin && !(is_invalid(bm) || is_invalid(b1))) gx00 = b1 - bm;
         if (yu && yin && !(is_invalid(a0) || is_invalid(c0))) gy00 = c0 - a0;
         float gx10 = gx00, gy10 = gy00, gx01 = gx00, gy01 = gy00, gx11 = gx00, gy11 = gy00;
         if (xin) { // texel (x1, y0)
-            const float a1 = yu ? __ldg(p - dy + dx) : DVO_INV;
+            const float a1 = yu ? tap_ld<SMEM>(p - dy + dx) : DVO_INV;
             gx10 = (xr && !(is_invalid(b0) || is_invalid(b2))) ? b2 - b0 : DVO_INV;
             gy10 = (yu && yin && !(is_invalid(a1) || is_invalid(c1))) ? c1 - a1 : DVO_INV;
         }
         if (yin) { // texel (x0, y1)
-            const float cm = xl ? __ldg(p + dy - dx) : DVO_INV;
+            const float cm = xl ? tap_ld<SMEM>(p + dy - dx) : DVO_INV;
             gx01 = (xl && xin && !(is_invalid(cm) || is_invalid(c1))) ? c1 - cm : DVO_INV;
             gy01 = (yd && !(is_invalid(b0) || is_invalid(d0))) ? d0 - b0 : DVO_INV;
         }
         if (xin && yin) { // texel (x1, y1)
-            const float c2 = xr ? __ldg(p + dy + 2 * dx) : DVO_INV;
-            const float d1 = yd ? __ldg(p + 2 * dy + dx) : DVO_INV;
+            const float c2 = xr ? tap_ld<SMEM>(p + dy + 2 * dx) : DVO_INV;
+            const float d1 = yd ? tap_ld<SMEM>(p + 2 * dy + dx) : DVO_INV;
             gx11 = (xr && !(is_invalid(c0) || is_invalid(c2))) ? c2 - c0 : DVO_INV;
             gy11 = (yd && !(is_invalid(b1) || is_invalid(d1))) ? d1 - b1 : DVO_INV;
         }
@@ -853,7 +855,11 @@ __device__ __forceinline__ void propagate_stream(const Consts& c, const SlotDev*
 
 __device__ __forceinline__ unsigned int ld_volatile_u32(const unsigned int* p) { return *(const volatile unsigned int*)p; }
 
-__global__ void __launch_bounds__(TRK_THREADS, TRK_MINB) k_track(const __grid_constant__ Consts c, const TrackArgs a)
+// STAGE: coarse reference levels (strided views of the finest level) are gathered once per level into a dense shared-memory tile.
+// Pays when a stream's Gauss-Newton chain is the critical path (few streams, CTAs of a stream split over the GPU: +11 % GN
+// iterations/s on C1); costs co-residency with Mapper::update when 256 streams fill the GPU (early frames -12 %): host picks.
+template <bool STAGE>
+__device__ __forceinline__ void track_body(const Consts& c, const TrackArgs& a)
 {
     const int s = blockIdx.y, b = blockIdx.x, B = a.B;
     const int tid = threadIdx.x;
@@ -869,6 +875,8 @@ __global__ void __launch_bounds__(TRK_THREADS, TRK_MINB) k_track(const __grid_co
     __shared__ const float* s_ref;
     __shared__ const float2* s_ds;
     __shared__ unsigned int s_gen0;
+    __shared__ float s_img[STAGE ? TRK_STAGE_PIXELS : 1]; // the reference level as a dense tile (coarse levels only)
+    int staged_level = -1;
 
     // the ingest kernel before this one has completed (a no-op unless launched as a programmatic dependent); from here on
     // k_map_update's CTAs may be scheduled onto whatever this kernel leaves free (they wait per stream, see ReadyQ)
@@ -940,6 +948,18 @@ __global__ void __launch_bounds__(TRK_THREADS, TRK_MINB) k_track(const __grid_co
         // (4 x 8, column-major) want X[k][r] on lane 4 r + k BOTH, so one conflict-free LDS.32 + F2D feeds both operands and the
         // 8 x 8 fp64 accumulator is 2 registers pairs per lane.  Exact fp64 FMAs like the scalar code, ~30 instructions per batch
         // instead of 110 (one accumulator per sum through shared memory) or 58 registers (29 accumulators per thread).
+        // coarse levels are strided views of the finest level: with STAGE the reference level is gathered ONCE per level into a dense
+        // shared-memory tile (cullImage's getPixel rule applied), so the 12 taps per pixel are LDS instead of L1 lookups
+        const bool staged = STAGE && lv.t > 0 && g.n <= TRK_STAGE_PIXELS;
+        if (staged && staged_level != level) {
+            for (int i = tid; i < g.n; i += TRK_THREADS) {
+                const int yy = i / g.w, xx = i - yy * g.w;
+                s_img[i] = level_value(lv, __ldg(ref_gray + top_index(lv, xx, yy)));
+            }
+            staged_level = level;
+            __syncthreads();
+        }
+        LevelView sv; sv.w = g.w; sv.h = g.h; sv.t = 0; sv.W = g.w;
         const int lane = tid & 31, warp = tid >> 5;
         double c0 = 0.0, c1 = 0.0; // C[lane >> 2][2 (lane & 3) + {0, 1}] of X^T X
         int nvalid = 0;
@@ -986,7 +1006,7 @@ __global__ void __launch_bounds__(TRK_THREADS, TRK_MINB) k_track(const __grid_co
                     const float tz = (sT[8] * X + sT[9] * Y + sT[10] * Z) + sT[11];
                     const float wx = tx * g.fx / tz + g.cx;
                     const float wy = ty * g.fy / tz + g.cy;
-                    const Sample3 sm = sample_level<true>(ref_gray, lv, wx, wy);
+                    const Sample3 sm = (STAGE && staged) ? sample_level<true, STAGE>(s_img, sv, wx, wy) : sample_level<true>(ref_gray, lv, wx, wy);
                     // I_2 valid (optimize.cpp:46); warped point inside the image (:52-56); gradients valid (:61)
                     ok = sm.in && !is_invalid(sm.I) && !(wx < 0 || wy < 0 || (float)g.w <= wx || (float)g.h <= wy)
                          && !(is_invalid(sm.gx) || is_invalid(sm.gy));
@@ -1151,6 +1171,8 @@ __global__ void __launch_bounds__(TRK_THREADS, TRK_MINB) k_track(const __grid_co
         if (a.winner && do_propagate) propagate_stream(c, a.slots, m, a.winner + (size_t)s * c.lv[c.L - 1].n, s, tid, TRK_THREADS);
     }
 }
+__global__ void __launch_bounds__(TRK_THREADS, TRK_MINB) k_track(const __grid_constant__ Consts c, const TrackArgs a) { track_body<false>(c, a); }
+__global__ void __launch_bounds__(TRK_THREADS, TRK_MINB) k_track_staged(const __grid_constant__ Consts c, const TrackArgs a) { track_body<true>(c, a); }
 
 // pose tables for the granular Mapper::update entry point.  grid = (ceil(max_kf/64), S)
 __global__ void k_pose_tables(const __grid_constant__ Consts c, const SlotDev* __restrict__ slots, MapState* __restrict__ mst,
