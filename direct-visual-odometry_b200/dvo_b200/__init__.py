@@ -219,9 +219,12 @@ class Dvo:
 
     # ---- geometry
     def level_size(self, level):
-        w = C.c_int(); h = C.c_int()
-        self._ck(self.lib.dvo_level_size(self.ctx, level, C.byref(w), C.byref(h)))
-        return w.value, h.value
+        cache = self.__dict__.setdefault("_level_sizes", {})
+        if level not in cache:
+            w = C.c_int(); h = C.c_int()
+            self._ck(self.lib.dvo_level_size(self.ctx, level, C.byref(w), C.byref(h)))
+            cache[level] = (w.value, h.value)
+        return cache[level]
 
     def level_K(self, level):
         K = np.empty(9, np.float32)
