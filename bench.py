@@ -790,6 +790,20 @@ def run_gpu_arm(args, rank, world, local_rank, dist):
                          unit="thread instructions per ROI pixel of an updating stream" if units else None,
                          note="instruction-issue-bound kernel: IPC per SM against 4 schedulers x 1 instruction/clock; stall reasons and "
                               "per-pipe utilisation of the same capture: profiles/issue_%s.txt" % source_hash())
+    # the ceiling of the memory system for the dominant kernel's ACCESS PATTERN (random 128-byte line fills), measured with
+    # tools/gather_peak.cu and committed; beside `frac` (algorithmic bytes), never instead of it
+    pattern = None
+    try:
+        gp = json.load(open(os.path.join(ROOT, "profiles", "gather_peak.json")))
+        if traffic and cap and top["kernel"] == "k_map_update":
+            dram_gbs = traffic / (cap["duration_us"] * 1e-6) / 1e9
+            pattern = dict(source="profiles/gather_peak.json", dram_gbs_of_capture=dram_gbs,
+                           ceiling_line_walk_gbs=gp["line_walk_33_dram_gbs"], ceiling_random_taps_gbs=gp["random_taps_dram_gbs"],
+                           frac_of_line_walk_ceiling=dram_gbs / gp["line_walk_33_dram_gbs"],
+                           frac_of_random_ceiling=dram_gbs / gp["random_taps_dram_gbs"],
+                           frac_of_hbm_peak_by_traffic=dram_gbs / peak, note=gp["note"])
+    except (OSError, KeyError, ValueError):
+        pattern = None
     total_frames = world * S * K_ * F
     res = dict(
         value=total_frames / (r["ms"] * 1e-3), ms_per_step=r["ms"] / K_, ms_per_frame_step=r["ms"] / (K_ * F),
@@ -812,7 +826,7 @@ def run_gpu_arm(args, rank, world, local_rank, dist):
                       traffic=traffic, traffic_source=cap_name if cap else None, traffic_note=cap_why, peak_source=peak_src,
                       launches=top["launches"], avg_launch_us=top["avg_launch_us"],
                       algorithmic_bytes_per_launch=top["algorithmic_bytes_per_launch"], share_of_step=top["share"],
-                      bytes_model=top["bytes_model"], hierarchy=hierarchy, issue=issue,
+                      bytes_model=top["bytes_model"], hierarchy=hierarchy, issue=issue, pattern_ceiling=pattern,
                       measured_on="frames %d..%d of the sequences (steady state), launches kept apart by the event records"
                                   % (r["roof_first_frame"], r["roof_first_frame"] + R - 1)),
         kernels=table,
