@@ -289,6 +289,8 @@ extern "C" int dvo_create(dvo_ctx** out, const dvo_params* p)
         const int useful = cdiv(ntop, TRK_THREADS * 4); // >= 4 pixels per thread at the finest level
         if (B > useful) B = useful;
         if (B < 1) B = 1;
+        // tests: force the one-CTA-per-stream form (the one 256 streams take: fused propagate, overlapped Mapper::update) on few streams
+        if (const char* e = getenv("DVO_TRK_B")) { const int f = atoi(e); if (f >= 1 && f <= B) B = f; }
         ctx->trk_B = B;
     }
     CK(cudaMalloc(&ctx->d_partials, sizeof(double) * 32 * (size_t)S * ctx->trk_B));

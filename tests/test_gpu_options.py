@@ -200,16 +200,30 @@ def test_vo_is_schedule_independent_and_repeatable():
     Implement::propagate in the tracking epilogue or as the two wide kernels - and (d) the first 4 of them run alone, where
     k_track splits every stream over several CTAs (inter-CTA barrier), must match within the fp64 summation-order difference."""
     S, n = 48, 9
-    T0, M0 = _vo_run(S, n, {})
+    # 48 streams are fewer than the GPU's tracking slots, so by default every stream is split over CTAs and neither the overlap nor
+    # the fused propagate is in play: DVO_TRK_B=1 selects the one-CTA-per-stream form that 256 streams take.
+    one = {"DVO_TRK_B": "1"}
+    T0, M0 = _vo_run(S, n, one)
     for env in ({}, {"DVO_OVERLAP": "0"}, {"DVO_FUSE_PROP": "0"}, {"DVO_OVERLAP": "0", "DVO_FUSE_PROP": "0"}):
-        T1, M1 = _vo_run(S, n, env)
+        T1, M1 = _vo_run(S, n, dict(one, **env))
         assert T1.tobytes() == T0.tobytes(), env
         for s in range(S):
             for a, b in zip(M0[s], M1[s]):
                 assert a.tobytes() == b.tobytes(), (env, s)
+    # (e) 160 streams take that form by themselves (more streams than slots would split), under a different schedule of the ticket
+    # / ready list: the first 48 are the same sequences and must come out bit-identical
+    Tb, Mb = _vo_run(160, n, {})
+    assert Tb[:, :S].tobytes() == T0.tobytes()
+    for s in range(S):
+        for a, b in zip(M0[s], Mb[s]):
+            assert a.tobytes() == b.tobytes(), ("160 streams", s)
+    # (d) split forms: 48 streams x 6 CTAs and 4 streams x 10 CTAs (k_track_staged, inter-CTA barrier)
+    T6, M6 = _vo_run(S, n, {})
     T4, M4 = _vo_run(4, n, {})
-    assert np.abs(T4 - T0[:, :4]).max() <= 1e-4
-    kf_same = sum(M4[s][2].tobytes() == M0[s][2].tobytes() for s in range(4))
-    print("SCHEDULES: 48 streams x %d frames bit-identical across repeat / overlap / fused-propagate settings; 4-stream split-CTA run: "
-          "max pose difference %.3g, age maps identical in %d of 4 streams" % (n, float(np.abs(T4 - T0[:, :4]).max()), kf_same))
+    assert np.abs(T6 - T0).max() <= 1e-4 and np.abs(T4 - T0[:, :4]).max() <= 1e-4
+    kf6 = sum(M6[s][2].tobytes() == M0[s][2].tobytes() for s in range(S))
+    kf4 = sum(M4[s][2].tobytes() == M0[s][2].tobytes() for s in range(4))
+    print("SCHEDULES: 48 streams x %d frames, one CTA per stream: bit-identical across repeat / overlap / fused-propagate settings and as "
+          "the first 48 of 160 streams; split over CTAs: max pose difference %.3g (48 streams x 6 CTAs, age maps identical in %d of 48), "
+          "%.3g (4 streams x 10 CTAs, %d of 4)" % (n, float(np.abs(T6 - T0).max()), kf6, float(np.abs(T4 - T0[:, :4]).max()), kf4))
 

@@ -197,6 +197,41 @@ def test_vo_batched_streams_in_lockstep(orc):
     _run_pair(orc, g, K, d0, s0, n_streams=4)
 
 
+def test_vo_one_cta_per_stream_form_against_oracle(orc, seq160, monkeypatch):
+    """The form 256 streams take - one tracking CTA per stream, Implement::propagate in its epilogue, Mapper::update launched as a
+    programmatic dependent that serves streams in completion order - forced on 4 streams (DVO_TRK_B=1) and compared with the oracle
+    frame by frame like every other VO test: masks and maps bit-identical, updates within 1e-5."""
+    monkeypatch.setenv("DVO_TRK_B", "1")
+    g, d, poses, K = seq160
+    d0 = orc.cull_image(d[0], 2)
+    s0 = np.full_like(d0, 0.2)
+    n_kf, n_upd, _ = _run_pair(orc, g, K, d0, s0, n_streams=4)
+    assert n_upd >= 1
+
+
+def test_vo_one_cta_per_stream_form_keyframes(orc, monkeypatch):
+    """The same form through keyframe switches: Implement::propagate runs in the tracking kernel's epilogue."""
+    monkeypatch.setenv("DVO_TRK_B", "1")
+    from dvo_b200 import synth
+    g, d, poses, K = synth.sequence(16, 640, 480, seed=77, trans_step=0.012, rot_step_deg=0.3)
+    g = np.stack([punch_invalid(x, seed=i, n_rect=2, frac_px=0.002) for i, x in enumerate(g)])
+    d0 = orc.cull_image(d[0], 2)
+    s0 = np.full_like(d0, 0.3)
+    n_kf, n_upd, _ = _run_pair(orc, g, K, d0, s0, n_streams=2)
+    assert n_kf >= 3 and n_upd >= 3, (n_kf, n_upd)
+
+
+def test_vo_one_cta_per_stream_form_resets(orc, monkeypatch):
+    """... and through Gaussian::update resets: phase B (mt19937 order) after the overlapped phase A."""
+    monkeypatch.setenv("DVO_TRK_B", "1")
+    from dvo_b200 import synth
+    g, d, poses, K = synth.sequence(12, 640, 480, seed=5, trans_step=0.01, rot_step_deg=0.2)
+    d0 = orc.cull_image(d[0], 2)
+    s0 = np.full_like(d0, 0.4)
+    n_kf, n_upd, _ = _run_pair(orc, g, K, d0, s0, n_streams=2, accept_sigma_hi=5.0, min_movement=0.05)
+    assert n_upd >= 4
+
+
 def test_vo_streams_diverge(orc):
     """Streams with different motion take keyframes at different frames; each must equal its own
     single-stream oracle run (independent sequences)."""
